@@ -1,0 +1,280 @@
+#!/usr/bin/env python
+"""bench.py -- headline benchmark of the cavity projection timestep on B200.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl b200|reference]
+    (N > 1: python -m torch.distributed.run --nproc-per-node N ... bench.py --gpus N ...)
+
+A "step" is ONE projection timestep (fused predictor, 100 Jacobi sweeps, fused corrector) of
+the 16384 x 16384 fp32 lid-driven cavity per GPU (BASELINE.json configs[2]; weak scaling:
+16384*N x 16384 over N x-slabs). Prints ONE JSON line (rank 0).
+
+  value     Gcell-updates/s, device-resident state, CUDA events on the launching stream
+  roofline  the Jacobi kernel: algorithmic bytes (12 B x cells x sweeps-per-launch) / mean launch
+            time measured with events inside the same timed steps, vs MEASURED_PEAKS.json
+  e2e       same metric through the C ABI with HOST buffers: every step uploads u,v,p from pinned
+            host memory, runs one timestep, downloads u,v,p
+  cpu_baseline  the reference's threaded C++ solver (oracle/_ref) on a bounded sample, host cores
+--impl reference times the reference's own CPU implementation on this box's host cores.
+"""
+from __future__ import annotations
+
+import argparse
+import ctypes as C
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+import numpy as np  # noqa: E402
+
+GRID = int(os.environ.get("FLUIDB200_BENCH_GRID", 16384))
+SWEEPS = int(os.environ.get("FLUIDB200_BENCH_SWEEPS", 100))
+KMAX = int(os.environ.get("FLUIDB200_KMAX", 4))
+METRIC = "Gcell-updates/s per timestep (cavity 16384x16384 fp32, 100 Poisson sweeps/step)"
+UNIT = "Gcell-updates/s"
+# stable, well-conditioned parameters for a 16384^2 grid: hx = hy = 1
+DT, NU, RHO, LID = 0.001, 0.1, 1.0, 1.0
+
+
+def peaks():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    except Exception:
+        return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled DURING the timed region."""
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index=0):
+        self.index, self.rows, self.proc = index, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", f"--id={self.index}", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                 "-lms", "100"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._read, daemon=True)
+            self.thread.start()
+        except Exception:
+            self.proc = None
+        return self
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except Exception:
+            self.proc.kill()
+        sm = [float(r[0]) for r in self.rows if len(r) >= 6 and r[0].replace(".", "").isdigit()]
+        mx = [float(r[1]) for r in self.rows if len(r) >= 6 and r[1].replace(".", "").isdigit()]
+        names = ("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap")
+        reasons = sorted({n for r in self.rows if len(r) >= 6 for n, v in zip(names, r[2:6]) if v == "Active"})
+        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": reasons, "samples": len(sm)}
+
+
+# ---------------------------------------------------------------------------------------------
+# reference arm / cpu baseline: the reference's own CPU solvers (oracle/_ref), bounded sample
+# ---------------------------------------------------------------------------------------------
+def cpu_reference_run(n, sweeps, steps, kind="threaded"):
+    """Time `steps` timesteps of the reference CPU solver on an n x n cavity. Returns
+    (Gcell-updates/s, descriptor). Uses oracle/_ref when present, else the oracle port."""
+    import oracle
+    dt = float(np.float32(DT))
+    if oracle.have_ref():
+        _, ms = oracle.ref_solve(kind, n, n, wx=float(n - 1), wy=float(n - 1), dt=dt, nu=NU, rho=RHO,
+                                 K=sweeps, S=steps, want=())
+        cores = 8 if kind == "threaded" else 1   # THREADED_GRID_SIZE, ThreadedNavierStokes.h:13
+        what = "reference"
+    else:
+        o = oracle.Oracle(n, n, float(n - 1), float(n - 1)).set_cavity(LID)
+        o.time_step, o.num_poisson_iterations, o.num_iterations = dt, sweeps, steps
+        t = time.perf_counter(); o.solve(); ms = (time.perf_counter() - t) * 1e3
+        cores, what, kind = 1, "port", "serial"
+    val = n * n * steps / (ms * 1e-3) / 1e9
+    return val, ms, {"kind": what, "cores": cores,
+                     "sample": f"{n}x{n} cavity (hx=hy=1, dt={DT}), {sweeps} sweeps/step, {steps} step(s), "
+                               f"{kind} C++ solver, solve() wall time {ms / 1e3:.1f} s; host has {os.cpu_count()} cpus"}
+
+
+def run_reference_arm(args):
+    rank = int(os.environ.get("RANK", 0))
+    if rank != 0:
+        return
+    n = int(os.environ.get("FLUIDB200_REF_GRID", 1024))
+    for _ in range(args.warmup):
+        cpu_reference_run(n, SWEEPS, 1)
+    t0 = time.perf_counter()
+    total_ms = 0.0
+    for _ in range(args.steps):
+        _, ms, desc = cpu_reference_run(n, SWEEPS, 1)
+        total_ms += ms
+    wall = time.perf_counter() - t0
+    val = n * n * args.steps / (total_ms * 1e-3) / 1e9
+    desc["value"] = val
+    desc["unit"] = UNIT
+    print(json.dumps({
+        "impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": total_ms / args.steps,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": f"cavity {GRID}x{GRID} fp32, {SWEEPS} Poisson sweeps/step",
+                   "sample": desc["sample"], "wall_s": round(wall, 2)},
+        "cpu_baseline": desc,
+        "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }))
+
+
+# ---------------------------------------------------------------------------------------------
+# our arm
+# ---------------------------------------------------------------------------------------------
+def run_single(args):
+    import torch
+
+    from fluid_simulation_b200 import ParallelNavierStokes, _lib
+
+    torch.cuda.set_device(0)
+    lib = _lib.load()
+    _lib.check(lib, lib.fluidb200_set_device(0))
+    X = Y = GRID
+    s = ParallelNavierStokes(X, Y, float(X - 1), float(Y - 1), dtype=np.float32)
+    s.time_step, s.kinematic_viscosity, s.density = DT, NU, RHO
+    s.num_poisson_iterations, s.num_iterations = SWEEPS, 1
+    s.set_sweeps_per_launch(KMAX)
+    stream = torch.cuda.current_stream()
+    _lib.check(lib, lib.fluidb200_set_stream(s._h, stream.cuda_stream))  # so torch events bracket our launches
+    s.upload_cavity(LID)
+    s._push_params()
+    h = s._h
+
+    def step(ev=None):
+        _lib.check(lib, lib.fluidb200_step_predictor(h))
+        if ev is not None:
+            ev[0].record(stream)
+        _lib.check(lib, lib.fluidb200_step_poisson(h, SWEEPS))
+        if ev is not None:
+            ev[1].record(stream)
+        _lib.check(lib, lib.fluidb200_step_corrector(h))
+
+    for _ in range(max(args.warmup, 3)):
+        step()
+    torch.cuda.synchronize()
+
+    clocks = ClockSampler(0).start()
+    time.sleep(0.3)
+    phase_ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    launches0 = s.launch_count()
+    torch.cuda.synchronize()
+    e0.record(stream)
+    for i in range(args.steps):
+        step(phase_ev[i])
+    e1.record(stream)
+    torch.cuda.synchronize()
+    clk = clocks.stop()
+    launches = s.launch_count() - launches0
+    total_ms = e0.elapsed_time(e1)
+    jac_ms = sum(a.elapsed_time(b) for a, b in phase_ev)
+    cells = X * Y
+    value = cells * args.steps / (total_ms * 1e-3) / 1e9
+
+    n_jac = args.steps * ((SWEEPS + KMAX - 1) // KMAX)
+    full = SWEEPS // KMAX                      # launches with the full blocking depth
+    # mean duration of a depth-KMAX launch (the remainder launch, if any, is charged pro rata by sweeps)
+    jac_launch_ms = jac_ms / args.steps * KMAX / SWEEPS if full else jac_ms / n_jac
+    alg_bytes = 12.0 * cells * KMAX
+    achieved = alg_bytes / (jac_launch_ms * 1e-3) / 1e9
+    peak, peak_src = peaks()
+    roofline = {"bound": "hbm", "kernel": f"jacobi_kernel<float,4,{KMAX},false>", "achieved": achieved, "peak": peak,
+                "unit": "GB/s", "frac": achieved / peak, "traffic": None,
+                "peak_source": peak_src, "sweeps_per_launch": KMAX,
+                "launch_ms": jac_launch_ms, "algorithmic_bytes_per_launch": alg_bytes,
+                "gcell_sweeps_per_s": cells * SWEEPS * args.steps / (jac_ms * 1e-3) / 1e9,
+                "share_of_step": jac_ms / total_ms,
+                "note": "achieved = algorithmic bytes (12 B/cell/sweep x sweeps_per_launch) / launch time; with temporal "
+                        "blocking the DRAM traffic per launch is ~12 B/cell, so frac > 1 is expected; see profiles/"}
+
+    # ---- e2e: host buffers in, host buffers out, every step ---------------------------------
+    e2e_steps = max(1, min(args.steps, int(os.environ.get("FLUIDB200_E2E_STEPS", 3))))
+    host = [torch.zeros((X, Y), dtype=torch.float32).pin_memory() for _ in range(3)]
+    host[0][:, Y - 1] = LID
+    fields = (C.c_void_p * _lib.NUM_FIELDS)()
+    for i in range(3):
+        fields[i] = host[i].data_ptr()
+
+    def e2e_step():
+        _lib.check(lib, lib.fluidb200_upload(h, fields, None, None))
+        _lib.check(lib, lib.fluidb200_solve(h))
+        for i in range(3):
+            _lib.check(lib, lib.fluidb200_download(h, i, host[i].data_ptr()))
+
+    e2e_step()  # warm-up
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    for _ in range(e2e_steps):
+        e2e_step()
+    torch.cuda.synchronize()
+    e2e_s = time.perf_counter() - t0
+    e2e = {"value": cells * e2e_steps / e2e_s / 1e9, "unit": UNIT, "h2d_bytes_per_step": 3 * cells * 4,
+           "d2h_bytes_per_step": 3 * cells * 4, "steps": e2e_steps, "ms_per_step": e2e_s / e2e_steps * 1e3,
+           "api": "fluidb200_upload(u,v,p pinned host) + fluidb200_solve(1 step) + fluidb200_download(u,v,p)"}
+    assert bool(torch.isfinite(host[0]).all()), "non-finite field after the e2e steps"
+    s.close()
+
+    # ---- cpu baseline: bounded sample of the same workload on the host cores ---------------
+    try:
+        cv, _, cdesc = cpu_reference_run(int(os.environ.get("FLUIDB200_CPU_GRID", 1536)), SWEEPS, 2)
+        cdesc.update({"value": cv, "unit": UNIT})
+    except Exception as ex:  # the checker is optional for the measurement itself
+        cdesc = {"value": None, "unit": UNIT, "cores": 0, "kind": "unavailable", "sample": repr(ex)}
+
+    return {
+        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": 1, "steps": args.steps, "warmup": max(args.warmup, 3),
+        "ms_per_step": total_ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "f32", "data": "synthetic",
+        "config": {"workload": f"cavity {X}x{Y} fp32, {SWEEPS} Poisson sweeps/step, 1 GPU (BASELINE.json configs[2])",
+                   "dt": DT, "nu": NU, "rho": RHO, "hx": 1.0, "hy": 1.0, "sweeps_per_launch": KMAX,
+                   "l2": "fields are 1.07 GB each, >> 126 MB L2, no flush needed",
+                   "effective_GBps_step": (40 + 12 * SWEEPS) * cells * args.steps / (total_ms * 1e-3) / 1e9},
+        "roofline": roofline, "cpu_baseline": cdesc, "e2e": e2e, "gpu_launches": int(launches), "clocks": clk,
+    }
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    args = ap.parse_args()
+    if args.impl == "reference":
+        run_reference_arm(args)
+        return
+    if args.gpus > 1 or int(os.environ.get("WORLD_SIZE", 1)) > 1:
+        from fluid_simulation_b200.distributed import bench_distributed
+        out = bench_distributed(args, GRID, SWEEPS, KMAX, dict(dt=DT, nu=NU, rho=RHO, lid=LID), METRIC, UNIT)
+    else:
+        out = run_single(args)
+    if out is not None:
+        print(json.dumps(out))
+
+
+if __name__ == "__main__":
+    main()

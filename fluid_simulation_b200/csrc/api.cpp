@@ -1,0 +1,714 @@
+// api.cpp -- host side of the C ABI declared in include/fluidb200.h: argument validation,
+// strip/chunk planning, the stateless launch entry points and the stateful solver handle.
+// Device work goes through backend.h only (kernels.cu in the product).
+#include <math.h>
+#include <stdarg.h>
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+
+#include <algorithm>
+#include <new>
+#include <vector>
+
+#include "../../include/fluidb200.h"
+#include "backend.h"
+
+namespace {
+
+thread_local char g_err[512] = "";
+
+int fail(int code, const char* fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+    return code;
+}
+int fail_backend(const char* what) {
+    return fail(FLUIDB200_ECUDA, "%s: %s", what, fbk::be_last_error_string());
+}
+#define BE_CHECK(expr, what)                      \
+    do {                                          \
+        if ((expr) != 0) return fail_backend(what); \
+    } while (0)
+
+int env_int(const char* name, int dflt) {
+    const char* s = getenv(name);
+    if (!s || !*s) return dflt;
+    return atoi(s);
+}
+
+template <typename T> constexpr int vec_width() { return 16 / (int)sizeof(T); }
+inline int halo_cols(int sweeps) { return (sweeps + 3) & ~3; }
+
+template <typename T> int num_strips(int Y, int H) {
+    const int W = 32 * vec_width<T>();
+    const int S = W - 2 * H;
+    const int n = (Y - H + S - 1) / S;
+    return n < 1 ? 1 : n;
+}
+
+// Split `n` output rows into chunks. More chunks = more warps in flight, but every chunk
+// recomputes `halo` rows at each end. A chunk that touches a wall must hold >= 2 rows because
+// the wall row is derived while its neighbour row is produced.
+void plan_chunks(int n, int halo, int nstrips, int* rpc_out, int* nchunks_out) {
+    const long long target_tasks = env_int("FLUIDB200_TARGET_TASKS", 148 * 20 * 4);
+    int min_rpc = env_int("FLUIDB200_MIN_RPC", 0);
+    if (min_rpc <= 0) min_rpc = std::max(8, 8 * halo);
+    long long want_chunks = (target_tasks + nstrips - 1) / nstrips;
+    if (want_chunks < 1) want_chunks = 1;
+    int rpc = (int)((n + want_chunks - 1) / want_chunks);
+    rpc = std::max(rpc, min_rpc);
+    const int fixed = env_int("FLUIDB200_RPC", 0);
+    if (fixed > 0) rpc = fixed;
+    rpc = std::max(2, std::min(rpc, n));
+    while (rpc < n && n % rpc == 1) ++rpc;  // never leave a 1-row tail chunk
+    int nchunks = (n + rpc - 1) / rpc;
+    if (nchunks > 65535) {
+        rpc = (n + 65534) / 65535;
+        while (rpc < n && n % rpc == 1) ++rpc;
+        nchunks = (n + rpc - 1) / rpc;
+    }
+    *rpc_out = rpc;
+    *nchunks_out = nchunks;
+}
+
+int check_slab(const fluidb200_slab* g) {
+    if (!g) return fail(FLUIDB200_EINVAL, "slab is NULL");
+    if (g->dtype != FLUIDB200_F32 && g->dtype != FLUIDB200_F64)
+        return fail(FLUIDB200_EINVAL, "dtype must be FLUIDB200_F32 or FLUIDB200_F64, got %d", g->dtype);
+    if (g->X < 3 || g->Y < 3)
+        return fail(FLUIDB200_EINVAL, "box must be at least 3x3 (got %dx%d): no interior cells", g->X, g->Y);
+    if (g->pitch < g->Y || g->pitch % 32 != 0)
+        return fail(FLUIDB200_EINVAL, "pitch %lld must be >= Y=%d and a multiple of 32 elements",
+                    (long long)g->pitch, g->Y);
+    if (g->row0 < 0 || g->rows < 1 || (long long)g->row0 + g->rows > g->X)
+        return fail(FLUIDB200_EINVAL, "local rows [%d,%d) outside the box [0,%d)", g->row0,
+                    g->row0 + g->rows, g->X);
+    if (!(g->hx > 0) || !(g->hy > 0)) return fail(FLUIDB200_EINVAL, "element lengths must be positive");
+    return 0;
+}
+int check_ptr(const void* p, const char* name) {
+    if (!p) return fail(FLUIDB200_EINVAL, "%s is NULL", name);
+    if ((uintptr_t)p % 16 != 0) return fail(FLUIDB200_EINVAL, "%s must be 16-byte aligned", name);
+    return 0;
+}
+// rows [lo,hi) to write, needing `halo` extra input rows on each non-wall side
+int check_range(const fluidb200_slab* g, int lo, int hi, int halo, const char* what) {
+    if (lo < 0 || hi > g->X || lo >= hi)
+        return fail(FLUIDB200_EINVAL, "%s: row range [%d,%d) is empty or outside [0,%d)", what, lo, hi, g->X);
+    const int need_lo = std::max(lo - halo, 0), need_hi = std::min(hi + halo, g->X);
+    if (need_lo < g->row0 || need_hi > g->row0 + g->rows)
+        return fail(FLUIDB200_EINVAL, "%s: needs rows [%d,%d) but the slab holds [%d,%d)", what, need_lo,
+                    need_hi, g->row0, g->row0 + g->rows);
+    if ((lo == 0 && hi < 2) || (hi == g->X && lo > g->X - 2))
+        return fail(FLUIDB200_EINVAL, "%s: a range touching a wall must include the row next to it", what);
+    return 0;
+}
+
+template <typename T> fb::Edges<T> to_dev_edges(const fluidb200_edges* e) {
+    fb::Edges<T> d;
+    for (int i = 0; i < 4; ++i) {
+        d.mode[i] = e ? e->mode[i] : FLUIDB200_EDGE_UNSET;
+        d.cval[i] = e ? (T)e->cval[i] : T(0);
+        d.val[i] = e ? (const T*)e->val[i] : nullptr;
+        d.set[i] = e ? e->set[i] : nullptr;
+    }
+    return d;
+}
+int check_edges(const fluidb200_edges* e, const char* name) {
+    if (!e) return fail(FLUIDB200_EINVAL, "%s is NULL", name);
+    for (int i = 0; i < 4; ++i) {
+        if (e->mode[i] < 0 || e->mode[i] > 2)
+            return fail(FLUIDB200_EINVAL, "%s: edge %d has bad mode %d", name, i, e->mode[i]);
+        if (e->mode[i] == FLUIDB200_EDGE_ARRAY && (!e->val[i] || !e->set[i]))
+            return fail(FLUIDB200_EINVAL, "%s: edge %d is ARRAY but val/set is NULL", name, i);
+    }
+    return 0;
+}
+fb::Geom make_geom(const fluidb200_slab* g, int nstrips, int rpc) {
+    fb::Geom q;
+    q.pitch = g->pitch;
+    q.X = g->X;
+    q.Y = g->Y;
+    q.row0 = g->row0;
+    q.rows = g->rows;
+    q.nstrips = nstrips;
+    q.rows_per_chunk = rpc;
+    return q;
+}
+
+template <typename T>
+int predictor_t(const fluidb200_slab* g, const void* u, const void* v, void* us, void* vs, void* rhs,
+                double dt, double nu, double rho, int star_lo, int star_hi, int rhs_lo, int rhs_hi,
+                void* stream) {
+    fb::PredictorArgs<T> a;
+    a.u = (const T*)u; a.v = (const T*)v;
+    a.us = (T*)us; a.vs = (T*)vs; a.rhs = (T*)rhs;
+    a.hx = (T)g->hx; a.hy = (T)g->hy;
+    a.hx2 = (T)2 * a.hx; a.hy2 = (T)2 * a.hy;
+    a.nu = (T)nu; a.dt = (T)dt;
+    a.rho_over_dt = (T)rho / (T)dt;  // (density / time_step) evaluated in T, SerialNavierStokes.cpp:332
+    a.star_lo = star_lo; a.star_hi = star_hi; a.rhs_lo = rhs_lo; a.rhs_hi = rhs_hi;
+    a.lo = std::min(star_lo, rhs_lo);
+    a.hi = std::max(star_hi, rhs_hi);
+    const int nstrips = num_strips<T>(g->Y, 4);
+    int rpc, nchunks;
+    plan_chunks(a.hi - a.lo, 2, nstrips, &rpc, &nchunks);
+    a.g = make_geom(g, nstrips, rpc);
+    BE_CHECK(fbk::launch_predictor<T>(a, nchunks, stream), "predictor launch");
+    return 0;
+}
+
+template <typename T>
+int poisson_t(const fluidb200_slab* g, const void* p_in, void* p_out, const void* rhs,
+              const fluidb200_edges* e, const fluidb200_mask* mask, int sweeps, int out_lo, int out_hi,
+              void* stream) {
+    fb::JacobiArgs<T> a;
+    a.p_in = (const T*)p_in; a.p_out = (T*)p_out; a.rhs = (const T*)rhs;
+    const bool use_mask = mask && mask->set;
+    a.mset = use_mask ? mask->set : nullptr;
+    a.mval = use_mask ? (const T*)mask->val : nullptr;
+    a.hx = (T)g->hx; a.hy = (T)g->hy;
+    a.out_lo = out_lo; a.out_hi = out_hi;
+    a.e = to_dev_edges<T>(e);
+    const int nstrips = num_strips<T>(g->Y, halo_cols(sweeps));
+    int rpc, nchunks;
+    plan_chunks(out_hi - out_lo, sweeps, nstrips, &rpc, &nchunks);
+    a.g = make_geom(g, nstrips, rpc);
+    BE_CHECK(fbk::launch_jacobi<T>(a, sweeps, use_mask, nchunks, stream), "poisson launch");
+    return 0;
+}
+
+template <typename T>
+int corrector_t(const fluidb200_slab* g, const void* p, const void* us, const void* vs, void* u, void* v,
+                const fluidb200_edges* eu, const fluidb200_edges* ev, const fluidb200_mask* mu,
+                const fluidb200_mask* mv, double dt, double rho, int out_lo, int out_hi, void* stream) {
+    fb::CorrectorArgs<T> a;
+    a.p = (const T*)p; a.us = (const T*)us; a.vs = (const T*)vs;
+    a.u = (T*)u; a.v = (T*)v;
+    const bool um = mu && mu->set, vm = mv && mv->set;
+    a.uset = um ? mu->set : nullptr; a.uval = um ? (const T*)mu->val : nullptr;
+    a.vset = vm ? mv->set : nullptr; a.vval = vm ? (const T*)mv->val : nullptr;
+    a.hx = (T)g->hx; a.hy = (T)g->hy;
+    a.hx2 = (T)2 * a.hx; a.hy2 = (T)2 * a.hy;
+    a.dt_over_rho = (T)dt / (T)rho;  // (time_step / density) in T, SerialNavierStokes.cpp:346
+    a.out_lo = out_lo; a.out_hi = out_hi;
+    a.eu = to_dev_edges<T>(eu);
+    a.ev = to_dev_edges<T>(ev);
+    const int nstrips = num_strips<T>(g->Y, 4);
+    int rpc, nchunks;
+    plan_chunks(out_hi - out_lo, 1, nstrips, &rpc, &nchunks);
+    a.g = make_geom(g, nstrips, rpc);
+    BE_CHECK(fbk::launch_corrector<T>(a, um || vm, nchunks, stream), "corrector launch");
+    return 0;
+}
+
+}  // namespace
+
+// =========================================================================================
+// stateless entry points
+// =========================================================================================
+extern "C" int fluidb200_predictor(const fluidb200_slab* g, const void* u, const void* v, void* u_next,
+                                   void* v_next, void* rhs, double dt, double nu, double rho, int star_lo,
+                                   int star_hi, int rhs_lo, int rhs_hi, void* stream) {
+    int rc;
+    if ((rc = check_slab(g))) return rc;
+    if ((rc = check_ptr(u, "u")) || (rc = check_ptr(v, "v")) || (rc = check_ptr(u_next, "u_next")) ||
+        (rc = check_ptr(v_next, "v_next")) || (rc = check_ptr(rhs, "rhs")))
+        return rc;
+    if (!(dt != 0)) return fail(FLUIDB200_EINVAL, "time_step must be non-zero");
+    if ((rc = check_range(g, rhs_lo, rhs_hi, 2, "predictor rhs"))) return rc;
+    if ((rc = check_range(g, star_lo, star_hi, 1, "predictor u_next"))) return rc;
+    return g->dtype == FLUIDB200_F32
+               ? predictor_t<float>(g, u, v, u_next, v_next, rhs, dt, nu, rho, star_lo, star_hi, rhs_lo, rhs_hi, stream)
+               : predictor_t<double>(g, u, v, u_next, v_next, rhs, dt, nu, rho, star_lo, star_hi, rhs_lo, rhs_hi, stream);
+}
+
+extern "C" int fluidb200_poisson_sweeps(const fluidb200_slab* g, const void* p_in, void* p_out,
+                                        const void* rhs, const fluidb200_edges* p_edges,
+                                        const fluidb200_mask* mask, int sweeps, int out_lo, int out_hi,
+                                        void* stream) {
+    int rc;
+    if ((rc = check_slab(g))) return rc;
+    if ((rc = check_ptr(p_in, "p_in")) || (rc = check_ptr(p_out, "p_out")) || (rc = check_ptr(rhs, "rhs")))
+        return rc;
+    if (p_in == p_out) return fail(FLUIDB200_EINVAL, "p_out must not alias p_in (Jacobi ping-pong)");
+    if ((rc = check_edges(p_edges, "p_edges"))) return rc;
+    if (sweeps < 1 || sweeps > FLUIDB200_MAX_SWEEPS_PER_LAUNCH)
+        return fail(FLUIDB200_EINVAL, "sweeps per launch must be in [1,%d], got %d",
+                    FLUIDB200_MAX_SWEEPS_PER_LAUNCH, sweeps);
+    if (mask && mask->set) {
+        if (sweeps != 1) return fail(FLUIDB200_EINVAL, "with an interior mask only sweeps == 1 is supported");
+        if (!mask->val) return fail(FLUIDB200_EINVAL, "mask.val is NULL");
+    }
+    if ((rc = check_range(g, out_lo, out_hi, sweeps, "poisson"))) return rc;
+    return g->dtype == FLUIDB200_F32
+               ? poisson_t<float>(g, p_in, p_out, rhs, p_edges, mask, sweeps, out_lo, out_hi, stream)
+               : poisson_t<double>(g, p_in, p_out, rhs, p_edges, mask, sweeps, out_lo, out_hi, stream);
+}
+
+extern "C" int fluidb200_corrector(const fluidb200_slab* g, const void* p, const void* u_next,
+                                   const void* v_next, void* u, void* v, const fluidb200_edges* u_edges,
+                                   const fluidb200_edges* v_edges, const fluidb200_mask* u_mask,
+                                   const fluidb200_mask* v_mask, double dt, double rho, int out_lo,
+                                   int out_hi, void* stream) {
+    int rc;
+    if ((rc = check_slab(g))) return rc;
+    if ((rc = check_ptr(p, "p")) || (rc = check_ptr(u_next, "u_next")) || (rc = check_ptr(v_next, "v_next")) ||
+        (rc = check_ptr(u, "u")) || (rc = check_ptr(v, "v")))
+        return rc;
+    if ((rc = check_edges(u_edges, "u_edges")) || (rc = check_edges(v_edges, "v_edges"))) return rc;
+    if (!(rho != 0)) return fail(FLUIDB200_EINVAL, "density must be non-zero");
+    if ((u_mask && u_mask->set && !u_mask->val) || (v_mask && v_mask->set && !v_mask->val))
+        return fail(FLUIDB200_EINVAL, "mask.val is NULL");
+    if ((rc = check_range(g, out_lo, out_hi, 1, "corrector"))) return rc;
+    return g->dtype == FLUIDB200_F32
+               ? corrector_t<float>(g, p, u_next, v_next, u, v, u_edges, v_edges, u_mask, v_mask, dt, rho, out_lo, out_hi, stream)
+               : corrector_t<double>(g, p, u_next, v_next, u, v, u_edges, v_edges, u_mask, v_mask, dt, rho, out_lo, out_hi, stream);
+}
+
+extern "C" int fluidb200_init_cavity(const fluidb200_slab* g, void* u, void* v, void* p, void* u_next,
+                                     void* v_next, void* p_next, void* rhs, double lid_velocity,
+                                     void* stream) {
+    int rc;
+    if ((rc = check_slab(g))) return rc;
+    void* f[7] = {u, v, p, u_next, v_next, p_next, rhs};
+    for (int i = 0; i < 7; ++i)
+        if (f[i] && (uintptr_t)f[i] % 16 != 0) return fail(FLUIDB200_EINVAL, "field %d must be 16-byte aligned", i);
+    if (g->dtype == FLUIDB200_F32) {
+        float* ff[7];
+        for (int i = 0; i < 7; ++i) ff[i] = (float*)f[i];
+        BE_CHECK(fbk::launch_init_cavity<float>(ff, g->pitch, g->X, g->Y, g->row0, g->rows, (float)lid_velocity, stream),
+                 "init_cavity launch");
+    } else {
+        double* ff[7];
+        for (int i = 0; i < 7; ++i) ff[i] = (double*)f[i];
+        BE_CHECK(fbk::launch_init_cavity<double>(ff, g->pitch, g->X, g->Y, g->row0, g->rows, lid_velocity, stream),
+                 "init_cavity launch");
+    }
+    return 0;
+}
+
+extern "C" int fluidb200_cavity_edges(char field, double lid_velocity, fluidb200_edges* out) {
+    if (!out) return fail(FLUIDB200_EINVAL, "out is NULL");
+    memset(out, 0, sizeof(*out));
+    if (field == 'u' || field == 'v') {
+        for (int i = 0; i < 4; ++i) out->mode[i] = FLUIDB200_EDGE_CONST;
+        out->cval[FLUIDB200_EDGE_TOP] = (field == 'u') ? lid_velocity : 0.0;
+    } else if (field == 'p') {
+        out->mode[FLUIDB200_EDGE_TOP] = FLUIDB200_EDGE_CONST;
+    } else {
+        return fail(FLUIDB200_EINVAL, "field must be 'u', 'v' or 'p'");
+    }
+    return 0;
+}
+
+// =========================================================================================
+// stateful solver handle
+// =========================================================================================
+struct fluidb200_solver {
+    int dtype = 0, X = 0, Y = 0;
+    double wx = 0, wy = 0;
+    double hx = 0, hy = 0;           // exact T values
+    double dt = 0.001, nu = 0.1, rho = 1.0;
+    int K = 50, S = 1000;            // NavierStokesSolver.h:22-26 defaults
+    int64_t pitch = 0;
+    size_t esize = 4;
+    void* f[FLUIDB200_NUM_FIELDS] = {};
+    bool p_next_is_p = false;        // after any sweep the reference has p_next == p
+    fluidb200_edges edges[3] = {};   // u, v, p
+    void* edge_val[3][4] = {};
+    uint8_t* edge_set[3][4] = {};
+    fluidb200_mask mask[3] = {};     // interior flags (device), NULL when none
+    void* stream = nullptr;
+    bool own_stream = false;
+    int kmax = 4;
+    bool use_graph = false;
+    void* graph[2] = {nullptr, nullptr};  // one timestep, for each ping-pong parity
+    double graph_key[6] = {};
+    void* graph_home_p = nullptr;     // where p lived when graph[0] was captured
+    int64_t launches = 0;
+};
+
+namespace {
+
+size_t field_bytes(const fluidb200_solver* s) { return (size_t)s->X * (size_t)s->pitch * s->esize; }
+
+void fill_slab(const fluidb200_solver* s, fluidb200_slab* g) {
+    g->dtype = s->dtype; g->X = s->X; g->Y = s->Y; g->pitch = s->pitch;
+    g->row0 = 0; g->rows = s->X; g->hx = s->hx; g->hy = s->hy;
+}
+
+void drop_graphs(fluidb200_solver* s) {
+    for (int i = 0; i < 2; ++i)
+        if (s->graph[i]) { fbk::be_graph_destroy(s->graph[i]); s->graph[i] = nullptr; }
+}
+
+void free_bc(fluidb200_solver* s, int f) {
+    for (int e = 0; e < 4; ++e) {
+        if (s->edge_val[f][e]) fbk::be_free(s->edge_val[f][e]);
+        if (s->edge_set[f][e]) fbk::be_free(s->edge_set[f][e]);
+        s->edge_val[f][e] = nullptr; s->edge_set[f][e] = nullptr;
+        s->edges[f].mode[e] = FLUIDB200_EDGE_UNSET; s->edges[f].cval[e] = 0;
+        s->edges[f].val[e] = nullptr; s->edges[f].set[e] = nullptr;
+    }
+    if (s->mask[f].set) fbk::be_free((void*)s->mask[f].set);
+    if (s->mask[f].val) fbk::be_free((void*)s->mask[f].val);
+    s->mask[f].set = nullptr; s->mask[f].val = nullptr;
+}
+
+// Turn dense host flag/value arrays of one field into the edge description (+ interior mask).
+template <typename T>
+int upload_bc_t(fluidb200_solver* s, int f, const T* val, const uint8_t* set) {
+    const int X = s->X, Y = s->Y;
+    free_bc(s, f);
+    drop_graphs(s);
+    for (int e = 0; e < 4; ++e) {
+        const bool along_x = (e == FLUIDB200_EDGE_BOTTOM || e == FLUIDB200_EDGE_TOP);
+        const int len = along_x ? X : Y;
+        const int first = along_x ? 0 : 1, last = along_x ? X - 1 : Y - 2;  // entries the kernels use
+        std::vector<T> ev(len, T(0));
+        std::vector<uint8_t> es(len, 0);
+        for (int i = 0; i < len; ++i) {
+            size_t idx;
+            if (e == FLUIDB200_EDGE_BOTTOM) idx = (size_t)i * Y;
+            else if (e == FLUIDB200_EDGE_TOP) idx = (size_t)i * Y + (Y - 1);
+            else if (e == FLUIDB200_EDGE_LEFT) idx = (size_t)i;
+            else idx = (size_t)(X - 1) * Y + i;
+            es[i] = set[idx] ? 1 : 0;
+            ev[i] = val[idx];
+        }
+        bool any = false, all = true, same = true;
+        for (int i = first; i <= last; ++i) {
+            any = any || es[i];
+            all = all && es[i];
+            if (memcmp(&ev[i], &ev[first], sizeof(T)) != 0) same = false;
+        }
+        if (!any) {
+            s->edges[f].mode[e] = FLUIDB200_EDGE_UNSET;
+        } else if (all && same) {
+            s->edges[f].mode[e] = FLUIDB200_EDGE_CONST;
+            s->edges[f].cval[e] = (double)ev[first];
+        } else {
+            void *dv = nullptr, *ds = nullptr;
+            BE_CHECK(fbk::be_malloc(&dv, len * sizeof(T)), "edge alloc");
+            s->edge_val[f][e] = dv;
+            BE_CHECK(fbk::be_malloc(&ds, len), "edge alloc");
+            s->edge_set[f][e] = (uint8_t*)ds;
+            BE_CHECK(fbk::be_memcpy_async(dv, ev.data(), len * sizeof(T), fbk::H2D, s->stream), "edge upload");
+            BE_CHECK(fbk::be_memcpy_async(ds, es.data(), len, fbk::H2D, s->stream), "edge upload");
+            BE_CHECK(fbk::be_stream_sync(s->stream), "edge upload");  // host vectors go out of scope
+            s->edges[f].mode[e] = FLUIDB200_EDGE_ARRAY;
+            s->edges[f].val[e] = dv;
+            s->edges[f].set[e] = (const uint8_t*)ds;
+        }
+    }
+    // interior flags -> dense pitched mask (the general-BC path)
+    bool interior = false;
+    for (int x = 1; x < X - 1 && !interior; ++x)
+        for (int y = 1; y < Y - 1; ++y)
+            if (set[(size_t)x * Y + y]) { interior = true; break; }
+    if (interior) {
+        void *ds = nullptr, *dv = nullptr;
+        const size_t n = (size_t)X * s->pitch;
+        BE_CHECK(fbk::be_malloc(&ds, n), "mask alloc");
+        s->mask[f].set = (const uint8_t*)ds;
+        BE_CHECK(fbk::be_malloc(&dv, n * sizeof(T)), "mask alloc");
+        s->mask[f].val = dv;
+        BE_CHECK(fbk::be_memset_async(ds, 0, n, s->stream), "mask clear");
+        BE_CHECK(fbk::be_memset_async(dv, 0, n * sizeof(T), s->stream), "mask clear");
+        BE_CHECK(fbk::be_memcpy2d_async(ds, s->pitch, set, Y, Y, X, fbk::H2D, s->stream), "mask upload");
+        BE_CHECK(fbk::be_memcpy2d_async(dv, s->pitch * sizeof(T), val, Y * sizeof(T), Y * sizeof(T), X, fbk::H2D,
+                                        s->stream), "mask upload");
+        BE_CHECK(fbk::be_stream_sync(s->stream), "mask upload");
+    }
+    return 0;
+}
+
+int step_predictor(fluidb200_solver* s) {
+    fluidb200_slab g;
+    fill_slab(s, &g);
+    int rc = fluidb200_predictor(&g, s->f[FLUIDB200_FIELD_U], s->f[FLUIDB200_FIELD_V], s->f[FLUIDB200_FIELD_U_NEXT],
+                                 s->f[FLUIDB200_FIELD_V_NEXT], s->f[FLUIDB200_FIELD_RHS], s->dt, s->nu, s->rho, 0,
+                                 s->X, 0, s->X, s->stream);
+    if (rc == 0) s->launches++;
+    return rc;
+}
+
+int step_poisson(fluidb200_solver* s, int sweeps) {
+    fluidb200_slab g;
+    fill_slab(s, &g);
+    const bool masked = s->mask[2].set != nullptr;
+    const int kmax = masked ? 1 : std::max(1, std::min(s->kmax, FLUIDB200_MAX_SWEEPS_PER_LAUNCH));
+    int left = sweeps;
+    while (left > 0) {
+        const int k = std::min(kmax, left);
+        int rc = fluidb200_poisson_sweeps(&g, s->f[FLUIDB200_FIELD_P], s->f[FLUIDB200_FIELD_P_NEXT],
+                                          s->f[FLUIDB200_FIELD_RHS], &s->edges[2], masked ? &s->mask[2] : nullptr, k, 0,
+                                          s->X, s->stream);
+        if (rc) return rc;
+        std::swap(s->f[FLUIDB200_FIELD_P], s->f[FLUIDB200_FIELD_P_NEXT]);  // ping-pong instead of p = p_next
+        s->p_next_is_p = true;
+        s->launches++;
+        left -= k;
+    }
+    return 0;
+}
+
+int step_corrector(fluidb200_solver* s) {
+    fluidb200_slab g;
+    fill_slab(s, &g);
+    int rc = fluidb200_corrector(&g, s->f[FLUIDB200_FIELD_P], s->f[FLUIDB200_FIELD_U_NEXT], s->f[FLUIDB200_FIELD_V_NEXT],
+                                 s->f[FLUIDB200_FIELD_U], s->f[FLUIDB200_FIELD_V], &s->edges[0], &s->edges[1],
+                                 s->mask[0].set ? &s->mask[0] : nullptr, s->mask[1].set ? &s->mask[1] : nullptr, s->dt,
+                                 s->rho, 0, s->X, s->stream);
+    if (rc == 0) s->launches++;
+    return rc;
+}
+
+int one_step(fluidb200_solver* s) {
+    int rc;
+    if ((rc = step_predictor(s))) return rc;
+    if ((rc = step_poisson(s, s->K))) return rc;
+    return step_corrector(s);
+}
+
+int launches_per_step(const fluidb200_solver* s) {
+    const int kmax = s->mask[2].set ? 1 : std::max(1, std::min(s->kmax, FLUIDB200_MAX_SWEEPS_PER_LAUNCH));
+    return 2 + (s->K + kmax - 1) / kmax;
+}
+
+}  // namespace
+
+extern "C" int fluidb200_create(fluidb200_solver** out, int dtype, int X, int Y, double domain_x, double domain_y) {
+    if (!out) return fail(FLUIDB200_EINVAL, "out is NULL");
+    *out = nullptr;
+    if (dtype != FLUIDB200_F32 && dtype != FLUIDB200_F64) return fail(FLUIDB200_EINVAL, "bad dtype %d", dtype);
+    if (X < 3 || Y < 3) return fail(FLUIDB200_EINVAL, "box must be at least 3x3 (got %dx%d)", X, Y);
+    fluidb200_solver* s = new (std::nothrow) fluidb200_solver();
+    if (!s) return fail(FLUIDB200_ENOMEM, "host allocation failed");
+    s->dtype = dtype; s->X = X; s->Y = Y;
+    s->esize = dtype == FLUIDB200_F32 ? 4 : 8;
+    s->pitch = ((int64_t)Y + 31) / 32 * 32;
+    s->kmax = env_int("FLUIDB200_KMAX", 4);
+    fluidb200_set_domain(s, domain_x, domain_y);
+    if (fbk::be_stream_create(&s->stream) != 0) {
+        delete s;
+        return fail_backend("stream create");
+    }
+    s->own_stream = true;
+    for (int i = 0; i < FLUIDB200_NUM_FIELDS; ++i) {
+        if (fbk::be_malloc(&s->f[i], field_bytes(s)) != 0 ||
+            fbk::be_memset_async(s->f[i], 0, field_bytes(s), s->stream) != 0) {
+            int rc = fail(FLUIDB200_ENOMEM, "device allocation of %zu bytes failed: %s", field_bytes(s),
+                          fbk::be_last_error_string());
+            fluidb200_destroy(s);
+            return rc;
+        }
+    }
+    *out = s;
+    return 0;
+}
+
+extern "C" int fluidb200_destroy(fluidb200_solver* s) {
+    if (!s) return 0;
+    if (s->stream) fbk::be_stream_sync(s->stream);
+    drop_graphs(s);
+    for (int f = 0; f < 3; ++f) free_bc(s, f);
+    for (int i = 0; i < FLUIDB200_NUM_FIELDS; ++i)
+        if (s->f[i]) fbk::be_free(s->f[i]);
+    if (s->own_stream && s->stream) fbk::be_stream_destroy(s->stream);
+    delete s;
+    return 0;
+}
+
+extern "C" int fluidb200_set_params(fluidb200_solver* s, double time_step, double kinematic_viscosity,
+                                    double density, int num_poisson_iterations, int num_iterations) {
+    if (!s) return fail(FLUIDB200_EINVAL, "solver is NULL");
+    if (num_poisson_iterations < 0 || num_iterations < 0)
+        return fail(FLUIDB200_EINVAL, "iteration counts must be >= 0");
+    s->dt = time_step; s->nu = kinematic_viscosity; s->rho = density;
+    s->K = num_poisson_iterations; s->S = num_iterations;
+    return 0;
+}
+
+extern "C" double fluidb200_element_length(int dtype, double domain, int n) {
+    if (dtype == FLUIDB200_F32) return (double)((float)domain / (float)(n - 1));
+    return domain / (double)(n - 1);
+}
+
+extern "C" int fluidb200_set_domain(fluidb200_solver* s, double domain_x, double domain_y) {
+    if (!s) return fail(FLUIDB200_EINVAL, "solver is NULL");
+    s->wx = domain_x; s->wy = domain_y;
+    s->hx = fluidb200_element_length(s->dtype, domain_x, s->X);
+    s->hy = fluidb200_element_length(s->dtype, domain_y, s->Y);
+    return 0;
+}
+
+extern "C" int fluidb200_upload(fluidb200_solver* s, const void* const fields[FLUIDB200_NUM_FIELDS],
+                                const void* const bc_val[3], const uint8_t* const bc_set[3]) {
+    if (!s) return fail(FLUIDB200_EINVAL, "solver is NULL");
+    const size_t row = (size_t)s->Y * s->esize;
+    if (fields) {
+        for (int i = 0; i < FLUIDB200_NUM_FIELDS; ++i) {
+            if (!fields[i]) continue;
+            BE_CHECK(fbk::be_memcpy2d_async(s->f[i], (size_t)s->pitch * s->esize, fields[i], row, row, s->X, fbk::H2D,
+                                            s->stream), "field upload");
+            if (i == FLUIDB200_FIELD_P || i == FLUIDB200_FIELD_P_NEXT) s->p_next_is_p = false;
+        }
+    }
+    for (int f = 0; f < 3; ++f) {
+        const void* v = bc_val ? bc_val[f] : nullptr;
+        const uint8_t* b = bc_set ? bc_set[f] : nullptr;
+        if (!v && !b) continue;
+        if (!v || !b) return fail(FLUIDB200_EINVAL, "bc_val[%d] and bc_set[%d] must both be given", f, f);
+        int rc = s->dtype == FLUIDB200_F32 ? upload_bc_t<float>(s, f, (const float*)v, b)
+                                           : upload_bc_t<double>(s, f, (const double*)v, b);
+        if (rc) return rc;
+    }
+    BE_CHECK(fbk::be_stream_sync(s->stream), "upload");  // caller may free its host buffers on return
+    return 0;
+}
+
+extern "C" int fluidb200_upload_cavity(fluidb200_solver* s, double lid_velocity) {
+    if (!s) return fail(FLUIDB200_EINVAL, "solver is NULL");
+    fluidb200_slab g;
+    fill_slab(s, &g);
+    for (int f = 0; f < 3; ++f) free_bc(s, f);
+    drop_graphs(s);
+    fluidb200_cavity_edges('u', lid_velocity, &s->edges[0]);
+    fluidb200_cavity_edges('v', lid_velocity, &s->edges[1]);
+    fluidb200_cavity_edges('p', lid_velocity, &s->edges[2]);
+    s->p_next_is_p = false;
+    int rc = fluidb200_init_cavity(&g, s->f[0], s->f[1], s->f[2], s->f[3], s->f[4], s->f[5], s->f[6], lid_velocity,
+                                   s->stream);
+    if (rc == 0) s->launches++;
+    return rc;
+}
+
+extern "C" int fluidb200_step_predictor(fluidb200_solver* s) {
+    if (!s) return fail(FLUIDB200_EINVAL, "solver is NULL");
+    return step_predictor(s);
+}
+extern "C" int fluidb200_step_poisson(fluidb200_solver* s, int sweeps) {
+    if (!s) return fail(FLUIDB200_EINVAL, "solver is NULL");
+    if (sweeps < 0) return fail(FLUIDB200_EINVAL, "sweeps must be >= 0");
+    return step_poisson(s, sweeps);
+}
+extern "C" int fluidb200_step_corrector(fluidb200_solver* s) {
+    if (!s) return fail(FLUIDB200_EINVAL, "solver is NULL");
+    return step_corrector(s);
+}
+
+extern "C" int fluidb200_solve(fluidb200_solver* s) {
+    if (!s) return fail(FLUIDB200_EINVAL, "solver is NULL");
+    if (s->S == 0) return 0;
+    if (!s->use_graph) {
+        for (int i = 0; i < s->S; ++i) {
+            int rc = one_step(s);
+            if (rc) return rc;
+        }
+        return 0;
+    }
+    // CUDA-graph replay: one captured timestep per ping-pong parity of p (a step with an odd
+    // number of sweep launches leaves p in the other buffer). The graphs bake the scalar
+    // parameters in, so they are rebuilt when any of them changes.
+    const double key[6] = {s->dt, s->nu, s->rho, (double)s->K + 4096.0 * s->kmax, s->hx, s->hy};
+    if (memcmp(key, s->graph_key, sizeof(key)) != 0) {
+        drop_graphs(s);
+        memcpy(s->graph_key, key, sizeof(key));
+    }
+    const bool odd = (launches_per_step(s) - 2) % 2 != 0;
+    for (int i = 0; i < s->S; ++i) {
+        const int parity = (s->graph[0] && s->f[FLUIDB200_FIELD_P] != s->graph_home_p) ? 1 : 0;
+        if (!s->graph[parity]) {
+            if (parity == 0) s->graph_home_p = s->f[FLUIDB200_FIELD_P];
+            const int64_t before = s->launches;
+            if (fbk::be_graph_begin(s->stream) != 0) {
+                s->use_graph = false;  // backend cannot capture: plain launches from here on
+                for (; i < s->S; ++i) {
+                    int rc = one_step(s);
+                    if (rc) return rc;
+                }
+                return 0;
+            }
+            const int rc = one_step(s);  // recorded, not executed
+            void* exec = nullptr;
+            const int rc2 = fbk::be_graph_end(s->stream, &exec);
+            s->launches = before;
+            if (odd) std::swap(s->f[FLUIDB200_FIELD_P], s->f[FLUIDB200_FIELD_P_NEXT]);  // undo recorded swaps
+            if (rc) return rc;
+            if (rc2 != 0) return fail_backend("graph capture");
+            s->graph[parity] = exec;
+        }
+        BE_CHECK(fbk::be_graph_launch(s->graph[parity], s->stream), "graph launch");
+        s->launches += launches_per_step(s);
+        if (s->K > 0) s->p_next_is_p = true;
+        if (odd) std::swap(s->f[FLUIDB200_FIELD_P], s->f[FLUIDB200_FIELD_P_NEXT]);
+    }
+    return 0;
+}
+
+extern "C" int fluidb200_synchronize(fluidb200_solver* s) {
+    if (!s) return fail(FLUIDB200_EINVAL, "solver is NULL");
+    BE_CHECK(fbk::be_stream_sync(s->stream), "synchronize");
+    return 0;
+}
+
+extern "C" int fluidb200_download(fluidb200_solver* s, int field, void* out) {
+    if (!s) return fail(FLUIDB200_EINVAL, "solver is NULL");
+    if (field < 0 || field >= FLUIDB200_NUM_FIELDS) return fail(FLUIDB200_EINVAL, "bad field %d", field);
+    if (!out) return fail(FLUIDB200_EINVAL, "out is NULL");
+    // updatePressure leaves p_next == p after every sweep (SerialNavierStokes.cpp:192-198); with
+    // ping-pong buffers the "other" buffer is one launch stale, so p_next reads p.
+    int src = field;
+    if (field == FLUIDB200_FIELD_P_NEXT && s->p_next_is_p) src = FLUIDB200_FIELD_P;
+    const size_t row = (size_t)s->Y * s->esize;
+    BE_CHECK(fbk::be_memcpy2d_async(out, row, s->f[src], (size_t)s->pitch * s->esize, row, s->X, fbk::D2H, s->stream),
+             "download");
+    BE_CHECK(fbk::be_stream_sync(s->stream), "download");
+    return 0;
+}
+
+extern "C" int fluidb200_get_slab(const fluidb200_solver* s, fluidb200_slab* out) {
+    if (!s || !out) return fail(FLUIDB200_EINVAL, "NULL argument");
+    fill_slab(s, out);
+    return 0;
+}
+extern "C" void* fluidb200_field_ptr(fluidb200_solver* s, int field) {
+    if (!s || field < 0 || field >= FLUIDB200_NUM_FIELDS) return nullptr;
+    return s->f[field];
+}
+extern "C" int fluidb200_set_stream(fluidb200_solver* s, void* stream) {
+    if (!s) return fail(FLUIDB200_EINVAL, "solver is NULL");
+    fbk::be_stream_sync(s->stream);
+    drop_graphs(s);
+    if (s->own_stream && s->stream) fbk::be_stream_destroy(s->stream);
+    s->stream = stream;
+    s->own_stream = false;
+    return 0;
+}
+extern "C" int fluidb200_set_sweeps_per_launch(fluidb200_solver* s, int k) {
+    if (!s) return fail(FLUIDB200_EINVAL, "solver is NULL");
+    if (k < 1 || k > FLUIDB200_MAX_SWEEPS_PER_LAUNCH)
+        return fail(FLUIDB200_EINVAL, "sweeps per launch must be in [1,%d]", FLUIDB200_MAX_SWEEPS_PER_LAUNCH);
+    s->kmax = k;
+    drop_graphs(s);
+    return 0;
+}
+extern "C" int fluidb200_set_use_graph(fluidb200_solver* s, int enable) {
+    if (!s) return fail(FLUIDB200_EINVAL, "solver is NULL");
+    s->use_graph = enable != 0;
+    if (!enable) drop_graphs(s);
+    return 0;
+}
+extern "C" int64_t fluidb200_launch_count(const fluidb200_solver* s) { return s ? s->launches : 0; }
+
+extern "C" int fluidb200_set_device(int device) {
+    BE_CHECK(fbk::be_set_device(device), "set_device");
+    return 0;
+}
+extern "C" const char* fluidb200_last_error(void) { return g_err; }
+extern "C" const char* fluidb200_version(void) { return "fluidb200 0.1 (sm_100a)"; }

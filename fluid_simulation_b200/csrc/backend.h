@@ -1,0 +1,41 @@
+// backend.h -- the narrow seam between the host logic (api.cpp: validation, planning, the
+// solver handle) and the device. The product implements it with CUDA (kernels.cu). The
+// CPU-only test build in tests/emu implements it with host threads so the same host logic and
+// the same warp task bodies can be exercised without a GPU; that build is never shipped.
+#pragma once
+#include <stddef.h>
+#include <stdint.h>
+
+#include "warp_args.h"
+
+namespace fbk {
+
+enum CopyKind { H2D = 0, D2H = 1, D2D = 2 };
+
+const char* backend_name();
+int be_set_device(int device);
+int be_malloc(void** p, size_t bytes);
+int be_free(void* p);
+int be_memset_async(void* p, int value, size_t bytes, void* stream);
+int be_memcpy_async(void* dst, const void* src, size_t bytes, CopyKind kind, void* stream);
+int be_memcpy2d_async(void* dst, size_t dpitch, const void* src, size_t spitch, size_t width_bytes,
+                      size_t height, CopyKind kind, void* stream);
+int be_stream_create(void** stream);
+int be_stream_destroy(void* stream);
+int be_stream_sync(void* stream);
+const char* be_last_error_string();
+
+// CUDA-graph capture of a launch sequence (returns non-zero when unsupported).
+int be_graph_begin(void* stream);
+int be_graph_end(void* stream, void** graph_exec);
+int be_graph_launch(void* graph_exec, void* stream);
+int be_graph_destroy(void* graph_exec);
+
+// Kernel launches. `nchunks` x ceil(nstrips / warps-per-CTA) CTAs; all asynchronous.
+template <typename T> int launch_jacobi(const fb::JacobiArgs<T>& a, int sweeps, bool mask, int nchunks, void* stream);
+template <typename T> int launch_predictor(const fb::PredictorArgs<T>& a, int nchunks, void* stream);
+template <typename T> int launch_corrector(const fb::CorrectorArgs<T>& a, bool mask, int nchunks, void* stream);
+template <typename T>
+int launch_init_cavity(T* const fields[7], long long pitch, int X, int Y, int row0, int rows, T lid, void* stream);
+
+}  // namespace fbk

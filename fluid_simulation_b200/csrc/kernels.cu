@@ -1,0 +1,176 @@
+// kernels.cu -- CUDA (sm_100a) implementation of backend.h: __global__ wrappers around the warp
+// tasks of warp_kernels.cuh, their launch dispatch, and the device-memory plumbing.
+//
+// Build: nvcc -gencode arch=compute_100a,code=sm_100a -O3 -lineinfo -fmad=false
+//        (no -use_fast_math: IEEE division, no flush-to-zero; -fmad=false as a second guard
+//        next to the *_rn intrinsics, see the arithmetic contract in warp_kernels.cuh)
+#include <cuda_runtime.h>
+#include <stdio.h>
+
+#include "backend.h"
+#include "warp_kernels.cuh"
+
+namespace {
+
+thread_local cudaError_t g_last = cudaSuccess;
+inline int rc_of(cudaError_t e) {
+    if (e != cudaSuccess) {
+        g_last = e;
+        return -1;
+    }
+    return 0;
+}
+
+constexpr int kThreads = fb::kWarpsPerCta * 32;
+
+template <typename T, int V, int K, bool MASK>
+__global__ void __launch_bounds__(kThreads) jacobi_kernel(const __grid_constant__ fb::JacobiArgs<T> A) {
+    const int strip = blockIdx.x * fb::kWarpsPerCta + (threadIdx.x >> 5);
+    if (strip >= A.g.nstrips) return;  // whole warps only; the tasks use no block barrier
+    fb::jacobi_task<T, V, K, MASK>(A, strip, blockIdx.y, threadIdx.x & 31);
+}
+
+template <typename T, int V>
+__global__ void __launch_bounds__(kThreads) predictor_kernel(const __grid_constant__ fb::PredictorArgs<T> A) {
+    const int strip = blockIdx.x * fb::kWarpsPerCta + (threadIdx.x >> 5);
+    if (strip >= A.g.nstrips) return;
+    fb::predictor_task<T, V>(A, strip, blockIdx.y, threadIdx.x & 31);
+}
+
+template <typename T, int V, bool MASK>
+__global__ void __launch_bounds__(kThreads) corrector_kernel(const __grid_constant__ fb::CorrectorArgs<T> A) {
+    const int strip = blockIdx.x * fb::kWarpsPerCta + (threadIdx.x >> 5);
+    if (strip >= A.g.nstrips) return;
+    fb::corrector_task<T, V, MASK>(A, strip, blockIdx.y, threadIdx.x & 31);
+}
+
+template <typename T> struct FieldPtrs {
+    T* f[7];
+};
+
+// zero state + cavity boundary values (fluid_cpp/main.cpp:43-55): only u on the lid is non-zero
+template <typename T>
+__global__ void init_cavity_kernel(FieldPtrs<T> F, long long pitch, int Y, long long n, T lid) {
+    const long long stride = (long long)gridDim.x * blockDim.x;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+        const int col = (int)(i % pitch);
+#pragma unroll
+        for (int k = 0; k < 7; ++k)
+            if (F.f[k]) F.f[k][i] = (k == 0 && col == Y - 1) ? lid : T(0);
+    }
+}
+
+inline dim3 grid_for(int nstrips, int nchunks) {
+    return dim3((unsigned)((nstrips + fb::kWarpsPerCta - 1) / fb::kWarpsPerCta), (unsigned)nchunks, 1);
+}
+
+template <typename T, int K> int launch_jacobi_k(const fb::JacobiArgs<T>& a, bool mask, int nchunks, cudaStream_t st) {
+    constexpr int V = fb::VecWidth<T>::V;
+    const dim3 grid = grid_for(a.g.nstrips, nchunks);
+    if (K == 1 && mask) jacobi_kernel<T, V, 1, true><<<grid, kThreads, 0, st>>>(a);
+    else jacobi_kernel<T, V, K, false><<<grid, kThreads, 0, st>>>(a);
+    return rc_of(cudaGetLastError());
+}
+
+}  // namespace
+
+namespace fbk {
+
+const char* backend_name() { return "cuda-sm_100a"; }
+const char* be_last_error_string() { return cudaGetErrorString(g_last); }
+int be_set_device(int device) { return rc_of(cudaSetDevice(device)); }
+
+int be_malloc(void** p, size_t bytes) { return rc_of(cudaMalloc(p, bytes)); }
+int be_free(void* p) { return rc_of(cudaFree(p)); }
+int be_memset_async(void* p, int value, size_t bytes, void* stream) {
+    return rc_of(cudaMemsetAsync(p, value, bytes, (cudaStream_t)stream));
+}
+static cudaMemcpyKind kind_of(CopyKind k) {
+    return k == H2D ? cudaMemcpyHostToDevice : (k == D2H ? cudaMemcpyDeviceToHost : cudaMemcpyDeviceToDevice);
+}
+int be_memcpy_async(void* dst, const void* src, size_t bytes, CopyKind kind, void* stream) {
+    return rc_of(cudaMemcpyAsync(dst, src, bytes, kind_of(kind), (cudaStream_t)stream));
+}
+int be_memcpy2d_async(void* dst, size_t dpitch, const void* src, size_t spitch, size_t width_bytes, size_t height,
+                      CopyKind kind, void* stream) {
+    return rc_of(cudaMemcpy2DAsync(dst, dpitch, src, spitch, width_bytes, height, kind_of(kind), (cudaStream_t)stream));
+}
+int be_stream_create(void** stream) {
+    cudaStream_t s;
+    const int rc = rc_of(cudaStreamCreateWithFlags(&s, cudaStreamNonBlocking));
+    *stream = rc ? nullptr : (void*)s;
+    return rc;
+}
+int be_stream_destroy(void* stream) { return rc_of(cudaStreamDestroy((cudaStream_t)stream)); }
+int be_stream_sync(void* stream) { return rc_of(cudaStreamSynchronize((cudaStream_t)stream)); }
+
+int be_graph_begin(void* stream) {
+    return rc_of(cudaStreamBeginCapture((cudaStream_t)stream, cudaStreamCaptureModeThreadLocal));
+}
+int be_graph_end(void* stream, void** graph_exec) {
+    cudaGraph_t g = nullptr;
+    *graph_exec = nullptr;
+    if (rc_of(cudaStreamEndCapture((cudaStream_t)stream, &g))) return -1;
+    cudaGraphExec_t ex = nullptr;
+    const int rc = rc_of(cudaGraphInstantiate(&ex, g, 0));
+    cudaGraphDestroy(g);
+    if (rc) return rc;
+    *graph_exec = (void*)ex;
+    return 0;
+}
+int be_graph_launch(void* graph_exec, void* stream) {
+    return rc_of(cudaGraphLaunch((cudaGraphExec_t)graph_exec, (cudaStream_t)stream));
+}
+int be_graph_destroy(void* graph_exec) { return rc_of(cudaGraphExecDestroy((cudaGraphExec_t)graph_exec)); }
+
+template <typename T>
+int launch_jacobi(const fb::JacobiArgs<T>& a, int sweeps, bool mask, int nchunks, void* stream) {
+    cudaStream_t st = (cudaStream_t)stream;
+    switch (sweeps) {
+        case 1: return launch_jacobi_k<T, 1>(a, mask, nchunks, st);
+        case 2: return launch_jacobi_k<T, 2>(a, mask, nchunks, st);
+        case 3: return launch_jacobi_k<T, 3>(a, mask, nchunks, st);
+        case 4: return launch_jacobi_k<T, 4>(a, mask, nchunks, st);
+        case 5: return launch_jacobi_k<T, 5>(a, mask, nchunks, st);
+        case 6: return launch_jacobi_k<T, 6>(a, mask, nchunks, st);
+        case 7: return launch_jacobi_k<T, 7>(a, mask, nchunks, st);
+        case 8: return launch_jacobi_k<T, 8>(a, mask, nchunks, st);
+        default: g_last = cudaErrorInvalidValue; return -1;
+    }
+}
+
+template <typename T> int launch_predictor(const fb::PredictorArgs<T>& a, int nchunks, void* stream) {
+    constexpr int V = fb::VecWidth<T>::V;
+    predictor_kernel<T, V><<<grid_for(a.g.nstrips, nchunks), kThreads, 0, (cudaStream_t)stream>>>(a);
+    return rc_of(cudaGetLastError());
+}
+
+template <typename T> int launch_corrector(const fb::CorrectorArgs<T>& a, bool mask, int nchunks, void* stream) {
+    constexpr int V = fb::VecWidth<T>::V;
+    const dim3 grid = grid_for(a.g.nstrips, nchunks);
+    if (mask) corrector_kernel<T, V, true><<<grid, kThreads, 0, (cudaStream_t)stream>>>(a);
+    else corrector_kernel<T, V, false><<<grid, kThreads, 0, (cudaStream_t)stream>>>(a);
+    return rc_of(cudaGetLastError());
+}
+
+template <typename T>
+int launch_init_cavity(T* const fields[7], long long pitch, int X, int Y, int row0, int rows, T lid, void* stream) {
+    (void)X; (void)row0;
+    FieldPtrs<T> F;
+    for (int k = 0; k < 7; ++k) F.f[k] = fields[k];
+    const long long n = (long long)rows * pitch;
+    long long blocks = (n + 255) / 256;
+    if (blocks > 148LL * 16) blocks = 148LL * 16;
+    init_cavity_kernel<T><<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(F, pitch, Y, n, lid);
+    return rc_of(cudaGetLastError());
+}
+
+#define INSTANTIATE(T)                                                                                   \
+    template int launch_jacobi<T>(const fb::JacobiArgs<T>&, int, bool, int, void*);                     \
+    template int launch_predictor<T>(const fb::PredictorArgs<T>&, int, void*);                          \
+    template int launch_corrector<T>(const fb::CorrectorArgs<T>&, bool, int, void*);                    \
+    template int launch_init_cavity<T>(T* const[7], long long, int, int, int, int, T, void*);
+INSTANTIATE(float)
+INSTANTIATE(double)
+
+}  // namespace fbk

@@ -1,0 +1,72 @@
+// warp_args.h -- plain argument structs of the three kernels (no CUDA types), shared by the
+// device code (warp_kernels.cuh), the host planner (api.cpp) and the backend seam (backend.h).
+#pragma once
+#include <stdint.h>
+
+namespace fb {
+
+constexpr int kWarpsPerCta = 4;
+
+// ---------------------------------------------------------------------------------------
+// boundary description on the device (see fluidb200_edges in include/fluidb200.h)
+// ---------------------------------------------------------------------------------------
+enum { EDGE_UNSET = 0, EDGE_CONST = 1, EDGE_ARRAY = 2 };
+enum { BOTTOM = 0, TOP = 1, LEFT = 2, RIGHT = 3 };
+
+template <typename T> struct Edges {
+    int mode[4];
+    T cval[4];
+    const T* val[4];
+    const uint8_t* set[4];
+};
+
+// Geometry shared by the kernels. All row indices are GLOBAL x; the arrays hold rows
+// [row0, row0+rows).
+struct Geom {
+    long long pitch;
+    int X, Y;
+    int row0, rows;
+    int nstrips;         // strips along y
+    int rows_per_chunk;  // x rows written by one warp task
+};
+
+// Jacobi sweeps (see jacobi_task in warp_kernels.cuh)
+template <typename T> struct JacobiArgs {
+    const T* p_in;
+    T* p_out;
+    const T* rhs;
+    const uint8_t* mset;  // interior pressure flags (MASK build only)
+    const T* mval;
+    Geom g;
+    T hx, hy;
+    int out_lo, out_hi;   // global rows to write
+    Edges<T> e;
+};
+
+// Fused tentative velocity + right-hand side (see predictor_task)
+template <typename T> struct PredictorArgs {
+    const T *u, *v;
+    T *us, *vs, *rhs;     // u_next, v_next, right_hand_size
+    Geom g;
+    T hx, hy, hx2, hy2;   // element lengths and their exact doubles
+    T nu, dt, rho_over_dt;
+    int lo, hi;           // chunked global row range = union of the two below
+    int star_lo, star_hi; // rows of u_next/v_next to write
+    int rhs_lo, rhs_hi;   // rows of rhs to write
+};
+
+// Fused correction + velocity boundary rows (see corrector_task)
+template <typename T> struct CorrectorArgs {
+    const T* p;
+    const T *us, *vs;   // u_next, v_next
+    T *u, *v;
+    const uint8_t *uset, *vset;  // interior flags (MASK build only)
+    const T *uval, *vval;
+    Geom g;
+    T hx, hy, hx2, hy2;
+    T dt_over_rho;
+    int out_lo, out_hi;
+    Edges<T> eu, ev;
+};
+
+}  // namespace fb

@@ -1,0 +1,641 @@
+// warp_kernels.cuh -- the three hot-path kernels of the cavity projection timestep, written as
+// warp-synchronous *streaming* stencils for sm_100a.
+//
+// Common shape (all three kernels):
+//   * fields are SoA, row x = `pitch` contiguous elements along y (the reference's device
+//     order, fluid_cpp/cuda/ParallelNavierStokes.cu:22, minus the 92-byte AoS cell);
+//   * one WARP owns a strip of 32*V contiguous y-columns (V elements = 16 bytes per lane,
+//     so every global access is a coalesced 128-bit load/store) and marches along x;
+//   * x-neighbours live in the lane's own registers (a sliding window of rows),
+//     y-neighbours of the lane's outer elements come from the adjacent lane by one
+//     warp shuffle -- no shared memory, no block barrier, no atomics;
+//   * strips overlap by a 2*H column halo and x-chunks by the stencil radius, the overlap is
+//     recomputed (a few percent) so that warps never communicate.
+//
+// The Jacobi kernel additionally blocks K sweeps in TIME: level t of the pipeline lags level
+// t-1 by one row, all K levels of a row strip stay in registers, and HBM sees one read of p,
+// one read of rhs and one write of p per K sweeps. Jacobi (p -> p_next, then copy; reference
+// SerialNavierStokes.cpp:140-198) has no intra-sweep dependence, so this is bit-identical to
+// K separate sweeps. The boundary rows of every intermediate sweep are applied inside the
+// pipeline (see jacobi_task).
+//
+// Arithmetic contract: operand order and rounding points of the
+// reference's serial fp32 path are reproduced exactly with *_rn intrinsics (never contracted
+// into FMAs), IEEE division and no flush-to-zero; the fp64 Laplacian tail of the fp32 path is
+// kept in fp64.
+//
+// This header is also compiled for the HOST by tests/emu (FLUIDB200_HOST_EMU) where a warp
+// is 32 threads and a shuffle is a barrier exchange; that build is test infrastructure only.
+#pragma once
+#include <stdint.h>
+
+#include "warp_args.h"
+
+#ifdef FLUIDB200_HOST_EMU
+#include "emu_shim.h"
+#else
+#include <cuda_runtime.h>
+#define FB_DEV __device__ __forceinline__
+#define FB_DEV_NOINLINE __device__ __noinline__
+#endif
+
+namespace fb {
+
+// ---------------------------------------------------------------------------------------
+// exact-rounding arithmetic
+// ---------------------------------------------------------------------------------------
+template <typename T> struct Ar;
+
+template <> struct Ar<float> {
+    static FB_DEV float add(float a, float b) { return __fadd_rn(a, b); }
+    static FB_DEV float sub(float a, float b) { return __fsub_rn(a, b); }
+    static FB_DEV float mul(float a, float b) { return __fmul_rn(a, b); }
+    // (a - b) / 2. / h of the reference: float subtract, exact halving in double, one double
+    // division, one rounding to float. 53 >= 2*24+2, so the double rounding is innocuous and
+    // the result equals the correctly rounded float quotient (a-b)/(2h); h2 = 2h is exact.
+    static FB_DEV float cdiff(float a, float b, float h, float h2) {
+        (void)h;
+        return __fdiv_rn(__fsub_rn(a, b), h2);
+    }
+    // (s - 4.*c) / hx / hy with s already rounded to float: the one place the fp32 path is
+    // observably mixed precision (SerialNavierStokes.cpp:308-311). 4.*c is exact in double, so
+    // s - 4.*c is a single rounding == fma(-4, c, s).
+    static FB_DEV float lap_tail(float s, float c, float hx, float hy) {
+        double d = __fma_rn(-4.0, (double)c, (double)s);
+        d = __ddiv_rn(d, (double)hx);
+        d = __ddiv_rn(d, (double)hy);
+        return __double2float_rn(d);
+    }
+    // t *= -0.25 : the double multiply is exact, so this is one float rounding (subnormals).
+    static FB_DEV float neg_quarter(float t) { return __fmul_rn(t, -0.25f); }
+};
+
+template <> struct Ar<double> {
+    static FB_DEV double add(double a, double b) { return __dadd_rn(a, b); }
+    static FB_DEV double sub(double a, double b) { return __dsub_rn(a, b); }
+    static FB_DEV double mul(double a, double b) { return __dmul_rn(a, b); }
+    static FB_DEV double cdiff(double a, double b, double h, double h2) {
+        (void)h2;
+        return __ddiv_rn(__dmul_rn(__dsub_rn(a, b), 0.5), h);  // "/ 2." is an exact halving
+    }
+    static FB_DEV double lap_tail(double s, double c, double hx, double hy) {
+        double d = __fma_rn(-4.0, c, s);  // 4.*c exact -> single rounding
+        d = __ddiv_rn(d, hx);
+        return __ddiv_rn(d, hy);
+    }
+    static FB_DEV double neg_quarter(double t) { return __dmul_rn(t, -0.25); }
+};
+
+// ---------------------------------------------------------------------------------------
+// 16-byte lane vectors
+// ---------------------------------------------------------------------------------------
+template <typename T, int V> struct alignas(sizeof(T) * V) Vec {
+    T a[V];
+};
+template <typename T> struct VecWidth;
+template <> struct VecWidth<float> { static constexpr int V = 4; };
+template <> struct VecWidth<double> { static constexpr int V = 2; };
+
+template <typename T, int V> FB_DEV Vec<T, V> vzero() {
+    Vec<T, V> r;
+#pragma unroll
+    for (int e = 0; e < V; ++e) r.a[e] = T(0);
+    return r;
+}
+// read-only streaming load (inputs never alias outputs in the kernels that use it)
+template <typename T, int V> FB_DEV Vec<T, V> ld_ro(const T* p) {
+#ifdef FLUIDB200_HOST_EMU
+    return *reinterpret_cast<const Vec<T, V>*>(p);
+#else
+    const int4 r = __ldg(reinterpret_cast<const int4*>(p));
+    Vec<T, V> v;
+    *reinterpret_cast<int4*>(&v) = r;
+    return v;
+#endif
+}
+template <typename T, int V> FB_DEV Vec<T, V> ld_rw(const T* p) {
+    return *reinterpret_cast<const Vec<T, V>*>(p);
+}
+template <typename T, int V> FB_DEV void st_vec(T* p, const Vec<T, V>& v) {
+    *reinterpret_cast<Vec<T, V>*>(p) = v;
+}
+
+
+// value of an edge cell: its boundary value when the flag is set, else `copy`
+template <typename T> FB_DEV T edge_value(const Edges<T>& e, int edge, int idx, T copy) {
+    const int m = e.mode[edge];
+    if (m == EDGE_UNSET) return copy;
+    if (m == EDGE_CONST) return e.cval[edge];
+    return e.set[edge][idx] ? e.val[edge][idx] : copy;
+}
+
+
+// Per-lane view of a strip.
+template <int V, int H> struct Strip {
+    static constexpr int W = 32 * V;      // columns loaded by the warp
+    static constexpr int S = W - 2 * H;   // columns owned (stride between strips)
+    int lane, col0;                       // first column of this lane
+    bool has_bottom, has_top, ld_ok, st_ok;
+    int top_lane, top_e;                  // where column Y-1 lives (valid when has_top)
+    int ym2_lane, ym2_e;                  // where column Y-2 lives
+    FB_DEV void init(const Geom& g, int strip, int lane_) {
+        lane = lane_;
+        const int ys = strip * S;
+        col0 = ys + lane * V;
+        has_bottom = (strip == 0);
+        has_top = (ys <= g.Y - 1) && (g.Y - 1 < ys + W);
+        top_lane = (g.Y - 1 - ys) / V;
+        top_e = (g.Y - 1 - ys) % V;
+        ym2_lane = (g.Y - 2 - ys) / V;
+        ym2_e = (g.Y - 2 - ys) % V;
+        ld_ok = (long long)col0 + V <= g.pitch;
+        const int vlo = has_bottom ? 0 : ys + H;
+        const int vhi = (strip == g.nstrips - 1) ? g.Y : ys + W - H;
+        st_ok = ld_ok && col0 >= vlo && col0 < vhi;
+    }
+};
+
+template <typename T> FB_DEV T shfl_up1(T x) { return __shfl_up_sync(0xffffffffu, x, 1); }
+template <typename T> FB_DEV T shfl_down1(T x) { return __shfl_down_sync(0xffffffffu, x, 1); }
+template <typename T> FB_DEV T shfl_idx(T x, int src) { return __shfl_sync(0xffffffffu, x, src); }
+
+// y-neighbours of every element of a lane vector: ym[e] = value at column-1, yp[e] = column+1
+template <typename T, int V>
+FB_DEV void y_neighbours(const Vec<T, V>& c, Vec<T, V>& ym, Vec<T, V>& yp) {
+    const T from_prev = shfl_up1(c.a[V - 1]);
+    const T from_next = shfl_down1(c.a[0]);
+#pragma unroll
+    for (int e = 0; e < V; ++e) {
+        ym.a[e] = (e > 0) ? c.a[e - 1] : from_prev;
+        yp.a[e] = (e < V - 1) ? c.a[e + 1] : from_next;
+    }
+}
+
+// The value held at global column `lane_/e_` of a row spread over the warp (warp-uniform call).
+template <typename T, int V> FB_DEV T pick(const Vec<T, V>& row, int lane_, int e_) {
+    T r = T(0);
+#pragma unroll
+    for (int e = 0; e < V; ++e) {
+        const T s = shfl_idx(row.a[e], lane_ & 31);
+        if (e == e_) r = s;
+    }
+    return r;
+}
+
+// store only interior columns [1, Y-2] of a row (edge cells of u_next/v_next/rhs are never
+// written by the reference, SerialNavierStokes.cpp:299-300,326-327)
+template <typename T, int V>
+FB_DEV void st_interior(T* rowp, int col0, int Y, const Vec<T, V>& v) {
+    if (col0 >= 1 && col0 + V - 1 <= Y - 2) {
+        st_vec<T, V>(rowp + col0, v);
+    } else {
+#pragma unroll
+        for (int e = 0; e < V; ++e)
+            if (col0 + e >= 1 && col0 + e <= Y - 2) rowp[col0 + e] = v.a[e];
+    }
+}
+
+// =========================================================================================
+// Jacobi pressure-Poisson sweeps, K sweeps per launch, boundary rows fused in.
+// Replaces poisson_step_kernel + enforce_pressure_BC_kernel + update_pressure_kernel
+// (fluid_cpp/cuda/ParallelNavierStokes.cu:172-192, :14-42, :44-56).
+// =========================================================================================
+
+// The x = 0 (LEFT) or x = X-1 (RIGHT) boundary row of one sweep level, derived from that
+// level's adjacent interior row `inner` (SerialNavierStokes.cpp:177-188). Corner elements are
+// placeholders here (corners feed no 5-point stencil); wall_row_out() fixes them for output.
+template <typename T, int V>
+FB_DEV_NOINLINE Vec<T, V> wall_row(const Edges<T>& e, int edge, const Vec<T, V>& inner, int col0,
+                                   int Y) {
+    Vec<T, V> r = inner;
+    const int m = e.mode[edge];
+    if (m == EDGE_UNSET) return r;
+#pragma unroll
+    for (int k = 0; k < V; ++k) {
+        const int col = col0 + k;
+        if (col >= 1 && col <= Y - 2) {
+            if (m == EDGE_CONST) r.a[k] = e.cval[edge];
+            else if (e.set[edge][col]) r.a[k] = e.val[edge][col];
+        }
+    }
+    return r;
+}
+
+// Final-level boundary row including the corners. `x` is 0 or X-1, `prev_wall` is the same
+// boundary row one sweep earlier: an unset corner copies its y-neighbour on the wall BEFORE
+// that neighbour is refreshed (the y-edge loop runs first, SerialNavierStokes.cpp:163-175 vs
+// :177-188), i.e. it is one sweep stale.
+template <typename T, int V, int H>
+FB_DEV_NOINLINE Vec<T, V> wall_row_out(const Edges<T>& e, int edge, int x, const Vec<T, V>& inner,
+                                       const Vec<T, V>& prev_wall, const Strip<V, H>& st, int Y) {
+    Vec<T, V> r = wall_row<T, V>(e, edge, inner, st.col0, Y);
+    if (st.has_bottom) {
+        const T stale = prev_wall.a[1];  // column 1 (V >= 2)
+        if (st.lane == 0) r.a[0] = edge_value(e, BOTTOM, x, stale);
+    }
+    if (st.has_top) {
+        const T stale = pick<T, V>(prev_wall, st.ym2_lane, st.ym2_e);
+#pragma unroll
+        for (int k = 0; k < V; ++k)
+            if (st.lane == st.top_lane && k == st.top_e) r.a[k] = edge_value(e, TOP, x, stale);
+    }
+    return r;
+}
+
+template <typename T, int V, int K, bool MASK>
+FB_DEV void jacobi_task(const JacobiArgs<T>& A, int strip, int chunk, int lane) {
+    constexpr int H = (K + 3) & ~3;
+    using A_ = Ar<T>;
+    using VT = Vec<T, V>;
+    const Geom& g = A.g;
+    const int X = g.X, Y = g.Y;
+    Strip<V, H> st;
+    st.init(g, strip, lane);
+
+    const int c0 = A.out_lo + chunk * g.rows_per_chunk;
+    const int c1 = min(c0 + g.rows_per_chunk, A.out_hi);
+    if (c0 >= c1) return;
+    const int slab_hi = g.row0 + g.rows;
+    const int r_begin = max(c0 - K, g.row0);
+    const int load_hi = min(c1 + K, slab_hi);
+    const int r_end = c1 - 1 + K;
+
+    const T* pin = A.p_in + (long long)st.col0 - (long long)g.row0 * g.pitch;
+    const T* rin = A.rhs + (long long)st.col0 - (long long)g.row0 * g.pitch;
+    T* pout = A.p_out + (long long)st.col0 - (long long)g.row0 * g.pitch;
+
+    VT w[K][2];   // w[t] = rows (q-1, q) of sweep level t, q = newest row of that level
+    VT bw[K];     // bw[j] = (rhs*hx)*hy of row r-1-j
+#pragma unroll
+    for (int t = 0; t < K; ++t) {
+        w[t][0] = vzero<T, V>();
+        w[t][1] = vzero<T, V>();
+        bw[t] = vzero<T, V>();
+    }
+
+    auto load_p = [&](int r) -> VT {
+        if (st.ld_ok && r >= r_begin && r < load_hi) return ld_ro<T, V>(pin + (long long)r * g.pitch);
+        return vzero<T, V>();
+    };
+    auto load_b = [&](int r) -> VT {  // rhs of row r (interior rows only)
+        if (st.ld_ok && r >= r_begin && r < load_hi && r >= 1 && r <= X - 2)
+            return ld_ro<T, V>(rin + (long long)r * g.pitch);
+        return vzero<T, V>();
+    };
+
+    VT nxt_p = load_p(r_begin);
+    VT nxt_b = load_b(r_begin - 1);
+    for (int r = r_begin; r <= r_end; ++r) {
+        VT cur = nxt_p;
+        VT bnew = nxt_b;
+        nxt_p = load_p(r + 1);
+        nxt_b = load_b(r);
+        // (rhs * hx) * hy, SerialNavierStokes.cpp:144 -- done once per row, reused by K levels
+#pragma unroll
+        for (int e = 0; e < V; ++e) bnew.a[e] = A_::mul(A_::mul(bnew.a[e], A.hx), A.hy);
+#pragma unroll
+        for (int t = K - 1; t > 0; --t) bw[t] = bw[t - 1];
+        bw[0] = bnew;
+
+#pragma unroll
+        for (int t = 1; t <= K; ++t) {
+            const int rr = r - t;  // row this level produces now
+            VT out = cur;
+            if (rr >= 1 && rr <= X - 2) {
+                VT xm = w[t - 1][0];
+                const VT c = w[t - 1][1];
+                VT xp = cur;
+                if (t > 1) {
+                    // levels >= 1 never materialise their boundary rows: rebuild them from the
+                    // adjacent interior row of the same level
+                    if (rr == 1) xm = wall_row<T, V>(A.e, LEFT, c, st.col0, Y);
+                    if (rr == X - 2) xp = wall_row<T, V>(A.e, RIGHT, c, st.col0, Y);
+                }
+                VT ym, yp;
+                y_neighbours<T, V>(c, ym, yp);
+#pragma unroll
+                for (int e = 0; e < V; ++e) {
+                    // p[x-1] + p[x+1] + p[y+1] + p[y-1], left to right (:145)
+                    const T s = A_::add(A_::add(A_::add(xm.a[e], xp.a[e]), yp.a[e]), ym.a[e]);
+                    out.a[e] = A_::neg_quarter(A_::sub(bw[t - 1].a[e], s));
+                }
+                if (MASK) {  // interior flags (:154-160)
+                    const long long off = (long long)(rr - g.row0) * g.pitch + st.col0;
+                    if (st.ld_ok) {
+#pragma unroll
+                        for (int e = 0; e < V; ++e) {
+                            const int col = st.col0 + e;
+                            if (col >= 1 && col <= Y - 2 && A.mset[off + e]) out.a[e] = A.mval[off + e];
+                        }
+                    }
+                }
+                // y-edges of this row (:163-175)
+                if (st.has_bottom) {
+                    if (lane == 0) out.a[0] = edge_value(A.e, BOTTOM, rr, out.a[1]);
+                }
+                if (st.has_top) {
+                    const T below = shfl_up1(out.a[V - 1]);
+#pragma unroll
+                    for (int e = 0; e < V; ++e)
+                        if (lane == st.top_lane && e == st.top_e)
+                            out.a[e] = edge_value(A.e, TOP, rr, (e > 0) ? out.a[e > 0 ? e - 1 : 0] : below);
+                }
+                if (t == K) {
+                    if (rr >= c0 && rr < c1 && st.st_ok) st_vec<T, V>(pout + (long long)rr * g.pitch, out);
+                    if (rr == 1 && c0 == 0) {
+                        const VT wr = wall_row_out<T, V, H>(A.e, LEFT, 0, out, xm, st, Y);
+                        if (st.st_ok) st_vec<T, V>(pout, wr);
+                    }
+                    if (rr == X - 2 && c1 == X) {
+                        const VT wr = wall_row_out<T, V, H>(A.e, RIGHT, X - 1, out, xp, st, Y);
+                        if (st.st_ok) st_vec<T, V>(pout + (long long)(X - 1) * g.pitch, wr);
+                    }
+                }
+            }
+            w[t - 1][0] = w[t - 1][1];
+            w[t - 1][1] = cur;
+            cur = out;
+        }
+    }
+}
+
+// =========================================================================================
+// Fused tentative velocity + divergence right-hand side ("predictor").
+// Replaces unified_timestep_kernel + compute_righthand_kernel
+// (fluid_cpp/cuda/ParallelNavierStokes.cu:113-148, :150-170).
+// =========================================================================================
+
+template <typename T, int V>
+FB_DEV void predictor_task(const PredictorArgs<T>& A, int strip, int chunk, int lane) {
+    constexpr int H = 4;
+    using A_ = Ar<T>;
+    using VT = Vec<T, V>;
+    const Geom& g = A.g;
+    const int X = g.X, Y = g.Y;
+    Strip<V, H> st;
+    st.init(g, strip, lane);
+
+    const int c0 = A.lo + chunk * g.rows_per_chunk;
+    const int c1 = min(c0 + g.rows_per_chunk, A.hi);
+    if (c0 >= c1) return;
+    const int slab_hi = g.row0 + g.rows;
+    // rows this task stores
+    const int s0 = max(c0, A.star_lo), s1 = min(c1, A.star_hi);
+    const int b0 = max(c0, A.rhs_lo), b1 = min(c1, A.rhs_hi);
+    const int r_begin = max(c0 - 2, g.row0);
+    const int load_hi = min(c1 + 2, slab_hi);
+    const int r_end = c1 + 1;
+
+    const long long base = (long long)st.col0 - (long long)g.row0 * g.pitch;
+    const T* up = A.u + base;
+    const T* vp = A.v + base;
+    T* usp = A.us + base;
+    T* vsp = A.vs + base;
+    T* rp = A.rhs + base;
+
+    VT wu[2] = {vzero<T, V>(), vzero<T, V>()};   // u rows r-2, r-1
+    VT wv[2] = {vzero<T, V>(), vzero<T, V>()};
+    VT wus[2] = {vzero<T, V>(), vzero<T, V>()};  // u_next rows r-3, r-2
+    VT wvs = vzero<T, V>();                      // v_next row r-2
+
+    auto load = [&](const T* f, int r) -> VT {
+        if (st.ld_ok && r >= r_begin && r < load_hi) return ld_ro<T, V>(f + (long long)r * g.pitch);
+        return vzero<T, V>();
+    };
+
+    VT nu_ = load(up, r_begin), nv_ = load(vp, r_begin);
+    for (int r = r_begin; r <= r_end; ++r) {
+        const VT cu = nu_, cv = nv_;
+        nu_ = load(up, r + 1);
+        nv_ = load(vp, r + 1);
+
+        // ---- level A: u_next, v_next of row ra = r-1 (SerialNavierStokes.cpp:298-322)
+        const int ra = r - 1;
+        VT us = vzero<T, V>(), vs = vzero<T, V>();
+        if (ra >= 1 && ra <= X - 2) {
+            const VT u0 = wu[1], v0 = wv[1];
+            VT uym, uyp, vym, vyp;
+            y_neighbours<T, V>(u0, uym, uyp);
+            y_neighbours<T, V>(v0, vym, vyp);
+#pragma unroll
+            for (int e = 0; e < V; ++e) {
+                const T uc = u0.a[e], vc = v0.a[e];
+                const T uxm = wu[0].a[e], uxp = cu.a[e], vxm = wv[0].a[e], vxp = cv.a[e];
+                const T du_dx = A_::cdiff(uxp, uxm, A.hx, A.hx2);
+                const T dv_dx = A_::cdiff(vxp, vxm, A.hx, A.hx2);
+                const T du_dy = A_::cdiff(uyp.a[e], uym.a[e], A.hy, A.hy2);
+                const T dv_dy = A_::cdiff(vyp.a[e], vym.a[e], A.hy, A.hy2);
+                const T su = A_::add(A_::add(A_::add(uxm, uxp), uyp.a[e]), uym.a[e]);
+                const T sv = A_::add(A_::add(A_::add(vxm, vxp), vyp.a[e]), vym.a[e]);
+                const T u_lap = A_::lap_tail(su, uc, A.hx, A.hy);
+                const T v_lap = A_::lap_tail(sv, vc, A.hx, A.hy);
+                const T du_dt = A_::sub(A_::sub(A_::mul(A.nu, u_lap), A_::mul(uc, du_dx)), A_::mul(vc, du_dy));
+                const T dv_dt = A_::sub(A_::sub(A_::mul(A.nu, v_lap), A_::mul(uc, dv_dx)), A_::mul(vc, dv_dy));
+                us.a[e] = A_::add(uc, A_::mul(A.dt, du_dt));
+                vs.a[e] = A_::add(vc, A_::mul(A.dt, dv_dt));
+            }
+            // edge columns of u_next/v_next keep whatever is stored (never written by the
+            // reference); the right-hand side below reads them as y-neighbours
+            if (st.has_bottom && lane == 0) {
+                us.a[0] = usp[(long long)ra * g.pitch];
+                vs.a[0] = vsp[(long long)ra * g.pitch];
+            }
+            if (st.has_top && lane == st.top_lane) {
+#pragma unroll
+                for (int e = 0; e < V; ++e)
+                    if (e == st.top_e) {
+                        us.a[e] = usp[(long long)ra * g.pitch + e];
+                        vs.a[e] = vsp[(long long)ra * g.pitch + e];
+                    }
+            }
+            if (ra >= s0 && ra < s1 && st.st_ok) {
+                st_interior<T, V>(A.us + (long long)(ra - g.row0) * g.pitch, st.col0, Y, us);
+                st_interior<T, V>(A.vs + (long long)(ra - g.row0) * g.pitch, st.col0, Y, vs);
+            }
+        } else if ((ra == 0 || ra == X - 1) && ra >= r_begin && ra < load_hi) {
+            // wall rows of u_next / v_next: stored values (x-neighbours of rows 1 and X-2)
+            if (st.ld_ok) {
+                us = ld_rw<T, V>(usp + (long long)ra * g.pitch);
+                vs = ld_rw<T, V>(vsp + (long long)ra * g.pitch);
+            }
+        }
+
+        // ---- level B: rhs of row rb = r-2 (SerialNavierStokes.cpp:325-335)
+        const int rb = r - 2;
+        if (rb >= 1 && rb <= X - 2) {
+            VT vym, vyp;
+            y_neighbours<T, V>(wvs, vym, vyp);
+            VT q;
+#pragma unroll
+            for (int e = 0; e < V; ++e) {
+                const T du_next_dx = A_::cdiff(us.a[e], wus[0].a[e], A.hx, A.hx2);
+                const T dv_next_dy = A_::cdiff(vyp.a[e], vym.a[e], A.hy, A.hy2);
+                q.a[e] = A_::mul(A.rho_over_dt, A_::add(du_next_dx, dv_next_dy));
+            }
+            if (rb >= b0 && rb < b1 && st.st_ok)
+                st_interior<T, V>(A.rhs + (long long)(rb - g.row0) * g.pitch, st.col0, Y, q);
+        }
+        (void)rp;
+        wu[0] = wu[1]; wu[1] = cu;
+        wv[0] = wv[1]; wv[1] = cv;
+        wus[0] = wus[1]; wus[1] = us;
+        wvs = vs;
+    }
+}
+
+// =========================================================================================
+// Fused pressure-gradient correction + velocity boundary rows ("corrector").
+// Replaces velocity_correction_kerenl + enforce_velocity_BC_kernel
+// (fluid_cpp/cuda/ParallelNavierStokes.cu:194-217, :58-111).
+// =========================================================================================
+
+// One velocity component of a boundary row x = 0 / X-1 (SerialNavierStokes.cpp:236-294).
+//   inner_copy : what an UNSET wall cell copies (u_next[1][y] on the left, corrected u[X-2][y]
+//                on the right -- the reference's asymmetry, :269 vs :276)
+//   old_wall   : this field's wall row BEFORE the step (unset bottom corner copies old [x][1])
+//   star_wall  : u_next's wall row (unset top corner copies u_next[x][Y-2], :246)
+template <typename T, int V, int H>
+FB_DEV_NOINLINE Vec<T, V> velocity_wall_row(const Edges<T>& e, int edge, int x,
+                                            const Vec<T, V>& inner_copy, const Vec<T, V>& old_wall,
+                                            const Vec<T, V>& star_wall, const Strip<V, H>& st,
+                                            int Y) {
+    Vec<T, V> r = wall_row<T, V>(e, edge, inner_copy, st.col0, Y);
+    if (st.has_bottom) {
+        const T stale = old_wall.a[1];
+        if (st.lane == 0) r.a[0] = edge_value(e, BOTTOM, x, stale);
+    }
+    if (st.has_top) {
+        const T sv = pick<T, V>(star_wall, st.ym2_lane, st.ym2_e);
+#pragma unroll
+        for (int k = 0; k < V; ++k)
+            if (st.lane == st.top_lane && k == st.top_e) r.a[k] = edge_value(e, TOP, x, sv);
+    }
+    return r;
+}
+
+template <typename T, int V, bool MASK>
+FB_DEV void corrector_task(const CorrectorArgs<T>& A, int strip, int chunk, int lane) {
+    constexpr int H = 4;
+    using A_ = Ar<T>;
+    using VT = Vec<T, V>;
+    const Geom& g = A.g;
+    const int X = g.X, Y = g.Y;
+    Strip<V, H> st;
+    st.init(g, strip, lane);
+
+    const int c0 = A.out_lo + chunk * g.rows_per_chunk;
+    const int c1 = min(c0 + g.rows_per_chunk, A.out_hi);
+    if (c0 >= c1) return;
+    const int slab_hi = g.row0 + g.rows;
+    const int r_begin = max(c0 - 1, g.row0);
+    const int load_hi = min(c1 + 1, slab_hi);
+    const int r_end = c1;
+
+    const long long base = (long long)st.col0 - (long long)g.row0 * g.pitch;
+    const T* pp = A.p + base;
+    const T* usp = A.us + base;
+    const T* vsp = A.vs + base;
+    T* up = A.u + base;
+    T* vp = A.v + base;
+
+    VT wp[2] = {vzero<T, V>(), vzero<T, V>()};  // p rows r-2, r-1
+
+    auto load = [&](const T* f, int r) -> VT {
+        if (st.ld_ok && r >= r_begin && r < load_hi) return ld_ro<T, V>(f + (long long)r * g.pitch);
+        return vzero<T, V>();
+    };
+    auto load_star = [&](const T* f, int r) -> VT {  // u_next / v_next of an interior row
+        if (st.ld_ok && r >= max(c0, 1) && r < min(c1, X - 1)) return ld_ro<T, V>(f + (long long)r * g.pitch);
+        return vzero<T, V>();
+    };
+
+    VT np_ = load(pp, r_begin);
+    VT nus = load_star(usp, r_begin - 1), nvs = load_star(vsp, r_begin - 1);
+    for (int r = r_begin; r <= r_end; ++r) {
+        const VT cp = np_;
+        const VT us = nus, vs = nvs;
+        np_ = load(pp, r + 1);
+        nus = load_star(usp, r);
+        nvs = load_star(vsp, r);
+        const int rr = r - 1;
+        if (rr >= max(c0, 1) && rr < min(c1, X - 1)) {
+            VT pym, pyp;
+            y_neighbours<T, V>(wp[1], pym, pyp);
+            VT un, vn;
+#pragma unroll
+            for (int e = 0; e < V; ++e) {
+                const T dp_dx = A_::cdiff(cp.a[e], wp[0].a[e], A.hx, A.hx2);
+                const T dp_dy = A_::cdiff(pyp.a[e], pym.a[e], A.hy, A.hy2);
+                un.a[e] = A_::sub(us.a[e], A_::mul(A.dt_over_rho, dp_dx));
+                vn.a[e] = A_::sub(vs.a[e], A_::mul(A.dt_over_rho, dp_dy));
+            }
+            if (MASK) {  // interior flags (SerialNavierStokes.cpp:224-233)
+                const long long off = (long long)(rr - g.row0) * g.pitch + st.col0;
+                if (st.ld_ok) {
+#pragma unroll
+                    for (int e = 0; e < V; ++e) {
+                        const int col = st.col0 + e;
+                        if (col >= 1 && col <= Y - 2) {
+                            if (A.uset && A.uset[off + e]) un.a[e] = A.uval[off + e];
+                            if (A.vset && A.vset[off + e]) vn.a[e] = A.vval[off + e];
+                        }
+                    }
+                }
+            }
+            // y-edges: bottom copies the corrected value (:239,:253), top copies u_next (:246,:260)
+            if (st.has_bottom && lane == 0) {
+                un.a[0] = edge_value(A.eu, BOTTOM, rr, un.a[1]);
+                vn.a[0] = edge_value(A.ev, BOTTOM, rr, vn.a[1]);
+            }
+            if (st.has_top) {
+                const T ubelow = shfl_up1(us.a[V - 1]);
+                const T vbelow = shfl_up1(vs.a[V - 1]);
+#pragma unroll
+                for (int e = 0; e < V; ++e)
+                    if (lane == st.top_lane && e == st.top_e) {
+                        un.a[e] = edge_value(A.eu, TOP, rr, (e > 0) ? us.a[e > 0 ? e - 1 : 0] : ubelow);
+                        vn.a[e] = edge_value(A.ev, TOP, rr, (e > 0) ? vs.a[e > 0 ? e - 1 : 0] : vbelow);
+                    }
+            }
+            if (st.st_ok) {
+                st_vec<T, V>(up + (long long)rr * g.pitch, un);
+                st_vec<T, V>(vp + (long long)rr * g.pitch, vn);
+            }
+            if (rr == 1 && c0 == 0) {  // boundary row x = 0: unset cells copy u_next[1][y] (:269,:283)
+                VT ou = vzero<T, V>(), ov = ou, su = ou, sv = ou;
+                if (st.ld_ok) {
+                    ou = ld_rw<T, V>(up);
+                    ov = ld_rw<T, V>(vp);
+                    su = ld_rw<T, V>(usp);
+                    sv = ld_rw<T, V>(vsp);
+                }
+                const VT wu_ = velocity_wall_row<T, V, H>(A.eu, LEFT, 0, us, ou, su, st, Y);
+                const VT wv_ = velocity_wall_row<T, V, H>(A.ev, LEFT, 0, vs, ov, sv, st, Y);
+                if (st.st_ok) {
+                    st_vec<T, V>(up, wu_);
+                    st_vec<T, V>(vp, wv_);
+                }
+            }
+            if (rr == X - 2 && c1 == X) {  // boundary row x = X-1: unset cells copy corrected u[X-2][y]
+                const long long o = (long long)(X - 1) * g.pitch;
+                VT ou = vzero<T, V>(), ov = ou, su = ou, sv = ou;
+                if (st.ld_ok) {
+                    ou = ld_rw<T, V>(up + o);
+                    ov = ld_rw<T, V>(vp + o);
+                    su = ld_rw<T, V>(usp + o);
+                    sv = ld_rw<T, V>(vsp + o);
+                }
+                const VT wu_ = velocity_wall_row<T, V, H>(A.eu, RIGHT, X - 1, un, ou, su, st, Y);
+                const VT wv_ = velocity_wall_row<T, V, H>(A.ev, RIGHT, X - 1, vn, ov, sv, st, Y);
+                if (st.st_ok) {
+                    st_vec<T, V>(up + o, wu_);
+                    st_vec<T, V>(vp + o, wv_);
+                }
+            }
+        }
+        wp[0] = wp[1];
+        wp[1] = cp;
+    }
+}
+
+}  // namespace fb

@@ -1,0 +1,111 @@
+// emu_backend.cpp -- HOST implementation of fluid_simulation_b200/csrc/backend.h.
+// TEST INFRASTRUCTURE ONLY: lets `pytest -m "not gpu"` run the product's host logic (api.cpp)
+// and the very same warp task bodies (warp_kernels.cuh) on the CPU, 32 threads per warp with
+// barrier-emulated shuffles, and compare them bit-for-bit with the oracle. It is built into
+// tests/emu/libfluidb200_emu.so, which nothing under fluid_simulation_b200/ ever loads.
+#include <stdlib.h>
+#include <string.h>
+
+#include <thread>
+#include <vector>
+
+#define FLUIDB200_HOST_EMU 1
+#include "backend.h"
+#include "warp_kernels.cuh"
+
+namespace {
+// run fn(strip, chunk, lane) for every warp task; a warp = 32 lockstep-capable threads
+template <typename F> void run_grid(int nstrips, int nchunks, F fn) {
+    struct Job { int strip, chunk; };
+    std::vector<Job> jobs;
+    for (int c = 0; c < nchunks; ++c)
+        for (int s = 0; s < nstrips; ++s) jobs.push_back({s, c});
+    // one warp at a time (32 threads); tasks are independent so order does not matter
+    for (const Job& j : jobs) {
+        EmuWarp w;
+        std::vector<std::thread> lanes;
+        for (int l = 0; l < 32; ++l)
+            lanes.emplace_back([&, l] {
+                emu_warp = &w;
+                emu_lane = l;
+                fn(j.strip, j.chunk, l);
+                w.bar.arrive_and_drop();
+            });
+        for (auto& t : lanes) t.join();
+    }
+}
+}  // namespace
+
+namespace fbk {
+const char* backend_name() { return "host-emulation (tests only)"; }
+const char* be_last_error_string() { return "host emulation error"; }
+int be_set_device(int) { return 0; }
+int be_malloc(void** p, size_t bytes) {
+    *p = aligned_alloc(256, (bytes + 255) / 256 * 256);
+    return *p ? 0 : -1;
+}
+int be_free(void* p) { free(p); return 0; }
+int be_memset_async(void* p, int v, size_t n, void*) { memset(p, v, n); return 0; }
+int be_memcpy_async(void* d, const void* s, size_t n, CopyKind, void*) { memcpy(d, s, n); return 0; }
+int be_memcpy2d_async(void* d, size_t dp, const void* s, size_t sp, size_t w, size_t h, CopyKind, void*) {
+    for (size_t i = 0; i < h; ++i) memcpy((char*)d + i * dp, (const char*)s + i * sp, w);
+    return 0;
+}
+int be_stream_create(void** s) { *s = nullptr; return 0; }
+int be_stream_destroy(void*) { return 0; }
+int be_stream_sync(void*) { return 0; }
+int be_graph_begin(void*) { return -1; }
+int be_graph_end(void*, void**) { return -1; }
+int be_graph_launch(void*, void*) { return -1; }
+int be_graph_destroy(void*) { return 0; }
+
+template <typename T, int K>
+static void jac_k(const fb::JacobiArgs<T>& a, bool mask, int nchunks) {
+    constexpr int V = fb::VecWidth<T>::V;
+    if (K == 1 && mask)
+        run_grid(a.g.nstrips, nchunks, [&](int s, int c, int l) { fb::jacobi_task<T, V, 1, true>(a, s, c, l); });
+    else
+        run_grid(a.g.nstrips, nchunks, [&](int s, int c, int l) { fb::jacobi_task<T, V, K, false>(a, s, c, l); });
+}
+template <typename T> int launch_jacobi(const fb::JacobiArgs<T>& a, int sweeps, bool mask, int nchunks, void*) {
+    switch (sweeps) {
+        case 1: jac_k<T, 1>(a, mask, nchunks); break;
+        case 2: jac_k<T, 2>(a, mask, nchunks); break;
+        case 3: jac_k<T, 3>(a, mask, nchunks); break;
+        case 4: jac_k<T, 4>(a, mask, nchunks); break;
+        case 5: jac_k<T, 5>(a, mask, nchunks); break;
+        case 6: jac_k<T, 6>(a, mask, nchunks); break;
+        case 7: jac_k<T, 7>(a, mask, nchunks); break;
+        case 8: jac_k<T, 8>(a, mask, nchunks); break;
+        default: return -1;
+    }
+    return 0;
+}
+template <typename T> int launch_predictor(const fb::PredictorArgs<T>& a, int nchunks, void*) {
+    constexpr int V = fb::VecWidth<T>::V;
+    run_grid(a.g.nstrips, nchunks, [&](int s, int c, int l) { fb::predictor_task<T, V>(a, s, c, l); });
+    return 0;
+}
+template <typename T> int launch_corrector(const fb::CorrectorArgs<T>& a, bool mask, int nchunks, void*) {
+    constexpr int V = fb::VecWidth<T>::V;
+    if (mask) run_grid(a.g.nstrips, nchunks, [&](int s, int c, int l) { fb::corrector_task<T, V, true>(a, s, c, l); });
+    else run_grid(a.g.nstrips, nchunks, [&](int s, int c, int l) { fb::corrector_task<T, V, false>(a, s, c, l); });
+    return 0;
+}
+template <typename T>
+int launch_init_cavity(T* const f[7], long long pitch, int, int Y, int, int rows, T lid, void*) {
+    for (int k = 0; k < 7; ++k) {
+        if (!f[k]) continue;
+        for (long long i = 0; i < (long long)rows * pitch; ++i)
+            f[k][i] = (k == 0 && (int)(i % pitch) == Y - 1) ? lid : T(0);
+    }
+    return 0;
+}
+#define INSTANTIATE(T)                                                                \
+    template int launch_jacobi<T>(const fb::JacobiArgs<T>&, int, bool, int, void*);  \
+    template int launch_predictor<T>(const fb::PredictorArgs<T>&, int, void*);       \
+    template int launch_corrector<T>(const fb::CorrectorArgs<T>&, bool, int, void*); \
+    template int launch_init_cavity<T>(T* const[7], long long, int, int, int, int, T, void*);
+INSTANTIATE(float)
+INSTANTIATE(double)
+}  // namespace fbk

@@ -1,0 +1,51 @@
+// emu_shim.h -- HOST emulation shims so fluid_simulation_b200/csrc/warp_kernels.cuh can be
+// compiled with g++ and its warp tasks run on the CPU (TEST INFRASTRUCTURE ONLY).
+// A warp is 32 std::threads, one per lane; a shuffle is "publish, barrier, read, barrier".
+// Warp-uniform control flow around shuffles is therefore REQUIRED, exactly as on the GPU:
+// a divergent shuffle deadlocks here instead of being undefined behaviour there.
+// Build with -ffp-contract=off so the *_rn shims below are never fused.
+#pragma once
+#include <algorithm>
+#include <barrier>
+#include <cmath>
+#include <cstdint>
+#include <cstring>
+
+#define FB_DEV inline
+#define FB_DEV_NOINLINE __attribute__((noinline))
+using std::max;
+using std::min;
+
+struct EmuWarp {
+    std::barrier<> bar{32};
+    alignas(8) unsigned char slot[32][8];
+};
+inline thread_local EmuWarp* emu_warp = nullptr;
+inline thread_local int emu_lane = 0;
+
+template <typename T> inline T emu_exchange(T x, int src) {
+    std::memcpy(emu_warp->slot[emu_lane], &x, sizeof(T));
+    emu_warp->bar.arrive_and_wait();
+    T r;
+    std::memcpy(&r, emu_warp->slot[src], sizeof(T));
+    emu_warp->bar.arrive_and_wait();
+    return r;
+}
+template <typename T> inline T __shfl_up_sync(unsigned, T x, int d) {
+    return emu_exchange(x, emu_lane - d >= 0 ? emu_lane - d : emu_lane);
+}
+template <typename T> inline T __shfl_down_sync(unsigned, T x, int d) {
+    return emu_exchange(x, emu_lane + d < 32 ? emu_lane + d : emu_lane);
+}
+template <typename T> inline T __shfl_sync(unsigned, T x, int src) { return emu_exchange(x, src & 31); }
+
+inline float __fadd_rn(float a, float b) { return a + b; }
+inline float __fsub_rn(float a, float b) { return a - b; }
+inline float __fmul_rn(float a, float b) { return a * b; }
+inline float __fdiv_rn(float a, float b) { return a / b; }
+inline double __dadd_rn(double a, double b) { return a + b; }
+inline double __dsub_rn(double a, double b) { return a - b; }
+inline double __dmul_rn(double a, double b) { return a * b; }
+inline double __ddiv_rn(double a, double b) { return a / b; }
+inline double __fma_rn(double a, double b, double c) { return std::fma(a, b, c); }
+inline float __double2float_rn(double a) { return (float)a; }

@@ -1,0 +1,151 @@
+"""Parity of the product's C ABI against the reference, on two back ends:
+
+* ``cuda`` (marked gpu): the real sm_100a library, fluid_simulation_b200/libfluidb200.so;
+* ``emu``  (CPU): tests/emu's host build of the SAME host logic (csrc/api.cpp) and the SAME
+  warp task bodies (csrc/warp_kernels.cuh), 32 threads per warp -- so the kernel and planner
+  logic is checked here, where there is no GPU.
+
+Expected values: the golden fields recorded from the reference (tests/golden/*.npz), and the
+oracle (pinned to the reference in tests/test_oracle.py) on the same inputs. Comparison is
+bit-exact on all seven fields (stricter than fluid_cpp/tests/test_main.cpp:77, which checks v
+only, with ==).
+"""
+import os
+
+import numpy as np
+import pytest
+
+from oracle import Oracle
+from tests import helpers as H
+
+BACKENDS = [pytest.param("emu"), pytest.param("cuda", marks=pytest.mark.gpu)]
+
+
+@pytest.fixture(scope="module", params=BACKENDS)
+def Solver(request):
+    if request.param == "emu":
+        return H.solver_factory(H.build_emu())
+    import torch
+    assert torch.cuda.is_available(), "gpu-marked test needs a CUDA device"
+    return H.solver_factory(None)
+
+
+@pytest.fixture
+def env():
+    saved = dict(os.environ)
+    yield os.environ
+    os.environ.clear()
+    os.environ.update(saved)
+
+
+GOLDEN_FIELD_CASES = [
+    ("cavity41_S3_K7", None, 1), ("cavity41_S3_K7", None, 2), ("cavity41_S3_K7", None, 3),
+    ("cavity41_S3_K7", None, 4), ("cavity41_S3_K7", None, 5), ("cavity41_S3_K7", None, 7),
+    ("cavity41_S3_K7", None, 8), ("cavity41_S1_K1", None, 4), ("cavity41_S10_K50", None, 4),
+    ("cavity41_S10_K50", None, 8), ("cavity67x45_S25_K30", 6, 4), ("cavity45x131_S12_K33", 5, 4),
+    ("cavity45x131_S12_K33", 3, 8), ("cavity41_f64_S100_K50", 6, 4), ("cavity41_f64_S100_K50", 3, 7),
+    ("general53x37_S20_K30", 5, 4), ("general53x37_f64_S20_K30", 4, 4),
+]
+
+
+@pytest.mark.parametrize("name,steps,kmax", GOLDEN_FIELD_CASES)
+def test_golden_fields(Solver, golden, name, steps, kmax):
+    """Full solve through migrateSolve(); S may be cut short for the emulator, in which case the
+    oracle (pinned to the same golden files) provides the expected fields."""
+    rec = dict(golden[name])
+    full = steps is None or steps >= rec["S"]
+    if not full:
+        rec["S"] = steps
+    s = H.golden_case_setup(rec, Solver)
+    s.set_sweeps_per_launch(kmax)
+    s.migrateSolve()
+    want = H.load_fields(golden[name]) if full else H.golden_case_setup(rec, Oracle).solve()
+    H.compare_with(s, want, tag=f"{name}/k{kmax}")
+    s.close()
+
+
+@pytest.mark.parametrize("dtype", ["float32", "float64"])
+@pytest.mark.parametrize("kmax", [1, 4, 6])
+def test_per_cell_edge_bcs_inside_temporal_blocking(Solver, dtype, kmax):
+    X, Y = 37, 150 if dtype == "float32" else 80   # more than one strip along y
+    src = H.edges_only_bcs(X, Y, np.dtype(dtype))
+    src.time_step, src.num_iterations, src.num_poisson_iterations = 0.0002, 3, 13
+    s = H.copy_bcs(src, Solver(X, Y, 1.0, 1.0, np.dtype(dtype)))
+    s.set_sweeps_per_launch(kmax)
+    s.migrateSolve()
+    src.solve()
+    H.compare_with(s, src, tag=f"edges/{dtype}/k{kmax}")
+    s.close()
+
+
+@pytest.mark.parametrize("rpc", [2, 3, 5, 16])
+def test_chunking_does_not_change_bits(Solver, env, golden, rpc):
+    env["FLUIDB200_RPC"] = str(rpc)
+    rec = dict(golden["cavity67x45_S25_K30"]); rec["S"] = 2; rec["K"] = 9
+    s = H.golden_case_setup(rec, Solver)
+    s.set_sweeps_per_launch(4)
+    s.migrateSolve()
+    H.compare_with(s, H.golden_case_setup(rec, Oracle).solve(), tag=f"rpc{rpc}")
+    s.close()
+
+
+def test_phases_one_at_a_time(Solver, golden):
+    rec = dict(golden["cavity45x131_S12_K33"]); rec["S"] = 1
+    s = H.golden_case_setup(rec, Solver)
+    o = H.golden_case_setup(rec, Oracle)
+    s.migrateHostToDevice()
+    for step in range(2):
+        s.unifiedApproximateTimeStepAndRightHand(); o.predictor()
+        for n in ("u_next", "v_next", "rhs"):
+            H.assert_bit_equal(s.device_field(n), getattr(o, n), f"step{step}:{n}")
+        s.poissonSweeps(11); o.poisson_sweeps(11)
+        for n in ("p", "p_next"):
+            H.assert_bit_equal(s.device_field(n), getattr(o, n), f"step{step}:{n}")
+        s.unifiedVelocityCorrection(); o.corrector()
+        for n in ("u", "v"):
+            H.assert_bit_equal(s.device_field(n), getattr(o, n), f"step{step}:{n}")
+    s.close()
+
+
+def test_solve_continues_from_device_state(Solver, golden):
+    """Repeated solve() continues the simulation (SURVEY 8b 'Semantics to preserve')."""
+    rec = dict(golden["cavity41_S10_K50"]); rec["K"] = 6
+    a = H.golden_case_setup(rec, Solver); a.num_iterations = 4
+    a.migrateHostToDevice(); a.solve(); a.solve(); a.migrateDeviceToHost()
+    o = H.golden_case_setup(rec, Oracle); o.num_iterations = 8; o.solve()
+    H.compare_with(a, o, tag="continue")
+    a.close()
+
+
+def test_setters_touch_host_only_until_migrate(Solver):
+    s = Solver(41, 41)
+    s.num_iterations, s.num_poisson_iterations = 1, 2
+    s.migrateHostToDevice()          # pristine grid, like the reference ctor upload
+    s.set_cavity(1.0)                # host only
+    s.solve(); s.synchronize()
+    assert not s.device_field("u").any(), "device must not see BCs before migrateHostToDevice"
+    s.close()
+
+
+def test_tiny_and_degenerate_boxes(Solver):
+    from fluid_simulation_b200 import FluidB200Error
+    for X, Y in ((3, 3), (3, 9), (9, 3), (4, 5)):
+        src = Oracle(X, Y).set_cavity()
+        src.num_iterations, src.num_poisson_iterations = 3, 5
+        s = H.copy_bcs(src, Solver(X, Y)); s.set_sweeps_per_launch(4)
+        s.migrateSolve(); src.solve()
+        H.compare_with(s, src, tag=f"{X}x{Y}")
+        s.close()
+    with pytest.raises(FluidB200Error):
+        Solver(2, 41)
+
+
+def test_zero_iterations_are_noops(Solver):
+    s = Solver(41, 41).set_cavity()
+    s.num_iterations, s.num_poisson_iterations = 2, 0
+    s.migrateSolve()
+    o = Oracle(41, 41).set_cavity(); o.num_iterations, o.num_poisson_iterations = 2, 0; o.solve()
+    H.compare_with(s, o, tag="K0")
+    s.num_iterations = 0
+    s.solve(); s.synchronize()
+    s.close()
