@@ -121,34 +121,28 @@ template <typename T, int V> FB_DEV void st_vec(T* p, const Vec<T, V>& v) {
 }
 
 
-// value of an edge cell: its boundary value when the flag is set, else `copy`
-template <typename T> FB_DEV T edge_value(const Edges<T>& e, int edge, int idx, T copy) {
-    const int m = e.mode[edge];
-    if (m == EDGE_UNSET) return copy;
-    if (m == EDGE_CONST) return e.cval[edge];
-    return e.set[edge][idx] ? e.val[edge][idx] : copy;
-}
-
-
 // Per-lane view of a strip.
 template <int V, int H> struct Strip {
     static constexpr int W = 32 * V;      // columns loaded by the warp
     static constexpr int S = W - 2 * H;   // columns owned (stride between strips)
     int lane, col0;                       // first column of this lane
+    int lcol;                             // column used for LOADS: col0 clamped into the row, so
+                                          // loads never need a predicate (such lanes never store)
     bool has_bottom, has_top, ld_ok, st_ok;
-    int top_lane, top_e;                  // where column Y-1 lives (valid when has_top)
-    int ym2_lane, ym2_e;                  // where column Y-2 lives
+    unsigned top_bits;                    // bit e set <=> element e of this lane is column Y-1
+    int ym2_lane, ym2_e;                  // where column Y-2 lives (valid when has_top)
     FB_DEV void init(const Geom& g, int strip, int lane_) {
         lane = lane_;
         const int ys = strip * S;
         col0 = ys + lane * V;
         has_bottom = (strip == 0);
         has_top = (ys <= g.Y - 1) && (g.Y - 1 < ys + W);
-        top_lane = (g.Y - 1 - ys) / V;
-        top_e = (g.Y - 1 - ys) % V;
+        const int top_lane = (g.Y - 1 - ys) / V, top_e = (g.Y - 1 - ys) % V;
+        top_bits = (has_top && lane == top_lane) ? (1u << top_e) : 0u;
         ym2_lane = (g.Y - 2 - ys) / V;
         ym2_e = (g.Y - 2 - ys) % V;
         ld_ok = (long long)col0 + V <= g.pitch;
+        lcol = ld_ok ? col0 : (int)(g.pitch - V);
         const int vlo = has_bottom ? 0 : ys + H;
         const int vhi = (strip == g.nstrips - 1) ? g.Y : ys + W - H;
         st_ok = ld_ok && col0 >= vlo && col0 < vhi;
@@ -171,15 +165,56 @@ FB_DEV void y_neighbours(const Vec<T, V>& c, Vec<T, V>& ym, Vec<T, V>& yp) {
     }
 }
 
-// The value held at global column `lane_/e_` of a row spread over the warp (warp-uniform call).
+// The value held at lane `lane_`, element `e_` of a row spread over the warp (warp-uniform call).
 template <typename T, int V> FB_DEV T pick(const Vec<T, V>& row, int lane_, int e_) {
     T r = T(0);
 #pragma unroll
     for (int e = 0; e < V; ++e) {
         const T s = shfl_idx(row.a[e], lane_ & 31);
-        if (e == e_) r = s;
+        r = (e == e_) ? s : r;
     }
     return r;
+}
+
+// resolved flag/value of one edge cell
+template <typename T> struct EdgeCell {
+    bool use;
+    T v;
+};
+template <typename T> FB_DEV EdgeCell<T> edge_cell(const Edges<T>& e, int edge, int idx) {
+    EdgeCell<T> r;
+    const int m = e.mode[edge];
+    if (m == EDGE_UNSET) {
+        r.use = false; r.v = T(0);
+    } else if (m == EDGE_CONST) {
+        r.use = true; r.v = e.cval[edge];
+    } else {
+        r.use = e.set[edge][idx] != 0; r.v = e.val[edge][idx];
+    }
+    return r;
+}
+
+// The two y-edge cells of interior row `row`: the boundary value when the flag is set, else a copy
+// of column 1 of `bottom_src` / column Y-2 of `top_src` (SerialNavierStokes.cpp:163-175; the
+// velocity version copies u_next at the top, :246). Element selection uses compile-time indices
+// and a per-lane bit mask so the vectors stay in registers.
+template <typename T, int V, int H>
+FB_DEV void apply_y_edges(const Edges<T>& e, const Strip<V, H>& st, int row, Vec<T, V>& out,
+                          const Vec<T, V>& bottom_src, const Vec<T, V>& top_src) {
+    if (st.has_bottom) {
+        const EdgeCell<T> b = edge_cell(e, BOTTOM, row);
+        const T nv = b.use ? b.v : bottom_src.a[1];
+        out.a[0] = (st.lane == 0) ? nv : out.a[0];
+    }
+    if (st.has_top) {
+        const EdgeCell<T> t = edge_cell(e, TOP, row);
+        const T below = shfl_up1(top_src.a[V - 1]);
+        Vec<T, V> cand;
+#pragma unroll
+        for (int k = 0; k < V; ++k) cand.a[k] = (k > 0) ? top_src.a[k > 0 ? k - 1 : 0] : below;
+#pragma unroll
+        for (int k = 0; k < V; ++k) out.a[k] = ((st.top_bits >> k) & 1u) ? (t.use ? t.v : cand.a[k]) : out.a[k];
+    }
 }
 
 // store only interior columns [1, Y-2] of a row (edge cells of u_next/v_next/rhs are never
@@ -205,17 +240,17 @@ FB_DEV void st_interior(T* rowp, int col0, int Y, const Vec<T, V>& v) {
 // level's adjacent interior row `inner` (SerialNavierStokes.cpp:177-188). Corner elements are
 // placeholders here (corners feed no 5-point stencil); wall_row_out() fixes them for output.
 template <typename T, int V>
-FB_DEV_NOINLINE Vec<T, V> wall_row(const Edges<T>& e, int edge, const Vec<T, V>& inner, int col0,
-                                   int Y) {
+FB_DEV Vec<T, V> wall_row(const Edges<T>& e, int edge, const Vec<T, V>& inner, int col0, int Y) {
     Vec<T, V> r = inner;
     const int m = e.mode[edge];
-    if (m == EDGE_UNSET) return r;
+    if (m != EDGE_UNSET) {
 #pragma unroll
-    for (int k = 0; k < V; ++k) {
-        const int col = col0 + k;
-        if (col >= 1 && col <= Y - 2) {
-            if (m == EDGE_CONST) r.a[k] = e.cval[edge];
-            else if (e.set[edge][col]) r.a[k] = e.val[edge][col];
+        for (int k = 0; k < V; ++k) {
+            const int col = col0 + k;
+            if (col >= 1 && col <= Y - 2) {
+                if (m == EDGE_CONST) r.a[k] = e.cval[edge];
+                else if (e.set[edge][col]) r.a[k] = e.val[edge][col];
+            }
         }
     }
     return r;
@@ -226,22 +261,44 @@ FB_DEV_NOINLINE Vec<T, V> wall_row(const Edges<T>& e, int edge, const Vec<T, V>&
 // that neighbour is refreshed (the y-edge loop runs first, SerialNavierStokes.cpp:163-175 vs
 // :177-188), i.e. it is one sweep stale.
 template <typename T, int V, int H>
-FB_DEV_NOINLINE Vec<T, V> wall_row_out(const Edges<T>& e, int edge, int x, const Vec<T, V>& inner,
-                                       const Vec<T, V>& prev_wall, const Strip<V, H>& st, int Y) {
+FB_DEV Vec<T, V> wall_row_out(const Edges<T>& e, int edge, int x, const Vec<T, V>& inner,
+                              const Vec<T, V>& prev_wall, const Strip<V, H>& st, int Y) {
     Vec<T, V> r = wall_row<T, V>(e, edge, inner, st.col0, Y);
     if (st.has_bottom) {
-        const T stale = prev_wall.a[1];  // column 1 (V >= 2)
-        if (st.lane == 0) r.a[0] = edge_value(e, BOTTOM, x, stale);
+        const EdgeCell<T> b = edge_cell(e, BOTTOM, x);
+        const T nv = b.use ? b.v : prev_wall.a[1];  // column 1 (V >= 2)
+        r.a[0] = (st.lane == 0) ? nv : r.a[0];
     }
     if (st.has_top) {
+        const EdgeCell<T> t = edge_cell(e, TOP, x);
         const T stale = pick<T, V>(prev_wall, st.ym2_lane, st.ym2_e);
+        const T nv = t.use ? t.v : stale;
 #pragma unroll
-        for (int k = 0; k < V; ++k)
-            if (st.lane == st.top_lane && k == st.top_e) r.a[k] = edge_value(e, TOP, x, stale);
+        for (int k = 0; k < V; ++k) r.a[k] = ((st.top_bits >> k) & 1u) ? nv : r.a[k];
     }
     return r;
 }
 
+// One Jacobi update of a row strip: out = ((b - (((xm + xp) + yp) + ym)) * -0.25
+// (SerialNavierStokes.cpp:144-146, operand order kept).
+template <typename T, int V>
+FB_DEV Vec<T, V> jacobi_row(const Vec<T, V>& xm, const Vec<T, V>& c, const Vec<T, V>& xp, const Vec<T, V>& b) {
+    using A_ = Ar<T>;
+    Vec<T, V> ym, yp, out;
+    y_neighbours<T, V>(c, ym, yp);
+#pragma unroll
+    for (int e = 0; e < V; ++e) {
+        const T s = A_::add(A_::add(A_::add(xm.a[e], xp.a[e]), yp.a[e]), ym.a[e]);
+        out.a[e] = A_::neg_quarter(A_::sub(b.a[e], s));
+    }
+    return out;
+}
+
+// Pipeline: at step r the warp loads row r of p (level 0) and level t = 1..K produces row r-t
+// from rows r-t-1, r-t, r-t+1 of level t-1. w[t] holds the two newest rows of level t, bw[j]
+// the scaled right-hand side of row r-1-j. Steps whose K rows are all plain interior rows take
+// the FAST path (no per-level range checks, no wall logic); pipeline fill/drain at the box walls
+// and masked sweeps take the GENERAL path. Both act on the same register state.
 template <typename T, int V, int K, bool MASK>
 FB_DEV void jacobi_task(const JacobiArgs<T>& A, int strip, int chunk, int lane) {
     constexpr int H = (K + 3) & ~3;
@@ -260,12 +317,14 @@ FB_DEV void jacobi_task(const JacobiArgs<T>& A, int strip, int chunk, int lane) 
     const int load_hi = min(c1 + K, slab_hi);
     const int r_end = c1 - 1 + K;
 
-    const T* pin = A.p_in + (long long)st.col0 - (long long)g.row0 * g.pitch;
-    const T* rin = A.rhs + (long long)st.col0 - (long long)g.row0 * g.pitch;
+    const long long base = (long long)st.lcol - (long long)g.row0 * g.pitch;
+    const T* pin = A.p_in + base;
+    const T* rin = A.rhs + base;
     T* pout = A.p_out + (long long)st.col0 - (long long)g.row0 * g.pitch;
+    const bool y_edges = st.has_bottom || st.has_top;
 
-    VT w[K][2];   // w[t] = rows (q-1, q) of sweep level t, q = newest row of that level
-    VT bw[K];     // bw[j] = (rhs*hx)*hy of row r-1-j
+    VT w[K][2];
+    VT bw[K];
 #pragma unroll
     for (int t = 0; t < K; ++t) {
         w[t][0] = vzero<T, V>();
@@ -274,88 +333,122 @@ FB_DEV void jacobi_task(const JacobiArgs<T>& A, int strip, int chunk, int lane) 
     }
 
     auto load_p = [&](int r) -> VT {
-        if (st.ld_ok && r >= r_begin && r < load_hi) return ld_ro<T, V>(pin + (long long)r * g.pitch);
+        if (r >= r_begin && r < load_hi) return ld_ro<T, V>(pin + (long long)r * g.pitch);
         return vzero<T, V>();
     };
     auto load_b = [&](int r) -> VT {  // rhs of row r (interior rows only)
-        if (st.ld_ok && r >= r_begin && r < load_hi && r >= 1 && r <= X - 2)
-            return ld_ro<T, V>(rin + (long long)r * g.pitch);
+        if (r >= r_begin && r < load_hi && r >= 1 && r <= X - 2) return ld_ro<T, V>(rin + (long long)r * g.pitch);
         return vzero<T, V>();
     };
-
-    VT nxt_p = load_p(r_begin);
-    VT nxt_b = load_b(r_begin - 1);
-    for (int r = r_begin; r <= r_end; ++r) {
-        VT cur = nxt_p;
-        VT bnew = nxt_b;
-        nxt_p = load_p(r + 1);
-        nxt_b = load_b(r);
-        // (rhs * hx) * hy, SerialNavierStokes.cpp:144 -- done once per row, reused by K levels
+    // (rhs * hx) * hy, SerialNavierStokes.cpp:144 -- once per row, reused by all K levels
+    auto push_b = [&](VT bnew) {
 #pragma unroll
         for (int e = 0; e < V; ++e) bnew.a[e] = A_::mul(A_::mul(bnew.a[e], A.hx), A.hy);
 #pragma unroll
         for (int t = K - 1; t > 0; --t) bw[t] = bw[t - 1];
         bw[0] = bnew;
+    };
 
+    // steps r in [fast_lo, fast_hi]: every level's row r-t lies in [2, X-3]. Strips that hold a
+    // y-edge column and masked sweeps always take the general path. The fast loop is unrolled U
+    // steps deep (U even and >= K) so that the row windows rotate by register renaming instead of
+    // moves, and it keeps U rows of p and rhs in flight per lane (U KB per warp) to cover HBM
+    // latency at the low occupancy this register-resident pipeline runs at.
+    constexpr int U = (K + 1) & ~1;
+    const int fast_lo = max(r_begin, K + 2);
+    int nfast = min(r_end, X - 2) - fast_lo + 1;
+    if (MASK || y_edges || nfast < 0) nfast = 0;
+    nfast -= nfast % U;
+    const int fast_hi = fast_lo + nfast - 1;
+
+    VT nxt_p = load_p(r_begin);
+    VT nxt_b = load_b(r_begin - 1);
+    int r = r_begin;
+#pragma unroll 1
+    for (int phase = 0; phase < 2; ++phase) {
+        // ---------------- GENERAL path: [r, fast_lo) first, then (fast_hi, r_end] ----------------
+        const int gen_hi = (phase == 0 && nfast > 0) ? fast_lo - 1 : r_end;
+#pragma unroll 1
+        for (; r <= gen_hi; ++r) {
+            VT cur = nxt_p;
+            push_b(nxt_b);
+            nxt_p = load_p(r + 1);
+            nxt_b = load_b(r);
 #pragma unroll
-        for (int t = 1; t <= K; ++t) {
-            const int rr = r - t;  // row this level produces now
-            VT out = cur;
-            if (rr >= 1 && rr <= X - 2) {
-                VT xm = w[t - 1][0];
-                const VT c = w[t - 1][1];
-                VT xp = cur;
-                if (t > 1) {
-                    // levels >= 1 never materialise their boundary rows: rebuild them from the
-                    // adjacent interior row of the same level
-                    if (rr == 1) xm = wall_row<T, V>(A.e, LEFT, c, st.col0, Y);
-                    if (rr == X - 2) xp = wall_row<T, V>(A.e, RIGHT, c, st.col0, Y);
-                }
-                VT ym, yp;
-                y_neighbours<T, V>(c, ym, yp);
+            for (int t = 1; t <= K; ++t) {
+                const int rr = r - t;  // row this level produces now
+                VT out = cur;
+                if (rr >= 1 && rr <= X - 2) {
+                    VT xm = w[t - 1][0];
+                    const VT c = w[t - 1][1];
+                    VT xp = cur;
+                    if (t > 1) {
+                        // levels >= 1 never materialise their boundary rows: rebuild them from the
+                        // adjacent interior row of the same level
+                        if (rr == 1) xm = wall_row<T, V>(A.e, LEFT, c, st.col0, Y);
+                        if (rr == X - 2) xp = wall_row<T, V>(A.e, RIGHT, c, st.col0, Y);
+                    }
+                    out = jacobi_row<T, V>(xm, c, xp, bw[t - 1]);
+                    if (MASK) {  // interior flags (:154-160)
+                        const long long off = (long long)(rr - g.row0) * g.pitch + st.col0;
+                        if (st.ld_ok) {
 #pragma unroll
-                for (int e = 0; e < V; ++e) {
-                    // p[x-1] + p[x+1] + p[y+1] + p[y-1], left to right (:145)
-                    const T s = A_::add(A_::add(A_::add(xm.a[e], xp.a[e]), yp.a[e]), ym.a[e]);
-                    out.a[e] = A_::neg_quarter(A_::sub(bw[t - 1].a[e], s));
-                }
-                if (MASK) {  // interior flags (:154-160)
-                    const long long off = (long long)(rr - g.row0) * g.pitch + st.col0;
-                    if (st.ld_ok) {
-#pragma unroll
-                        for (int e = 0; e < V; ++e) {
-                            const int col = st.col0 + e;
-                            if (col >= 1 && col <= Y - 2 && A.mset[off + e]) out.a[e] = A.mval[off + e];
+                            for (int e = 0; e < V; ++e) {
+                                const int col = st.col0 + e;
+                                if (col >= 1 && col <= Y - 2 && A.mset[off + e]) out.a[e] = A.mval[off + e];
+                            }
+                        }
+                    }
+                    if (y_edges) apply_y_edges<T, V, H>(A.e, st, rr, out, out, out);  // (:163-175)
+                    if (t == K) {
+                        if (rr >= c0 && rr < c1 && st.st_ok) st_vec<T, V>(pout + (long long)rr * g.pitch, out);
+                        if (rr == 1 && c0 == 0) {
+                            const VT wr = wall_row_out<T, V, H>(A.e, LEFT, 0, out, xm, st, Y);
+                            if (st.st_ok) st_vec<T, V>(pout, wr);
+                        }
+                        if (rr == X - 2 && c1 == X) {
+                            const VT wr = wall_row_out<T, V, H>(A.e, RIGHT, X - 1, out, xp, st, Y);
+                            if (st.st_ok) st_vec<T, V>(pout + (long long)(X - 1) * g.pitch, wr);
                         }
                     }
                 }
-                // y-edges of this row (:163-175)
-                if (st.has_bottom) {
-                    if (lane == 0) out.a[0] = edge_value(A.e, BOTTOM, rr, out.a[1]);
-                }
-                if (st.has_top) {
-                    const T below = shfl_up1(out.a[V - 1]);
-#pragma unroll
-                    for (int e = 0; e < V; ++e)
-                        if (lane == st.top_lane && e == st.top_e)
-                            out.a[e] = edge_value(A.e, TOP, rr, (e > 0) ? out.a[e > 0 ? e - 1 : 0] : below);
-                }
-                if (t == K) {
-                    if (rr >= c0 && rr < c1 && st.st_ok) st_vec<T, V>(pout + (long long)rr * g.pitch, out);
-                    if (rr == 1 && c0 == 0) {
-                        const VT wr = wall_row_out<T, V, H>(A.e, LEFT, 0, out, xm, st, Y);
-                        if (st.st_ok) st_vec<T, V>(pout, wr);
-                    }
-                    if (rr == X - 2 && c1 == X) {
-                        const VT wr = wall_row_out<T, V, H>(A.e, RIGHT, X - 1, out, xp, st, Y);
-                        if (st.st_ok) st_vec<T, V>(pout + (long long)(X - 1) * g.pitch, wr);
-                    }
-                }
+                w[t - 1][0] = w[t - 1][1];
+                w[t - 1][1] = cur;
+                cur = out;
             }
-            w[t - 1][0] = w[t - 1][1];
-            w[t - 1][1] = cur;
-            cur = out;
         }
+        if (phase == 1 || nfast == 0) break;
+        // ---------------- FAST path: [fast_lo, fast_hi], U steps per iteration ----------------
+        const int pmax = load_hi - 1, bmax = min(load_hi - 1, X - 2);  // prefetch clamps (never consumed)
+        VT pfp[U], pfb[U];
+        pfp[0] = nxt_p;
+        pfb[0] = nxt_b;
+#pragma unroll
+        for (int u = 1; u < U; ++u) {
+            pfp[u] = ld_ro<T, V>(pin + (long long)min(r + u, pmax) * g.pitch);
+            pfb[u] = ld_ro<T, V>(rin + (long long)min(r + u - 1, bmax) * g.pitch);
+        }
+        const int first_store = c0 + K;  // step at which level K reaches row c0
+#pragma unroll 1
+        for (; r <= fast_hi; r += U) {
+#pragma unroll
+            for (int u = 0; u < U; ++u) {
+                VT cur = pfp[u];
+                push_b(pfb[u]);
+                pfp[u] = ld_ro<T, V>(pin + (long long)min(r + u + U, pmax) * g.pitch);
+                pfb[u] = ld_ro<T, V>(rin + (long long)min(r + u + U - 1, bmax) * g.pitch);
+#pragma unroll
+                for (int t = 1; t <= K; ++t) {
+                    const VT out = jacobi_row<T, V>(w[t - 1][0], w[t - 1][1], cur, bw[t - 1]);
+                    w[t - 1][0] = w[t - 1][1];
+                    w[t - 1][1] = cur;
+                    cur = out;
+                }
+                if (st.st_ok && r + u >= first_store) st_vec<T, V>(pout + (long long)(r + u - K) * g.pitch, cur);
+            }
+        }
+        nxt_p = pfp[0];
+        nxt_b = pfb[0];
     }
 }
 
@@ -440,13 +533,14 @@ FB_DEV void predictor_task(const PredictorArgs<T>& A, int strip, int chunk, int 
                 us.a[0] = usp[(long long)ra * g.pitch];
                 vs.a[0] = vsp[(long long)ra * g.pitch];
             }
-            if (st.has_top && lane == st.top_lane) {
+            if (st.top_bits) {
+                const long long o = (long long)(ra - g.row0) * g.pitch + (Y - 1);
+                const T ue = A.us[o], ve = A.vs[o];
 #pragma unroll
-                for (int e = 0; e < V; ++e)
-                    if (e == st.top_e) {
-                        us.a[e] = usp[(long long)ra * g.pitch + e];
-                        vs.a[e] = vsp[(long long)ra * g.pitch + e];
-                    }
+                for (int e = 0; e < V; ++e) {
+                    us.a[e] = ((st.top_bits >> e) & 1u) ? ue : us.a[e];
+                    vs.a[e] = ((st.top_bits >> e) & 1u) ? ve : vs.a[e];
+                }
             }
             if (ra >= s0 && ra < s1 && st.st_ok) {
                 st_interior<T, V>(A.us + (long long)(ra - g.row0) * g.pitch, st.col0, Y, us);
@@ -495,20 +589,21 @@ FB_DEV void predictor_task(const PredictorArgs<T>& A, int strip, int chunk, int 
 //   old_wall   : this field's wall row BEFORE the step (unset bottom corner copies old [x][1])
 //   star_wall  : u_next's wall row (unset top corner copies u_next[x][Y-2], :246)
 template <typename T, int V, int H>
-FB_DEV_NOINLINE Vec<T, V> velocity_wall_row(const Edges<T>& e, int edge, int x,
-                                            const Vec<T, V>& inner_copy, const Vec<T, V>& old_wall,
-                                            const Vec<T, V>& star_wall, const Strip<V, H>& st,
-                                            int Y) {
+FB_DEV Vec<T, V> velocity_wall_row(const Edges<T>& e, int edge, int x, const Vec<T, V>& inner_copy,
+                                   const Vec<T, V>& old_wall, const Vec<T, V>& star_wall,
+                                   const Strip<V, H>& st, int Y) {
     Vec<T, V> r = wall_row<T, V>(e, edge, inner_copy, st.col0, Y);
     if (st.has_bottom) {
-        const T stale = old_wall.a[1];
-        if (st.lane == 0) r.a[0] = edge_value(e, BOTTOM, x, stale);
+        const EdgeCell<T> b = edge_cell(e, BOTTOM, x);
+        const T nv = b.use ? b.v : old_wall.a[1];
+        r.a[0] = (st.lane == 0) ? nv : r.a[0];
     }
     if (st.has_top) {
+        const EdgeCell<T> t = edge_cell(e, TOP, x);
         const T sv = pick<T, V>(star_wall, st.ym2_lane, st.ym2_e);
+        const T nv = t.use ? t.v : sv;
 #pragma unroll
-        for (int k = 0; k < V; ++k)
-            if (st.lane == st.top_lane && k == st.top_e) r.a[k] = edge_value(e, TOP, x, sv);
+        for (int k = 0; k < V; ++k) r.a[k] = ((st.top_bits >> k) & 1u) ? nv : r.a[k];
     }
     return r;
 }
@@ -583,19 +678,9 @@ FB_DEV void corrector_task(const CorrectorArgs<T>& A, int strip, int chunk, int 
                 }
             }
             // y-edges: bottom copies the corrected value (:239,:253), top copies u_next (:246,:260)
-            if (st.has_bottom && lane == 0) {
-                un.a[0] = edge_value(A.eu, BOTTOM, rr, un.a[1]);
-                vn.a[0] = edge_value(A.ev, BOTTOM, rr, vn.a[1]);
-            }
-            if (st.has_top) {
-                const T ubelow = shfl_up1(us.a[V - 1]);
-                const T vbelow = shfl_up1(vs.a[V - 1]);
-#pragma unroll
-                for (int e = 0; e < V; ++e)
-                    if (lane == st.top_lane && e == st.top_e) {
-                        un.a[e] = edge_value(A.eu, TOP, rr, (e > 0) ? us.a[e > 0 ? e - 1 : 0] : ubelow);
-                        vn.a[e] = edge_value(A.ev, TOP, rr, (e > 0) ? vs.a[e > 0 ? e - 1 : 0] : vbelow);
-                    }
+            if (st.has_bottom || st.has_top) {
+                apply_y_edges<T, V, H>(A.eu, st, rr, un, un, us);
+                apply_y_edges<T, V, H>(A.ev, st, rr, vn, vn, vs);
             }
             if (st.st_ok) {
                 st_vec<T, V>(up + (long long)rr * g.pitch, un);
