@@ -18,6 +18,7 @@ NUM_FIELDS = 7
 EDGE_UNSET, EDGE_CONST, EDGE_ARRAY = 0, 1, 2
 EDGE_BOTTOM, EDGE_TOP, EDGE_LEFT, EDGE_RIGHT = 0, 1, 2, 3
 MAX_SWEEPS_PER_LAUNCH = 8
+NOALLOC_MAX_BYTES = 16 << 20
 
 
 class Slab(C.Structure):
@@ -49,6 +50,7 @@ _SIGS = {
                                            C.POINTER(Mask), C.c_int, C.c_int, C.c_int, C.c_void_p]),
     "fluidb200_corrector": (C.c_int, [C.POINTER(Slab)] + [C.c_void_p] * 5 + [C.POINTER(Edges)] * 2 + [C.POINTER(Mask)] * 2
                             + [C.c_double] * 2 + [C.c_int] * 2 + [C.c_void_p]),
+    "fluidb200_poisson_solve_noalloc": (C.c_int, [C.POINTER(Slab), C.c_void_p, C.c_void_p, C.POINTER(Edges), C.c_int, C.c_void_p]),
     "fluidb200_init_cavity": (C.c_int, [C.POINTER(Slab)] + [C.c_void_p] * 7 + [C.c_double, C.c_void_p]),
     "fluidb200_cavity_edges": (C.c_int, [C.c_char, C.c_double, C.POINTER(Edges)]),
     "fluidb200_create": (C.c_int, [C.POINTER(C.c_void_p), C.c_int, C.c_int, C.c_int, C.c_double, C.c_double]),
@@ -71,6 +73,7 @@ _SIGS = {
     "fluidb200_launch_count": (C.c_int64, [C.c_void_p]),
     "fluidb200_set_device": (C.c_int, [C.c_int]),
     "fluidb200_last_error": (C.c_char_p, []),
+    "fluidb200_report_error": (C.c_int, [C.c_int, C.c_char_p]),
     "fluidb200_version": (C.c_char_p, []),
     "fluidb200_element_length": (C.c_double, [C.c_int, C.c_double, C.c_int]),
 }

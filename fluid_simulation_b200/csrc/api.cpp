@@ -710,5 +710,6 @@ extern "C" int fluidb200_set_device(int device) {
     BE_CHECK(fbk::be_set_device(device), "set_device");
     return 0;
 }
+extern "C" int fluidb200_report_error(int code, const char* message) { return fail(code, "%s", message ? message : ""); }
 extern "C" const char* fluidb200_last_error(void) { return g_err; }
 extern "C" const char* fluidb200_version(void) { return "fluidb200 0.1 (sm_100a)"; }

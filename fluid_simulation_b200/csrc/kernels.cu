@@ -174,3 +174,97 @@ INSTANTIATE(float)
 INSTANTIATE(double)
 
 }  // namespace fbk
+
+// =========================================================================================
+// Allocation-free Poisson entry point (see include/fluidb200.h for the user-facing contract)
+// =========================================================================================
+// The Jacobi sweeps ping-pong between two pressure buffers. Every other entry point gets the
+// second buffer from the caller or from cudaMalloc. Some callers can do neither: code running
+// while a memory pool is frozen or nearly exhausted, real-time loops that must not enter the
+// driver's allocator (cudaMalloc serialises against the whole device and may block for
+// milliseconds), and plug-in hosts that hand a library its input and output buffers and forbid
+// any allocation of its own. For them the partner buffer lives in this module's own image:
+// a file-scope __device__ array, reserved on every GPU that loads the library, for the life of
+// the process.
+#include "../../include/fluidb200.h"
+
+#include <mutex>
+
+static __device__ __align__(256) unsigned char g_noalloc_scratch[FLUIDB200_NOALLOC_MAX_BYTES];
+
+namespace {
+
+constexpr int kMaxDevices = 64;
+void* g_noalloc_ptr[kMaxDevices] = {};   // device address of g_noalloc_scratch, per device
+std::mutex g_noalloc_mutex;
+
+// In host code `g_noalloc_scratch` is only a handle for the symbol, not a device address; the
+// address a kernel may dereference has to be asked for, with the device in question current.
+int noalloc_scratch_for_current_device(void** out) {
+    int dev = -1;
+    if (rc_of(cudaGetDevice(&dev))) return -1;
+    if (dev < 0 || dev >= kMaxDevices) {
+        g_last = cudaErrorInvalidDevice;
+        return -1;
+    }
+    std::lock_guard<std::mutex> lock(g_noalloc_mutex);
+    if (!g_noalloc_ptr[dev]) {
+        void* p = nullptr;
+        if (rc_of(cudaGetSymbolAddress(&p, g_noalloc_scratch))) return -1;
+        g_noalloc_ptr[dev] = p;
+    }
+    *out = g_noalloc_ptr[dev];
+    return 0;
+}
+
+thread_local char g_noalloc_err[256];
+
+}  // namespace
+
+extern "C" int fluidb200_poisson_solve_noalloc(const fluidb200_slab* g, void* p, const void* rhs,
+                                               const fluidb200_edges* p_edges, int sweeps, void* stream) {
+    if (!g || !p || !rhs || !p_edges) return fluidb200_report_error(FLUIDB200_EINVAL, "poisson_solve_noalloc: NULL argument");
+    if (sweeps < 0) return fluidb200_report_error(FLUIDB200_EINVAL, "poisson_solve_noalloc: sweeps must be >= 0");
+    if (g->row0 != 0 || g->rows != g->X)
+        return fluidb200_report_error(FLUIDB200_EINVAL, "poisson_solve_noalloc: works on a whole grid (row0 = 0, rows = X)");
+    const size_t esize = g->dtype == FLUIDB200_F64 ? 8 : 4;
+    if (g->pitch <= 0 || g->rows <= 0) return fluidb200_report_error(FLUIDB200_EINVAL, "poisson_solve_noalloc: bad geometry");
+    const unsigned long long need = (unsigned long long)g->rows * (unsigned long long)g->pitch * esize;
+    if (need > (unsigned long long)FLUIDB200_NOALLOC_MAX_BYTES) {
+        snprintf(g_noalloc_err, sizeof(g_noalloc_err),
+                 "poisson_solve_noalloc: the grid needs %llu bytes of scratch (rows x pitch x element size) but the "
+                 "built-in scratch holds %llu; use fluidb200_poisson_sweeps with your own second buffer",
+                 need, (unsigned long long)FLUIDB200_NOALLOC_MAX_BYTES);
+        return fluidb200_report_error(FLUIDB200_EINVAL, g_noalloc_err);
+    }
+    if (sweeps == 0) return 0;
+    void* scratch = nullptr;
+    if (noalloc_scratch_for_current_device(&scratch)) {
+        snprintf(g_noalloc_err, sizeof(g_noalloc_err), "poisson_solve_noalloc: cannot resolve the scratch symbol: %s",
+                 cudaGetErrorString(g_last));
+        return fluidb200_report_error(FLUIDB200_ECUDA, g_noalloc_err);
+    }
+    // Split the sweeps into launches of at most 4, and into an EVEN number of launches when
+    // possible, so the ping-pong ends in the caller's buffer. A single sweep ends in the scratch
+    // and is copied back.
+    const int kmax = 4;
+    int nl = (sweeps + kmax - 1) / kmax;
+    if (sweeps >= 2 && (nl & 1)) ++nl;
+    void* src = p;
+    void* dst = scratch;
+    int left = sweeps;
+    for (int i = 0; i < nl; ++i) {
+        const int k = (left + (nl - i) - 1) / (nl - i);   // spread the sweeps evenly over the launches
+        const int rc = fluidb200_poisson_sweeps(g, src, dst, rhs, p_edges, nullptr, k, 0, g->X, stream);
+        if (rc) return rc;
+        left -= k;
+        void* t = src; src = dst; dst = t;
+    }
+    if (src != p) {  // odd number of launches (sweeps == 1): result sits in the scratch
+        if (rc_of(cudaMemcpyAsync(p, scratch, (size_t)need, cudaMemcpyDeviceToDevice, (cudaStream_t)stream))) {
+            snprintf(g_noalloc_err, sizeof(g_noalloc_err), "poisson_solve_noalloc: copy back failed: %s", cudaGetErrorString(g_last));
+            return fluidb200_report_error(FLUIDB200_ECUDA, g_noalloc_err);
+        }
+    }
+    return 0;
+}

@@ -158,6 +158,35 @@ int fluidb200_corrector(const fluidb200_slab* g, const void* p, const void* u_ne
                         const fluidb200_mask* v_mask, double dt, double rho, int out_lo,
                         int out_hi, void* stream);
 
+/* Jacobi sweeps IN PLACE on the caller's pressure field without allocating anything.
+ * No counterpart in the reference (its solver owns all of its memory and allocates it in the
+ * constructor); added for callers that cannot allocate device memory themselves and cannot let a
+ * library do it for them: code that runs after a memory pool has been frozen or filled, loops
+ * with a latency budget that a trip into the driver's allocator would break (cudaMalloc may
+ * block and synchronises the device), and hosts that pass a plug-in its buffers and forbid it
+ * any allocation of its own.
+ *
+ * Runs `sweeps` (any count >= 0) sweeps of fluidb200_poisson_sweeps' arithmetic on the whole grid
+ * (g->row0 must be 0 and g->rows == g->X) and leaves the result in `p`; `rhs` and `p_edges` as for
+ * fluidb200_poisson_sweeps; no interior mask. The second buffer Jacobi needs is a fixed array of
+ * FLUIDB200_NOALLOC_MAX_BYTES inside the library image: every GPU that loads the library holds
+ * those bytes until the process exits, whether or not this function is ever called.
+ *   - Limit: g->rows * g->pitch * sizeof(T) must not exceed FLUIDB200_NOALLOC_MAX_BYTES (16 MiB: a
+ *     2048 x 2048 fp32 or 2048 x 1024 fp64 grid). Larger grids are refused with FLUIDB200_EINVAL
+ *     and a message that says so; use fluidb200_poisson_sweeps with a buffer of your own.
+ *   - The function calls no cudaMalloc / cudaFree and no routine that allocates. The first call on
+ *     each device looks the array's device address up (one cudaGetSymbolAddress, with that device
+ *     current) and caches it; make that first call outside any stream capture.
+ *   - One array serves every call on a device and is not cleared between calls. Nothing needs to
+ *     start at zero: each launch writes every cell that a later launch of the same call reads for
+ *     a result, so leftovers of an earlier call (even of another grid size) cannot reach `p`.
+ *   - Because the array is shared, two calls whose kernels may run at the same time on one GPU
+ *     (different streams, different host threads) race on it. Serialise them.
+ * Asynchronous on `stream`, like the other launches. */
+#define FLUIDB200_NOALLOC_MAX_BYTES (16u << 20)
+int fluidb200_poisson_solve_noalloc(const fluidb200_slab* g, void* p, const void* rhs,
+                                    const fluidb200_edges* p_edges, int sweeps, void* stream);
+
 /* Device-side initialiser: zero state plus the lid-driven-cavity boundary values of
  * fluid_cpp/main.cpp:43-55 (lid u = lid_velocity for all x at y=Y-1 incl. corners, everything
  * else 0), without any host array. Fills the local rows of u, v, p, u_next, v_next, p_next, rhs
@@ -231,6 +260,9 @@ int64_t fluidb200_launch_count(const fluidb200_solver* s);
  * this library's own runtime instance). The reference never selects a device (single GPU). */
 int fluidb200_set_device(int device);
 const char* fluidb200_last_error(void);
+/* Record `message` as the calling thread's last error and return `code` (used by the parts of the
+ * library that live in other translation units; harmless for callers). */
+int fluidb200_report_error(int code, const char* message);
 const char* fluidb200_version(void);
 /* element_length = domain / (n - 1) evaluated in T (NavierStokesSolver.cpp:57-58). */
 double fluidb200_element_length(int dtype, double domain, int n);

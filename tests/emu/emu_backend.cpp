@@ -109,3 +109,9 @@ int launch_init_cavity(T* const f[7], long long pitch, int, int Y, int, int rows
 INSTANTIATE(float)
 INSTANTIATE(double)
 }  // namespace fbk
+
+// The allocation-free entry point needs a __device__ symbol; the host emulation has none.
+#include "../../include/fluidb200.h"
+extern "C" int fluidb200_poisson_solve_noalloc(const fluidb200_slab*, void*, const void*, const fluidb200_edges*, int, void*) {
+    return fluidb200_report_error(FLUIDB200_ESTATE, "poisson_solve_noalloc is not available in the host emulation");
+}
