@@ -165,6 +165,8 @@ def run_single(args):
     h = s._h
 
     def step(ev=None):
+        if ev is not None:
+            ev[2].record(stream)
         _lib.check(lib, lib.fluidb200_step_predictor(h))
         if ev is not None:
             ev[0].record(stream)
@@ -172,6 +174,8 @@ def run_single(args):
         if ev is not None:
             ev[1].record(stream)
         _lib.check(lib, lib.fluidb200_step_corrector(h))
+        if ev is not None:
+            ev[3].record(stream)
 
     for _ in range(max(args.warmup, 3)):
         step()
@@ -179,7 +183,7 @@ def run_single(args):
 
     clocks = ClockSampler(0).start()
     time.sleep(0.3)
-    phase_ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
+    phase_ev = [tuple(torch.cuda.Event(enable_timing=True) for _ in range(4)) for _ in range(args.steps)]
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     launches0 = s.launch_count()
     torch.cuda.synchronize()
@@ -191,7 +195,9 @@ def run_single(args):
     clk = clocks.stop()
     launches = s.launch_count() - launches0
     total_ms = e0.elapsed_time(e1)
-    jac_ms = sum(a.elapsed_time(b) for a, b in phase_ev)
+    jac_ms = sum(e[0].elapsed_time(e[1]) for e in phase_ev)
+    pred_ms = sum(e[2].elapsed_time(e[0]) for e in phase_ev) / args.steps
+    corr_ms = sum(e[1].elapsed_time(e[3]) for e in phase_ev) / args.steps
     cells = X * Y
     value = cells * args.steps / (total_ms * 1e-3) / 1e9
 
@@ -208,6 +214,8 @@ def run_single(args):
                 "launch_ms": jac_launch_ms, "algorithmic_bytes_per_launch": alg_bytes,
                 "gcell_sweeps_per_s": cells * SWEEPS * args.steps / (jac_ms * 1e-3) / 1e9,
                 "share_of_step": jac_ms / total_ms,
+                "other_kernels": {"predictor_ms": pred_ms, "predictor_GBps": 20.0 * cells / (pred_ms * 1e-3) / 1e9,
+                                  "corrector_ms": corr_ms, "corrector_GBps": 20.0 * cells / (corr_ms * 1e-3) / 1e9},
                 "note": "achieved = algorithmic bytes (12 B/cell/sweep x sweeps_per_launch) / launch time; with temporal "
                         "blocking the DRAM traffic per launch is ~12 B/cell, so frac > 1 is expected; see profiles/"}
 

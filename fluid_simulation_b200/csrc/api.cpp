@@ -49,15 +49,22 @@ template <typename T> int num_strips(int Y, int H) {
     return n < 1 ? 1 : n;
 }
 
-// Split `n` output rows into chunks. More chunks = more warps in flight, but every chunk
-// recomputes `halo` rows at each end. A chunk that touches a wall must hold >= 2 rows because
-// the wall row is derived while its neighbour row is produced.
-void plan_chunks(int n, int halo, int nstrips, int* rpc_out, int* nchunks_out) {
-    const long long target_tasks = env_int("FLUIDB200_TARGET_TASKS", 148 * 20 * 4);
+// Split `n` output rows into chunks. More chunks = more warps in flight and a smaller tail, but
+// every chunk recomputes `halo` rows at each end. The chunk count is chosen so that the grid is
+// (just under) a whole number of waves over the SMs: `ctas_per_sm` is the occupancy the kernel is
+// compiled for, and a partial last wave showed up as a 10-15 % loss at 16384^2. A chunk that
+// touches a wall must hold >= 2 rows because the wall row is derived while its neighbour row is
+// produced.
+void plan_chunks(int n, int halo, int nstrips, int ctas_per_sm, int* rpc_out, int* nchunks_out) {
+    const long long target_tasks = env_int("FLUIDB200_TARGET_TASKS", 148 * 16 * 10);
     int min_rpc = env_int("FLUIDB200_MIN_RPC", 0);
     if (min_rpc <= 0) min_rpc = std::max(8, 8 * halo);
-    long long want_chunks = (target_tasks + nstrips - 1) / nstrips;
-    if (want_chunks < 1) want_chunks = 1;
+    const long long ctas_x = (nstrips + fb::kWarpsPerCta - 1) / fb::kWarpsPerCta;
+    const long long slots = (long long)fbk::be_sm_count() * std::max(1, ctas_per_sm);
+    long long want_chunks = std::max(1LL, (target_tasks + nstrips - 1) / nstrips);
+    long long waves = std::max(1LL, (want_chunks * ctas_x + slots / 2) / slots);
+    long long aligned = (waves * slots) / ctas_x;  // chunks that fill `waves` waves exactly (rounded down)
+    if (aligned >= 1 && !env_int("FLUIDB200_NO_WAVE_ALIGN", 0)) want_chunks = aligned;
     int rpc = (int)((n + want_chunks - 1) / want_chunks);
     rpc = std::max(rpc, min_rpc);
     const int fixed = env_int("FLUIDB200_RPC", 0);
@@ -146,8 +153,7 @@ int predictor_t(const fluidb200_slab* g, const void* u, const void* v, void* us,
     fb::PredictorArgs<T> a;
     a.u = (const T*)u; a.v = (const T*)v;
     a.us = (T*)us; a.vs = (T*)vs; a.rhs = (T*)rhs;
-    a.hx = (T)g->hx; a.hy = (T)g->hy;
-    a.hx2 = (T)2 * a.hx; a.hy2 = (T)2 * a.hy;
+    a.m = fb::make_metric<T>((T)g->hx, (T)g->hy);
     a.nu = (T)nu; a.dt = (T)dt;
     a.rho_over_dt = (T)rho / (T)dt;  // (density / time_step) evaluated in T, SerialNavierStokes.cpp:332
     a.star_lo = star_lo; a.star_hi = star_hi; a.rhs_lo = rhs_lo; a.rhs_hi = rhs_hi;
@@ -155,7 +161,7 @@ int predictor_t(const fluidb200_slab* g, const void* u, const void* v, void* us,
     a.hi = std::max(star_hi, rhs_hi);
     const int nstrips = num_strips<T>(g->Y, 4);
     int rpc, nchunks;
-    plan_chunks(a.hi - a.lo, 2, nstrips, &rpc, &nchunks);
+    plan_chunks(a.hi - a.lo, 2, nstrips, 4, &rpc, &nchunks);
     a.g = make_geom(g, nstrips, rpc);
     BE_CHECK(fbk::launch_predictor<T>(a, nchunks, stream), "predictor launch");
     return 0;
@@ -175,7 +181,7 @@ int poisson_t(const fluidb200_slab* g, const void* p_in, void* p_out, const void
     a.e = to_dev_edges<T>(e);
     const int nstrips = num_strips<T>(g->Y, halo_cols(sweeps));
     int rpc, nchunks;
-    plan_chunks(out_hi - out_lo, sweeps, nstrips, &rpc, &nchunks);
+    plan_chunks(out_hi - out_lo, sweeps, nstrips, sweeps <= 2 ? 5 : sweeps <= 4 ? 4 : 2, &rpc, &nchunks);
     a.g = make_geom(g, nstrips, rpc);
     BE_CHECK(fbk::launch_jacobi<T>(a, sweeps, use_mask, nchunks, stream), "poisson launch");
     return 0;
@@ -191,15 +197,14 @@ int corrector_t(const fluidb200_slab* g, const void* p, const void* us, const vo
     const bool um = mu && mu->set, vm = mv && mv->set;
     a.uset = um ? mu->set : nullptr; a.uval = um ? (const T*)mu->val : nullptr;
     a.vset = vm ? mv->set : nullptr; a.vval = vm ? (const T*)mv->val : nullptr;
-    a.hx = (T)g->hx; a.hy = (T)g->hy;
-    a.hx2 = (T)2 * a.hx; a.hy2 = (T)2 * a.hy;
+    a.m = fb::make_metric<T>((T)g->hx, (T)g->hy);
     a.dt_over_rho = (T)dt / (T)rho;  // (time_step / density) in T, SerialNavierStokes.cpp:346
     a.out_lo = out_lo; a.out_hi = out_hi;
     a.eu = to_dev_edges<T>(eu);
     a.ev = to_dev_edges<T>(ev);
     const int nstrips = num_strips<T>(g->Y, 4);
     int rpc, nchunks;
-    plan_chunks(out_hi - out_lo, 1, nstrips, &rpc, &nchunks);
+    plan_chunks(out_hi - out_lo, 1, nstrips, 4, &rpc, &nchunks);
     a.g = make_geom(g, nstrips, rpc);
     BE_CHECK(fbk::launch_corrector<T>(a, um || vm, nchunks, stream), "corrector launch");
     return 0;

@@ -14,6 +14,7 @@ enum CopyKind { H2D = 0, D2H = 1, D2D = 2 };
 
 const char* backend_name();
 int be_set_device(int device);
+int be_sm_count();  // SMs of the current device (148 on B200)
 int be_malloc(void** p, size_t bytes);
 int be_free(void* p);
 int be_memset_async(void* p, int value, size_t bytes, void* stream);

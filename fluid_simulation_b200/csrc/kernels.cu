@@ -23,8 +23,13 @@ inline int rc_of(cudaError_t e) {
 
 constexpr int kThreads = fb::kWarpsPerCta * 32;
 
+// Resident CTAs per SM the register allocator must leave room for: the pipeline is latency bound
+// (ncu: ~50 % issue, ~50 % DRAM at 12 warps/SM), so shallow depths trade registers for warps.
+#ifndef FLUIDB200_JACOBI_MIN_BLOCKS
+#define FLUIDB200_JACOBI_MIN_BLOCKS(K) ((K) <= 2 ? 5 : (K) <= 4 ? 4 : (K) <= 6 ? 2 : 2)
+#endif
 template <typename T, int V, int K, bool MASK>
-__global__ void __launch_bounds__(kThreads) jacobi_kernel(const __grid_constant__ fb::JacobiArgs<T> A) {
+__global__ void __launch_bounds__(kThreads, FLUIDB200_JACOBI_MIN_BLOCKS(K)) jacobi_kernel(const __grid_constant__ fb::JacobiArgs<T> A) {
     const int strip = blockIdx.x * fb::kWarpsPerCta + (threadIdx.x >> 5);
     if (strip >= A.g.nstrips) return;  // whole warps only; the tasks use no block barrier
     fb::jacobi_task<T, V, K, MASK>(A, strip, blockIdx.y, threadIdx.x & 31);
@@ -79,6 +84,17 @@ namespace fbk {
 const char* backend_name() { return "cuda-sm_100a"; }
 const char* be_last_error_string() { return cudaGetErrorString(g_last); }
 int be_set_device(int device) { return rc_of(cudaSetDevice(device)); }
+int be_sm_count() {
+    static thread_local int cached_dev = -1, cached = 148;
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess) return 148;
+    if (dev != cached_dev) {
+        int n = 0;
+        if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) == cudaSuccess && n > 0) cached = n;
+        cached_dev = dev;
+    }
+    return cached;
+}
 
 int be_malloc(void** p, size_t bytes) { return rc_of(cudaMalloc(p, bytes)); }
 int be_free(void* p) { return rc_of(cudaFree(p)); }

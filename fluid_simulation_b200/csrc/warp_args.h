@@ -30,6 +30,23 @@ struct Geom {
     int rows_per_chunk;  // x rows written by one warp task
 };
 
+// Grid spacing as the kernels consume it. hx2 = 2*hx (exact). The three reciprocals are in
+// double and only feed the fp32 build's division-free fast path (see Ar<float> in
+// warp_kernels.cuh); hx*hy is exact in double (two 24-bit significands).
+template <typename T> struct Metric {
+    T hx, hy, hx2, hy2;
+    double inv_hx2, inv_hy2, inv_hxhy;
+};
+template <typename T> inline Metric<T> make_metric(T hx, T hy) {
+    Metric<T> m;
+    m.hx = hx; m.hy = hy;
+    m.hx2 = (T)2 * hx; m.hy2 = (T)2 * hy;
+    m.inv_hx2 = 1.0 / (double)m.hx2;
+    m.inv_hy2 = 1.0 / (double)m.hy2;
+    m.inv_hxhy = 1.0 / ((double)hx * (double)hy);
+    return m;
+}
+
 // Jacobi sweeps (see jacobi_task in warp_kernels.cuh)
 template <typename T> struct JacobiArgs {
     const T* p_in;
@@ -48,7 +65,7 @@ template <typename T> struct PredictorArgs {
     const T *u, *v;
     T *us, *vs, *rhs;     // u_next, v_next, right_hand_size
     Geom g;
-    T hx, hy, hx2, hy2;   // element lengths and their exact doubles
+    Metric<T> m;          // element lengths (+ exact doubles, reciprocals)
     T nu, dt, rho_over_dt;
     int lo, hi;           // chunked global row range = union of the two below
     int star_lo, star_hi; // rows of u_next/v_next to write
@@ -63,7 +80,7 @@ template <typename T> struct CorrectorArgs {
     const uint8_t *uset, *vset;  // interior flags (MASK build only)
     const T *uval, *vval;
     Geom g;
-    T hx, hy, hx2, hy2;
+    Metric<T> m;
     T dt_over_rho;
     int out_lo, out_hi;
     Edges<T> eu, ev;

@@ -46,25 +46,73 @@ namespace fb {
 // ---------------------------------------------------------------------------------------
 template <typename T> struct Ar;
 
+// Out-of-line exact paths of the fp32 arithmetic (rare; kept out of the hot loops' code).
+FB_DEV_NOINLINE float cdiff_exact_f32(float d, float h2) { return __fdiv_rn(d, h2); }
+FB_DEV_NOINLINE float lap_tail_exact_f32(float s, float c, float hx, float hy) {
+    double d = __fma_rn(-4.0, (double)c, (double)s);
+    d = __ddiv_rn(d, (double)hx);
+    d = __ddiv_rn(d, (double)hy);
+    return __double2float_rn(d);
+}
+
+// float -> double by integer repacking: exact for normal floats and (signed) zero; the caller
+// routes subnormal / inf / nan inputs to the exact path. Keeps the conversion off the XU pipe,
+// which the rounding double -> float conversions already load (ncu: XU was the busiest pipe of
+// the predictor when both directions used F2F).
+FB_DEV double f2d_normal(unsigned bits) {
+    const unsigned ab = bits & 0x7fffffffu;
+    const unsigned hi_n = (bits & 0x80000000u) | ((ab >> 3) + 0x38000000u);
+    const unsigned hi = (ab == 0u) ? bits : hi_n;
+    return __hiloint2double((int)hi, (int)(bits << 29));
+}
+// true for subnormal, inf and nan bit patterns (NOT for zero)
+FB_DEV bool f32_special(unsigned bits) {
+    const unsigned ab = bits & 0x7fffffffu;
+    return ab != 0u && (ab - 0x00800000u) >= 0x7f000000u;
+}
+
 template <> struct Ar<float> {
     static FB_DEV float add(float a, float b) { return __fadd_rn(a, b); }
     static FB_DEV float sub(float a, float b) { return __fsub_rn(a, b); }
     static FB_DEV float mul(float a, float b) { return __fmul_rn(a, b); }
     // (a - b) / 2. / h of the reference: float subtract, exact halving in double, one double
     // division, one rounding to float. 53 >= 2*24+2, so the double rounding is innocuous and
-    // the result equals the correctly rounded float quotient (a-b)/(2h); h2 = 2h is exact.
-    static FB_DEV float cdiff(float a, float b, float h, float h2) {
+    // the result equals the correctly rounded float quotient d/(2h), d = a-b; h2 = 2h is exact.
+    //
+    // Division-free evaluation: q~ = (double)d * RN64(1/h2) is within 2^-52 (relative) of d/h2,
+    // while the quotient of two 24-bit floats is never closer than ~2^-49 (relative) to a
+    // rounding boundary of a NORMAL float result, so RN32(q~) is the correctly rounded quotient.
+    // Results in or near the subnormal range (coarser, absolute rounding grid, exact ties are
+    // possible) and special inputs take the IEEE division. The cost is data independent, unlike
+    // __fdiv_rn whose slow path the mostly-zero fields of an impulsively started cavity hit all
+    // the time.
+    static FB_DEV float cdiff(float a, float b, float h, float h2, double inv_h2) {
         (void)h;
-        return __fdiv_rn(__fsub_rn(a, b), h2);
+        const float d = __fsub_rn(a, b);
+        const unsigned bits = __float_as_uint(d);
+        float r = __double2float_rn(__dmul_rn(f2d_normal(bits), inv_h2));
+        if (f32_special(bits) || ((bits << 1) != 0u && fabsf(r) < 7.52316385e-37f /* 2^-120 */)) r = cdiff_exact_f32(d, h2);
+        return r;
     }
     // (s - 4.*c) / hx / hy with s already rounded to float: the one place the fp32 path is
     // observably mixed precision (SerialNavierStokes.cpp:308-311). 4.*c is exact in double, so
-    // s - 4.*c is a single rounding == fma(-4, c, s).
-    static FB_DEV float lap_tail(float s, float c, float hx, float hy) {
-        double d = __fma_rn(-4.0, (double)c, (double)s);
-        d = __ddiv_rn(d, (double)hx);
-        d = __ddiv_rn(d, (double)hy);
-        return __double2float_rn(d);
+    // s - 4.*c is a single rounding == fma(-4, c, s). Reference value: RN32(T), T = RN64(RN64(d/hx)/hy).
+    //
+    // Division-free evaluation (Ziv's strategy): q~ = d * RN64(1/(hx*hy)) and T are both within
+    // 2^-52 (relative) of the exact quotient, hence within 4 ulp64 of each other; RN32(q~) = RN32(T)
+    // unless a float rounding boundary lies between them, i.e. unless the 29 bits of q~ below
+    // float precision are within a few units of the midpoint pattern. Those (about 1 in 2^24) and
+    // results near the subnormal range are recomputed with the two IEEE divisions.
+    static FB_DEV float lap_tail(float s, float c, float hx, float hy, double inv_hxhy) {
+        const unsigned sb = __float_as_uint(s), cb = __float_as_uint(c);
+        const double d = __fma_rn(-4.0, f2d_normal(cb), f2d_normal(sb));
+        const double q = __dmul_rn(d, inv_hxhy);
+        float r = __double2float_rn(q);
+        const unsigned low = (unsigned)__double2loint(q) & 0x1fffffffu;
+        const unsigned dist = (low > 0x10000000u) ? low - 0x10000000u : 0x10000000u - low;
+        if (dist <= 16u || f32_special(sb) || f32_special(cb) || (fabsf(r) < 7.52316385e-37f && d != 0.0))
+            r = lap_tail_exact_f32(s, c, hx, hy);
+        return r;
     }
     // t *= -0.25 : the double multiply is exact, so this is one float rounding (subnormals).
     static FB_DEV float neg_quarter(float t) { return __fmul_rn(t, -0.25f); }
@@ -74,11 +122,11 @@ template <> struct Ar<double> {
     static FB_DEV double add(double a, double b) { return __dadd_rn(a, b); }
     static FB_DEV double sub(double a, double b) { return __dsub_rn(a, b); }
     static FB_DEV double mul(double a, double b) { return __dmul_rn(a, b); }
-    static FB_DEV double cdiff(double a, double b, double h, double h2) {
+    static FB_DEV double cdiff(double a, double b, double h, double h2, double) {
         (void)h2;
         return __ddiv_rn(__dmul_rn(__dsub_rn(a, b), 0.5), h);  // "/ 2." is an exact halving
     }
-    static FB_DEV double lap_tail(double s, double c, double hx, double hy) {
+    static FB_DEV double lap_tail(double s, double c, double hx, double hy, double) {
         double d = __fma_rn(-4.0, c, s);  // 4.*c exact -> single rounding
         d = __ddiv_rn(d, hx);
         return __ddiv_rn(d, hy);
@@ -458,10 +506,56 @@ FB_DEV void jacobi_task(const JacobiArgs<T>& A, int strip, int chunk, int lane) 
 // (fluid_cpp/cuda/ParallelNavierStokes.cu:113-148, :150-170).
 // =========================================================================================
 
+// u_next, v_next of one interior row strip from rows x-1 (um,vm), x (u0,v0), x+1 (up,vp) of u, v
+// (SerialNavierStokes.cpp:298-322, operand order kept).
+template <typename T, int V>
+FB_DEV void tentative_row(const PredictorArgs<T>& A, const Vec<T, V>& um, const Vec<T, V>& u0, const Vec<T, V>& up_,
+                          const Vec<T, V>& vm, const Vec<T, V>& v0, const Vec<T, V>& vp_, Vec<T, V>& us, Vec<T, V>& vs) {
+    using A_ = Ar<T>;
+    Vec<T, V> uym, uyp, vym, vyp;
+    y_neighbours<T, V>(u0, uym, uyp);
+    y_neighbours<T, V>(v0, vym, vyp);
+#pragma unroll
+    for (int e = 0; e < V; ++e) {
+        const T uc = u0.a[e], vc = v0.a[e];
+        const T uxm = um.a[e], uxp = up_.a[e], vxm = vm.a[e], vxp = vp_.a[e];
+        const T du_dx = A_::cdiff(uxp, uxm, A.m.hx, A.m.hx2, A.m.inv_hx2);
+        const T dv_dx = A_::cdiff(vxp, vxm, A.m.hx, A.m.hx2, A.m.inv_hx2);
+        const T du_dy = A_::cdiff(uyp.a[e], uym.a[e], A.m.hy, A.m.hy2, A.m.inv_hy2);
+        const T dv_dy = A_::cdiff(vyp.a[e], vym.a[e], A.m.hy, A.m.hy2, A.m.inv_hy2);
+        const T su = A_::add(A_::add(A_::add(uxm, uxp), uyp.a[e]), uym.a[e]);
+        const T sv = A_::add(A_::add(A_::add(vxm, vxp), vyp.a[e]), vym.a[e]);
+        const T u_lap = A_::lap_tail(su, uc, A.m.hx, A.m.hy, A.m.inv_hxhy);
+        const T v_lap = A_::lap_tail(sv, vc, A.m.hx, A.m.hy, A.m.inv_hxhy);
+        const T du_dt = A_::sub(A_::sub(A_::mul(A.nu, u_lap), A_::mul(uc, du_dx)), A_::mul(vc, du_dy));
+        const T dv_dt = A_::sub(A_::sub(A_::mul(A.nu, v_lap), A_::mul(uc, dv_dx)), A_::mul(vc, dv_dy));
+        us.a[e] = A_::add(uc, A_::mul(A.dt, du_dt));
+        vs.a[e] = A_::add(vc, A_::mul(A.dt, dv_dt));
+    }
+}
+
+// right-hand side of one interior row from u_next rows x-1, x+1 and v_next row x
+// (SerialNavierStokes.cpp:325-335)
+template <typename T, int V>
+FB_DEV Vec<T, V> rhs_row(const PredictorArgs<T>& A, const Vec<T, V>& us_m, const Vec<T, V>& us_p, const Vec<T, V>& vs0) {
+    using A_ = Ar<T>;
+    Vec<T, V> vym, vyp, q;
+    y_neighbours<T, V>(vs0, vym, vyp);
+#pragma unroll
+    for (int e = 0; e < V; ++e) {
+        const T du_next_dx = A_::cdiff(us_p.a[e], us_m.a[e], A.m.hx, A.m.hx2, A.m.inv_hx2);
+        const T dv_next_dy = A_::cdiff(vyp.a[e], vym.a[e], A.m.hy, A.m.hy2, A.m.inv_hy2);
+        q.a[e] = A_::mul(A.rho_over_dt, A_::add(du_next_dx, dv_next_dy));
+    }
+    return q;
+}
+
+// Pipeline: step r loads row r of u, v; level A produces u_next, v_next of row r-1, level B the
+// right-hand side of row r-2 (it needs u_next of rows r-3 and r-1). Interior strips away from the
+// box walls take the FAST path (2 steps per iteration, no range checks).
 template <typename T, int V>
 FB_DEV void predictor_task(const PredictorArgs<T>& A, int strip, int chunk, int lane) {
     constexpr int H = 4;
-    using A_ = Ar<T>;
     using VT = Vec<T, V>;
     const Geom& g = A.g;
     const int X = g.X, Y = g.Y;
@@ -479,12 +573,11 @@ FB_DEV void predictor_task(const PredictorArgs<T>& A, int strip, int chunk, int 
     const int load_hi = min(c1 + 2, slab_hi);
     const int r_end = c1 + 1;
 
-    const long long base = (long long)st.col0 - (long long)g.row0 * g.pitch;
-    const T* up = A.u + base;
-    const T* vp = A.v + base;
-    T* usp = A.us + base;
-    T* vsp = A.vs + base;
-    T* rp = A.rhs + base;
+    const long long lbase = (long long)st.lcol - (long long)g.row0 * g.pitch;
+    const long long sbase = (long long)st.col0 - (long long)g.row0 * g.pitch;
+    const T* up = A.u + lbase;
+    const T* vp = A.v + lbase;
+    const bool y_edges = st.has_bottom || st.has_top;
 
     VT wu[2] = {vzero<T, V>(), vzero<T, V>()};   // u rows r-2, r-1
     VT wv[2] = {vzero<T, V>(), vzero<T, V>()};
@@ -492,88 +585,108 @@ FB_DEV void predictor_task(const PredictorArgs<T>& A, int strip, int chunk, int 
     VT wvs = vzero<T, V>();                      // v_next row r-2
 
     auto load = [&](const T* f, int r) -> VT {
-        if (st.ld_ok && r >= r_begin && r < load_hi) return ld_ro<T, V>(f + (long long)r * g.pitch);
+        if (r >= r_begin && r < load_hi) return ld_ro<T, V>(f + (long long)r * g.pitch);
         return vzero<T, V>();
     };
 
+    // fast steps: level A row r-1 in [1, X-2] and level B rows r-3, r-1 both computed interior rows
+    constexpr int U = 2;
+    const int fast_lo = max(r_begin, 4);
+    int nfast = min(r_end, X - 1) - fast_lo + 1;
+    if (y_edges || nfast < 0) nfast = 0;
+    nfast -= nfast % U;
+    const int fast_hi = fast_lo + nfast - 1;
+
     VT nu_ = load(up, r_begin), nv_ = load(vp, r_begin);
-    for (int r = r_begin; r <= r_end; ++r) {
-        const VT cu = nu_, cv = nv_;
-        nu_ = load(up, r + 1);
-        nv_ = load(vp, r + 1);
-
-        // ---- level A: u_next, v_next of row ra = r-1 (SerialNavierStokes.cpp:298-322)
-        const int ra = r - 1;
-        VT us = vzero<T, V>(), vs = vzero<T, V>();
-        if (ra >= 1 && ra <= X - 2) {
-            const VT u0 = wu[1], v0 = wv[1];
-            VT uym, uyp, vym, vyp;
-            y_neighbours<T, V>(u0, uym, uyp);
-            y_neighbours<T, V>(v0, vym, vyp);
-#pragma unroll
-            for (int e = 0; e < V; ++e) {
-                const T uc = u0.a[e], vc = v0.a[e];
-                const T uxm = wu[0].a[e], uxp = cu.a[e], vxm = wv[0].a[e], vxp = cv.a[e];
-                const T du_dx = A_::cdiff(uxp, uxm, A.hx, A.hx2);
-                const T dv_dx = A_::cdiff(vxp, vxm, A.hx, A.hx2);
-                const T du_dy = A_::cdiff(uyp.a[e], uym.a[e], A.hy, A.hy2);
-                const T dv_dy = A_::cdiff(vyp.a[e], vym.a[e], A.hy, A.hy2);
-                const T su = A_::add(A_::add(A_::add(uxm, uxp), uyp.a[e]), uym.a[e]);
-                const T sv = A_::add(A_::add(A_::add(vxm, vxp), vyp.a[e]), vym.a[e]);
-                const T u_lap = A_::lap_tail(su, uc, A.hx, A.hy);
-                const T v_lap = A_::lap_tail(sv, vc, A.hx, A.hy);
-                const T du_dt = A_::sub(A_::sub(A_::mul(A.nu, u_lap), A_::mul(uc, du_dx)), A_::mul(vc, du_dy));
-                const T dv_dt = A_::sub(A_::sub(A_::mul(A.nu, v_lap), A_::mul(uc, dv_dx)), A_::mul(vc, dv_dy));
-                us.a[e] = A_::add(uc, A_::mul(A.dt, du_dt));
-                vs.a[e] = A_::add(vc, A_::mul(A.dt, dv_dt));
-            }
-            // edge columns of u_next/v_next keep whatever is stored (never written by the
-            // reference); the right-hand side below reads them as y-neighbours
-            if (st.has_bottom && lane == 0) {
-                us.a[0] = usp[(long long)ra * g.pitch];
-                vs.a[0] = vsp[(long long)ra * g.pitch];
-            }
-            if (st.top_bits) {
-                const long long o = (long long)(ra - g.row0) * g.pitch + (Y - 1);
-                const T ue = A.us[o], ve = A.vs[o];
-#pragma unroll
-                for (int e = 0; e < V; ++e) {
-                    us.a[e] = ((st.top_bits >> e) & 1u) ? ue : us.a[e];
-                    vs.a[e] = ((st.top_bits >> e) & 1u) ? ve : vs.a[e];
+    int r = r_begin;
+#pragma unroll 1
+    for (int phase = 0; phase < 2; ++phase) {
+        const int gen_hi = (phase == 0 && nfast > 0) ? fast_lo - 1 : r_end;
+#pragma unroll 1
+        for (; r <= gen_hi; ++r) {
+            const VT cu = nu_, cv = nv_;
+            nu_ = load(up, r + 1);
+            nv_ = load(vp, r + 1);
+            // ---- level A: u_next, v_next of row ra = r-1
+            const int ra = r - 1;
+            VT us = vzero<T, V>(), vs = vzero<T, V>();
+            if (ra >= 1 && ra <= X - 2) {
+                tentative_row<T, V>(A, wu[0], wu[1], cu, wv[0], wv[1], cv, us, vs);
+                // edge columns of u_next/v_next keep whatever is stored (never written by the
+                // reference); the right-hand side below reads them as y-neighbours
+                const long long ro = (long long)(ra - g.row0) * g.pitch;
+                if (st.has_bottom) {
+                    const T ue = A.us[ro], ve = A.vs[ro];
+                    us.a[0] = (lane == 0) ? ue : us.a[0];
+                    vs.a[0] = (lane == 0) ? ve : vs.a[0];
                 }
-            }
-            if (ra >= s0 && ra < s1 && st.st_ok) {
-                st_interior<T, V>(A.us + (long long)(ra - g.row0) * g.pitch, st.col0, Y, us);
-                st_interior<T, V>(A.vs + (long long)(ra - g.row0) * g.pitch, st.col0, Y, vs);
-            }
-        } else if ((ra == 0 || ra == X - 1) && ra >= r_begin && ra < load_hi) {
-            // wall rows of u_next / v_next: stored values (x-neighbours of rows 1 and X-2)
-            if (st.ld_ok) {
-                us = ld_rw<T, V>(usp + (long long)ra * g.pitch);
-                vs = ld_rw<T, V>(vsp + (long long)ra * g.pitch);
-            }
-        }
-
-        // ---- level B: rhs of row rb = r-2 (SerialNavierStokes.cpp:325-335)
-        const int rb = r - 2;
-        if (rb >= 1 && rb <= X - 2) {
-            VT vym, vyp;
-            y_neighbours<T, V>(wvs, vym, vyp);
-            VT q;
+                if (st.has_top) {
+                    const T ue = A.us[ro + (Y - 1)], ve = A.vs[ro + (Y - 1)];
 #pragma unroll
-            for (int e = 0; e < V; ++e) {
-                const T du_next_dx = A_::cdiff(us.a[e], wus[0].a[e], A.hx, A.hx2);
-                const T dv_next_dy = A_::cdiff(vyp.a[e], vym.a[e], A.hy, A.hy2);
-                q.a[e] = A_::mul(A.rho_over_dt, A_::add(du_next_dx, dv_next_dy));
+                    for (int e = 0; e < V; ++e) {
+                        us.a[e] = ((st.top_bits >> e) & 1u) ? ue : us.a[e];
+                        vs.a[e] = ((st.top_bits >> e) & 1u) ? ve : vs.a[e];
+                    }
+                }
+                if (ra >= s0 && ra < s1 && st.st_ok) {
+                    st_interior<T, V>(A.us + ro, st.col0, Y, us);
+                    st_interior<T, V>(A.vs + ro, st.col0, Y, vs);
+                }
+            } else if ((ra == 0 || ra == X - 1) && ra >= r_begin && ra < load_hi) {
+                // wall rows of u_next / v_next: stored values (x-neighbours of rows 1 and X-2)
+                us = ld_rw<T, V>(A.us + lbase + (long long)ra * g.pitch);
+                vs = ld_rw<T, V>(A.vs + lbase + (long long)ra * g.pitch);
             }
-            if (rb >= b0 && rb < b1 && st.st_ok)
-                st_interior<T, V>(A.rhs + (long long)(rb - g.row0) * g.pitch, st.col0, Y, q);
+            // ---- level B: rhs of row rb = r-2
+            const int rb = r - 2;
+            if (rb >= 1 && rb <= X - 2) {
+                const VT q = rhs_row<T, V>(A, wus[0], us, wvs);
+                if (rb >= b0 && rb < b1 && st.st_ok)
+                    st_interior<T, V>(A.rhs + (long long)(rb - g.row0) * g.pitch, st.col0, Y, q);
+            }
+            wu[0] = wu[1]; wu[1] = cu;
+            wv[0] = wv[1]; wv[1] = cv;
+            wus[0] = wus[1]; wus[1] = us;
+            wvs = vs;
         }
-        (void)rp;
-        wu[0] = wu[1]; wu[1] = cu;
-        wv[0] = wv[1]; wv[1] = cv;
-        wus[0] = wus[1]; wus[1] = us;
-        wvs = vs;
+        if (phase == 1 || nfast == 0) break;
+        // ---------------- FAST path ----------------
+        const int pmax = load_hi - 1;
+        VT pfu[U], pfv[U];
+        pfu[0] = nu_;
+        pfv[0] = nv_;
+#pragma unroll
+        for (int k = 1; k < U; ++k) {
+            pfu[k] = ld_ro<T, V>(up + (long long)min(r + k, pmax) * g.pitch);
+            pfv[k] = ld_ro<T, V>(vp + (long long)min(r + k, pmax) * g.pitch);
+        }
+        T* uso = A.us + sbase;
+        T* vso = A.vs + sbase;
+        T* rho = A.rhs + sbase;
+#pragma unroll 1
+        for (; r <= fast_hi; r += U) {
+#pragma unroll
+            for (int k = 0; k < U; ++k) {
+                const VT cu = pfu[k], cv = pfv[k];
+                pfu[k] = ld_ro<T, V>(up + (long long)min(r + k + U, pmax) * g.pitch);
+                pfv[k] = ld_ro<T, V>(vp + (long long)min(r + k + U, pmax) * g.pitch);
+                VT us, vs;
+                tentative_row<T, V>(A, wu[0], wu[1], cu, wv[0], wv[1], cv, us, vs);
+                const int ra = r + k - 1, rb = r + k - 2;
+                if (st.st_ok && ra >= s0 && ra < s1) {
+                    st_vec<T, V>(uso + (long long)ra * g.pitch, us);
+                    st_vec<T, V>(vso + (long long)ra * g.pitch, vs);
+                }
+                const VT q = rhs_row<T, V>(A, wus[0], us, wvs);
+                if (st.st_ok && rb >= b0 && rb < b1) st_vec<T, V>(rho + (long long)rb * g.pitch, q);
+                wu[0] = wu[1]; wu[1] = cu;
+                wv[0] = wv[1]; wv[1] = cv;
+                wus[0] = wus[1]; wus[1] = us;
+                wvs = vs;
+            }
+        }
+        nu_ = pfu[0];
+        nv_ = pfv[0];
     }
 }
 
@@ -608,10 +721,26 @@ FB_DEV Vec<T, V> velocity_wall_row(const Edges<T>& e, int edge, int x, const Vec
     return r;
 }
 
+// corrected u, v of one interior row from p rows x-1 (pm), x (p0), x+1 (pp_) and u_next, v_next
+// (SerialNavierStokes.cpp:338-350)
+template <typename T, int V>
+FB_DEV void correct_row(const CorrectorArgs<T>& A, const Vec<T, V>& pm, const Vec<T, V>& p0, const Vec<T, V>& pp_,
+                        const Vec<T, V>& us, const Vec<T, V>& vs, Vec<T, V>& un, Vec<T, V>& vn) {
+    using A_ = Ar<T>;
+    Vec<T, V> pym, pyp;
+    y_neighbours<T, V>(p0, pym, pyp);
+#pragma unroll
+    for (int e = 0; e < V; ++e) {
+        const T dp_dx = A_::cdiff(pp_.a[e], pm.a[e], A.m.hx, A.m.hx2, A.m.inv_hx2);
+        const T dp_dy = A_::cdiff(pyp.a[e], pym.a[e], A.m.hy, A.m.hy2, A.m.inv_hy2);
+        un.a[e] = A_::sub(us.a[e], A_::mul(A.dt_over_rho, dp_dx));
+        vn.a[e] = A_::sub(vs.a[e], A_::mul(A.dt_over_rho, dp_dy));
+    }
+}
+
 template <typename T, int V, bool MASK>
 FB_DEV void corrector_task(const CorrectorArgs<T>& A, int strip, int chunk, int lane) {
     constexpr int H = 4;
-    using A_ = Ar<T>;
     using VT = Vec<T, V>;
     const Geom& g = A.g;
     const int X = g.X, Y = g.Y;
@@ -626,100 +755,130 @@ FB_DEV void corrector_task(const CorrectorArgs<T>& A, int strip, int chunk, int 
     const int load_hi = min(c1 + 1, slab_hi);
     const int r_end = c1;
 
-    const long long base = (long long)st.col0 - (long long)g.row0 * g.pitch;
-    const T* pp = A.p + base;
-    const T* usp = A.us + base;
-    const T* vsp = A.vs + base;
-    T* up = A.u + base;
-    T* vp = A.v + base;
+    const long long lbase = (long long)st.lcol - (long long)g.row0 * g.pitch;
+    const long long sbase = (long long)st.col0 - (long long)g.row0 * g.pitch;
+    const T* pp = A.p + lbase;
+    const T* usp = A.us + lbase;
+    const T* vsp = A.vs + lbase;
+    T* up = A.u + sbase;
+    T* vp = A.v + sbase;
+    const bool y_edges = st.has_bottom || st.has_top;
+    const int i_lo = max(c0, 1), i_hi = min(c1, X - 1);  // interior rows this task corrects: [i_lo, i_hi)
 
     VT wp[2] = {vzero<T, V>(), vzero<T, V>()};  // p rows r-2, r-1
 
     auto load = [&](const T* f, int r) -> VT {
-        if (st.ld_ok && r >= r_begin && r < load_hi) return ld_ro<T, V>(f + (long long)r * g.pitch);
+        if (r >= r_begin && r < load_hi) return ld_ro<T, V>(f + (long long)r * g.pitch);
         return vzero<T, V>();
     };
     auto load_star = [&](const T* f, int r) -> VT {  // u_next / v_next of an interior row
-        if (st.ld_ok && r >= max(c0, 1) && r < min(c1, X - 1)) return ld_ro<T, V>(f + (long long)r * g.pitch);
+        if (r >= i_lo && r < i_hi) return ld_ro<T, V>(f + (long long)r * g.pitch);
         return vzero<T, V>();
     };
 
+    // fast steps: row rr = r-1 in [i_lo, i_hi) and not next to a wall (rows 1 and X-2 also emit the
+    // boundary rows), interior strips, no interior flags
+    constexpr int U = 2;
+    const int fast_lo = max(max(i_lo, 2) + 1, r_begin + 2);
+    int nfast = min(i_hi - 1, X - 3) + 1 - fast_lo + 1;
+    if (MASK || y_edges || nfast < 0) nfast = 0;
+    nfast -= nfast % U;
+    const int fast_hi = fast_lo + nfast - 1;
+
     VT np_ = load(pp, r_begin);
     VT nus = load_star(usp, r_begin - 1), nvs = load_star(vsp, r_begin - 1);
-    for (int r = r_begin; r <= r_end; ++r) {
-        const VT cp = np_;
-        const VT us = nus, vs = nvs;
-        np_ = load(pp, r + 1);
-        nus = load_star(usp, r);
-        nvs = load_star(vsp, r);
-        const int rr = r - 1;
-        if (rr >= max(c0, 1) && rr < min(c1, X - 1)) {
-            VT pym, pyp;
-            y_neighbours<T, V>(wp[1], pym, pyp);
-            VT un, vn;
+    int r = r_begin;
+#pragma unroll 1
+    for (int phase = 0; phase < 2; ++phase) {
+        const int gen_hi = (phase == 0 && nfast > 0) ? fast_lo - 1 : r_end;
+#pragma unroll 1
+        for (; r <= gen_hi; ++r) {
+            const VT cp = np_;
+            const VT us = nus, vs = nvs;
+            np_ = load(pp, r + 1);
+            nus = load_star(usp, r);
+            nvs = load_star(vsp, r);
+            const int rr = r - 1;
+            if (rr >= i_lo && rr < i_hi) {
+                VT un, vn;
+                correct_row<T, V>(A, wp[0], wp[1], cp, us, vs, un, vn);
+                if (MASK) {  // interior flags (SerialNavierStokes.cpp:224-233)
+                    const long long off = (long long)(rr - g.row0) * g.pitch + st.col0;
+                    if (st.ld_ok) {
 #pragma unroll
-            for (int e = 0; e < V; ++e) {
-                const T dp_dx = A_::cdiff(cp.a[e], wp[0].a[e], A.hx, A.hx2);
-                const T dp_dy = A_::cdiff(pyp.a[e], pym.a[e], A.hy, A.hy2);
-                un.a[e] = A_::sub(us.a[e], A_::mul(A.dt_over_rho, dp_dx));
-                vn.a[e] = A_::sub(vs.a[e], A_::mul(A.dt_over_rho, dp_dy));
-            }
-            if (MASK) {  // interior flags (SerialNavierStokes.cpp:224-233)
-                const long long off = (long long)(rr - g.row0) * g.pitch + st.col0;
-                if (st.ld_ok) {
-#pragma unroll
-                    for (int e = 0; e < V; ++e) {
-                        const int col = st.col0 + e;
-                        if (col >= 1 && col <= Y - 2) {
-                            if (A.uset && A.uset[off + e]) un.a[e] = A.uval[off + e];
-                            if (A.vset && A.vset[off + e]) vn.a[e] = A.vval[off + e];
+                        for (int e = 0; e < V; ++e) {
+                            const int col = st.col0 + e;
+                            if (col >= 1 && col <= Y - 2) {
+                                if (A.uset && A.uset[off + e]) un.a[e] = A.uval[off + e];
+                                if (A.vset && A.vset[off + e]) vn.a[e] = A.vval[off + e];
+                            }
                         }
                     }
                 }
-            }
-            // y-edges: bottom copies the corrected value (:239,:253), top copies u_next (:246,:260)
-            if (st.has_bottom || st.has_top) {
-                apply_y_edges<T, V, H>(A.eu, st, rr, un, un, us);
-                apply_y_edges<T, V, H>(A.ev, st, rr, vn, vn, vs);
-            }
-            if (st.st_ok) {
-                st_vec<T, V>(up + (long long)rr * g.pitch, un);
-                st_vec<T, V>(vp + (long long)rr * g.pitch, vn);
-            }
-            if (rr == 1 && c0 == 0) {  // boundary row x = 0: unset cells copy u_next[1][y] (:269,:283)
-                VT ou = vzero<T, V>(), ov = ou, su = ou, sv = ou;
-                if (st.ld_ok) {
-                    ou = ld_rw<T, V>(up);
-                    ov = ld_rw<T, V>(vp);
-                    su = ld_rw<T, V>(usp);
-                    sv = ld_rw<T, V>(vsp);
+                // y-edges: bottom copies the corrected value (:239,:253), top copies u_next (:246,:260)
+                if (y_edges) {
+                    apply_y_edges<T, V, H>(A.eu, st, rr, un, un, us);
+                    apply_y_edges<T, V, H>(A.ev, st, rr, vn, vn, vs);
                 }
-                const VT wu_ = velocity_wall_row<T, V, H>(A.eu, LEFT, 0, us, ou, su, st, Y);
-                const VT wv_ = velocity_wall_row<T, V, H>(A.ev, LEFT, 0, vs, ov, sv, st, Y);
                 if (st.st_ok) {
-                    st_vec<T, V>(up, wu_);
-                    st_vec<T, V>(vp, wv_);
+                    st_vec<T, V>(up + (long long)rr * g.pitch, un);
+                    st_vec<T, V>(vp + (long long)rr * g.pitch, vn);
+                }
+                if (rr == 1 && c0 == 0) {  // boundary row x = 0: unset cells copy u_next[1][y] (:269,:283)
+                    const VT ou = ld_rw<T, V>(A.u + lbase), ov = ld_rw<T, V>(A.v + lbase);
+                    const VT su = ld_rw<T, V>(usp), sv = ld_rw<T, V>(vsp);
+                    const VT wu_ = velocity_wall_row<T, V, H>(A.eu, LEFT, 0, us, ou, su, st, Y);
+                    const VT wv_ = velocity_wall_row<T, V, H>(A.ev, LEFT, 0, vs, ov, sv, st, Y);
+                    if (st.st_ok) {
+                        st_vec<T, V>(up, wu_);
+                        st_vec<T, V>(vp, wv_);
+                    }
+                }
+                if (rr == X - 2 && c1 == X) {  // boundary row x = X-1: unset cells copy corrected u[X-2][y]
+                    const long long o = (long long)(X - 1) * g.pitch;
+                    const VT ou = ld_rw<T, V>(A.u + lbase + o), ov = ld_rw<T, V>(A.v + lbase + o);
+                    const VT su = ld_rw<T, V>(usp + o), sv = ld_rw<T, V>(vsp + o);
+                    const VT wu_ = velocity_wall_row<T, V, H>(A.eu, RIGHT, X - 1, un, ou, su, st, Y);
+                    const VT wv_ = velocity_wall_row<T, V, H>(A.ev, RIGHT, X - 1, vn, ov, sv, st, Y);
+                    if (st.st_ok) {
+                        st_vec<T, V>(up + o, wu_);
+                        st_vec<T, V>(vp + o, wv_);
+                    }
                 }
             }
-            if (rr == X - 2 && c1 == X) {  // boundary row x = X-1: unset cells copy corrected u[X-2][y]
-                const long long o = (long long)(X - 1) * g.pitch;
-                VT ou = vzero<T, V>(), ov = ou, su = ou, sv = ou;
-                if (st.ld_ok) {
-                    ou = ld_rw<T, V>(up + o);
-                    ov = ld_rw<T, V>(vp + o);
-                    su = ld_rw<T, V>(usp + o);
-                    sv = ld_rw<T, V>(vsp + o);
-                }
-                const VT wu_ = velocity_wall_row<T, V, H>(A.eu, RIGHT, X - 1, un, ou, su, st, Y);
-                const VT wv_ = velocity_wall_row<T, V, H>(A.ev, RIGHT, X - 1, vn, ov, sv, st, Y);
+            wp[0] = wp[1];
+            wp[1] = cp;
+        }
+        if (phase == 1 || nfast == 0) break;
+        // ---------------- FAST path: rows r-1 all plain interior rows of this task ----------------
+        const int pmax = load_hi - 1, smax = i_hi - 1;
+        VT pfp[U], pfu[U], pfv[U];
+        pfp[0] = np_; pfu[0] = nus; pfv[0] = nvs;
+#pragma unroll
+        for (int k = 1; k < U; ++k) {
+            pfp[k] = ld_ro<T, V>(pp + (long long)min(r + k, pmax) * g.pitch);
+            pfu[k] = ld_ro<T, V>(usp + (long long)min(r + k - 1, smax) * g.pitch);
+            pfv[k] = ld_ro<T, V>(vsp + (long long)min(r + k - 1, smax) * g.pitch);
+        }
+#pragma unroll 1
+        for (; r <= fast_hi; r += U) {
+#pragma unroll
+            for (int k = 0; k < U; ++k) {
+                const VT cp = pfp[k], us = pfu[k], vs = pfv[k];
+                pfp[k] = ld_ro<T, V>(pp + (long long)min(r + k + U, pmax) * g.pitch);
+                pfu[k] = ld_ro<T, V>(usp + (long long)min(r + k + U - 1, smax) * g.pitch);
+                pfv[k] = ld_ro<T, V>(vsp + (long long)min(r + k + U - 1, smax) * g.pitch);
+                VT un, vn;
+                correct_row<T, V>(A, wp[0], wp[1], cp, us, vs, un, vn);
                 if (st.st_ok) {
-                    st_vec<T, V>(up + o, wu_);
-                    st_vec<T, V>(vp + o, wv_);
+                    st_vec<T, V>(up + (long long)(r + k - 1) * g.pitch, un);
+                    st_vec<T, V>(vp + (long long)(r + k - 1) * g.pitch, vn);
                 }
+                wp[0] = wp[1];
+                wp[1] = cp;
             }
         }
-        wp[0] = wp[1];
-        wp[1] = cp;
+        np_ = pfp[0]; nus = pfu[0]; nvs = pfv[0];
     }
 }
 

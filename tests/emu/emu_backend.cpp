@@ -40,6 +40,7 @@ namespace fbk {
 const char* backend_name() { return "host-emulation (tests only)"; }
 const char* be_last_error_string() { return "host emulation error"; }
 int be_set_device(int) { return 0; }
+int be_sm_count() { return 148; }
 int be_malloc(void** p, size_t bytes) {
     *p = aligned_alloc(256, (bytes + 255) / 256 * 256);
     return *p ? 0 : -1;
@@ -114,4 +115,15 @@ INSTANTIATE(double)
 #include "../../include/fluidb200.h"
 extern "C" int fluidb200_poisson_solve_noalloc(const fluidb200_slab*, void*, const void*, const fluidb200_edges*, int, void*) {
     return fluidb200_report_error(FLUIDB200_ESTATE, "poisson_solve_noalloc is not available in the host emulation");
+}
+
+// Test hooks: the product's exact-rounding arithmetic (Ar<float>), element-wise, so that its
+// division-free fast paths can be hammered against the reference formulas in NumPy.
+extern "C" void emu_cdiff_f32(const float* a, const float* b, float h, long long n, float* out) {
+    const fb::Metric<float> m = fb::make_metric<float>(h, h);
+    for (long long i = 0; i < n; ++i) out[i] = fb::Ar<float>::cdiff(a[i], b[i], m.hx, m.hx2, m.inv_hx2);
+}
+extern "C" void emu_lap_tail_f32(const float* s, const float* c, float hx, float hy, long long n, float* out) {
+    const fb::Metric<float> m = fb::make_metric<float>(hx, hy);
+    for (long long i = 0; i < n; ++i) out[i] = fb::Ar<float>::lap_tail(s[i], c[i], m.hx, m.hy, m.inv_hxhy);
 }

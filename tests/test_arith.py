@@ -1,0 +1,89 @@
+"""CPU-only: the fp32 kernels replace the reference's divisions by a division-free fast path
+with an exact fallback (Ar<float>::cdiff / lap_tail in csrc/warp_kernels.cuh). This hammers them
+against the reference's own formulas evaluated in NumPy:
+
+  (a - b) / 2. / h                      SerialNavierStokes.cpp:302-305  (float sub, double divs, one float rounding)
+  (s - 4. * c) / hx / hy                SerialNavierStokes.cpp:309      (all double, one float rounding)
+
+with random magnitudes over the whole float range, subnormals, zeros of both signs, exact ties
+in the subnormal range, and spacings that are / are not powers of two."""
+import ctypes as C
+
+import numpy as np
+import pytest
+
+from tests import helpers as H
+
+
+@pytest.fixture(scope="module")
+def emu():
+    lib = C.CDLL(H.build_emu())
+    lib.emu_cdiff_f32.argtypes = [C.c_void_p, C.c_void_p, C.c_float, C.c_longlong, C.c_void_p]
+    lib.emu_lap_tail_f32.argtypes = [C.c_void_p, C.c_void_p, C.c_float, C.c_float, C.c_longlong, C.c_void_p]
+    return lib
+
+
+def _inputs(n, seed):
+    rng = np.random.default_rng(seed)
+    mant = rng.uniform(1.0, 2.0, n)
+    expo = rng.integers(-149, 60, n)
+    x = (mant * np.exp2(expo.astype(np.float64)) * rng.choice([-1.0, 1.0], n)).astype(np.float32)
+    x[rng.integers(0, n, n // 50)] = 0.0
+    x[rng.integers(0, n, n // 50)] = -0.0
+    sub = rng.integers(1, 1 << 23, n // 20).astype(np.uint32).view(np.float32)   # true subnormals
+    x[rng.integers(0, n, n // 20)] = sub
+    return x
+
+
+SPACINGS = [1.0, 0.5, 1.0 / 128, 1.0 / 99, 1.0 / 16383, 3.0, 0.1, 7.0 / 3, 1e-3, 123.456]
+
+
+@pytest.mark.parametrize("h", SPACINGS)
+def test_central_difference_matches_reference_formula(emu, h):
+    n = 400_000
+    a, b = _inputs(n, 1), _inputs(n, 2)
+    # near-cancelling pairs and tiny differences (subnormal quotients, exact ties for h = 3)
+    b[: n // 4] = a[: n // 4] * np.float32(1 + 2.0 ** -20)
+    k = np.arange(1, 2001, dtype=np.float64)
+    a[n // 2: n // 2 + 2000] = (k * 2.0 ** -149).astype(np.float32)
+    b[n // 2: n // 2 + 2000] = 0.0
+    h32 = np.float32(h)
+    out = np.empty(n, np.float32)
+    emu.emu_cdiff_f32(a.ctypes.data, b.ctypes.data, h32, n, out.ctypes.data)
+    with np.errstate(all="ignore"):
+        d = (a - b).astype(np.float32)
+        want = (d.astype(np.float64) / 2.0 / np.float64(h32)).astype(np.float32)
+    ok = (out.view(np.uint32) == want.view(np.uint32)) | (np.isnan(out) & np.isnan(want))
+    assert ok.all(), f"h={h}: {np.count_nonzero(~ok)} mismatches, first {a[~ok][:3]}, {b[~ok][:3]}"
+
+
+@pytest.mark.parametrize("hx,hy", [(1.0, 1.0), (1.0 / 99, 1.0 / 99), (1.0 / 16383, 1.0 / 16383), (0.1, 3.0),
+                                   (1.0 / 128, 1.0 / 40), (7.0 / 3, 1e-3)])
+def test_laplacian_tail_matches_reference_formula(emu, hx, hy):
+    n = 400_000
+    c = _inputs(n, 3)
+    s = (4.0 * c.astype(np.float64) * (1 + np.random.default_rng(4).normal(0, 1e-3, n))).astype(np.float32)
+    s[: n // 3] = _inputs(n // 3, 5)
+    hx32, hy32 = np.float32(hx), np.float32(hy)
+    out = np.empty(n, np.float32)
+    emu.emu_lap_tail_f32(s.ctypes.data, c.ctypes.data, hx32, hy32, n, out.ctypes.data)
+    with np.errstate(all="ignore"):
+        want = ((s.astype(np.float64) - 4.0 * c.astype(np.float64)) / np.float64(hx32) / np.float64(hy32)).astype(np.float32)
+    ok = (out.view(np.uint32) == want.view(np.uint32)) | (np.isnan(out) & np.isnan(want))
+    assert ok.all(), f"{np.count_nonzero(~ok)} mismatches"
+
+
+def test_laplacian_tail_ambiguous_cases_take_the_exact_path(emu):
+    """Construct quotients that land (nearly) on a float rounding boundary: d = m * hx * hy with m
+    a float midpoint, so only the exact two-division path rounds like the reference."""
+    rng = np.random.default_rng(7)
+    hx32, hy32 = np.float32(1.0 / 99), np.float32(1.0 / 57)
+    base = rng.uniform(1.0, 2.0, 20000).astype(np.float32)
+    mid = base.astype(np.float64) + 2.0 ** -24            # midpoints between adjacent floats in [1,2)
+    d = mid * np.float64(hx32) * np.float64(hy32)         # quotient ~ mid (up to double rounding)
+    c = np.zeros_like(base)
+    s = d.astype(np.float32)                               # d must come from floats: use c = 0, s = RN32(d)
+    out = np.empty(s.size, np.float32)
+    emu.emu_lap_tail_f32(s.ctypes.data, c.ctypes.data, hx32, hy32, s.size, out.ctypes.data)
+    want = (s.astype(np.float64) / np.float64(hx32) / np.float64(hy32)).astype(np.float32)
+    assert np.array_equal(out.view(np.uint32), want.view(np.uint32))

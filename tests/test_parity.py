@@ -149,3 +149,23 @@ def test_zero_iterations_are_noops(Solver):
     s.num_iterations = 0
     s.solve(); s.synchronize()
     s.close()
+
+
+@pytest.mark.parametrize("X,Y,K,kmax,dtype,rpc", [
+    (40, 300, 9, 4, "float32", 0), (40, 300, 17, 8, "float32", 0), (40, 300, 7, 3, "float32", 0),
+    (50, 300, 5, 4, "float32", 7), (40, 170, 5, 2, "float64", 0), (23, 300, 3, 1, "float32", 0),
+])
+def test_interior_strip_fast_paths(Solver, env, X, Y, K, kmax, dtype, rpc):
+    """Grids wide enough (>= 3 strips along y) that the register-pipelined fast paths of all three
+    kernels run (interior strips, rows away from the walls), next to the general path."""
+    if rpc:
+        env["FLUIDB200_RPC"] = str(rpc)
+    o = Oracle(X, Y, dtype=np.dtype(dtype)).set_cavity()
+    o.time_step, o.num_iterations, o.num_poisson_iterations = 1e-5, 2, K
+    s = Solver(X, Y, dtype=np.dtype(dtype)).set_cavity()
+    s.time_step, s.num_iterations, s.num_poisson_iterations = 1e-5, 2, K
+    s.set_sweeps_per_launch(kmax)
+    s.migrateSolve()
+    o.solve()
+    H.compare_with(s, o, tag=f"fast/{X}x{Y}/k{kmax}")
+    s.close()
