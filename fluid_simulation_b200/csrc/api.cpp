@@ -153,7 +153,7 @@ int predictor_t(const fluidb200_slab* g, const void* u, const void* v, void* us,
     fb::PredictorArgs<T> a;
     a.u = (const T*)u; a.v = (const T*)v;
     a.us = (T*)us; a.vs = (T*)vs; a.rhs = (T*)rhs;
-    a.m = fb::make_metric<T>((T)g->hx, (T)g->hy);
+    a.m = fb::make_metric<T>((T)g->hx, (T)g->hy, env_int("FLUIDB200_DIVMODE", -1));
     a.nu = (T)nu; a.dt = (T)dt;
     a.rho_over_dt = (T)rho / (T)dt;  // (density / time_step) evaluated in T, SerialNavierStokes.cpp:332
     a.star_lo = star_lo; a.star_hi = star_hi; a.rhs_lo = rhs_lo; a.rhs_hi = rhs_hi;
@@ -197,7 +197,7 @@ int corrector_t(const fluidb200_slab* g, const void* p, const void* us, const vo
     const bool um = mu && mu->set, vm = mv && mv->set;
     a.uset = um ? mu->set : nullptr; a.uval = um ? (const T*)mu->val : nullptr;
     a.vset = vm ? mv->set : nullptr; a.vval = vm ? (const T*)mv->val : nullptr;
-    a.m = fb::make_metric<T>((T)g->hx, (T)g->hy);
+    a.m = fb::make_metric<T>((T)g->hx, (T)g->hy, env_int("FLUIDB200_DIVMODE", -1));
     a.dt_over_rho = (T)dt / (T)rho;  // (time_step / density) in T, SerialNavierStokes.cpp:346
     a.out_lo = out_lo; a.out_hi = out_hi;
     a.eu = to_dev_edges<T>(eu);

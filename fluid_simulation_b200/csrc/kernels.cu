@@ -35,18 +35,18 @@ __global__ void __launch_bounds__(kThreads, FLUIDB200_JACOBI_MIN_BLOCKS(K)) jaco
     fb::jacobi_task<T, V, K, MASK>(A, strip, blockIdx.y, threadIdx.x & 31);
 }
 
-template <typename T, int V>
+template <typename T, int V, int MODE>
 __global__ void __launch_bounds__(kThreads) predictor_kernel(const __grid_constant__ fb::PredictorArgs<T> A) {
     const int strip = blockIdx.x * fb::kWarpsPerCta + (threadIdx.x >> 5);
     if (strip >= A.g.nstrips) return;
-    fb::predictor_task<T, V>(A, strip, blockIdx.y, threadIdx.x & 31);
+    fb::predictor_task<T, V, MODE>(A, strip, blockIdx.y, threadIdx.x & 31);
 }
 
-template <typename T, int V, bool MASK>
+template <typename T, int V, bool MASK, int MODE>
 __global__ void __launch_bounds__(kThreads) corrector_kernel(const __grid_constant__ fb::CorrectorArgs<T> A) {
     const int strip = blockIdx.x * fb::kWarpsPerCta + (threadIdx.x >> 5);
     if (strip >= A.g.nstrips) return;
-    fb::corrector_task<T, V, MASK>(A, strip, blockIdx.y, threadIdx.x & 31);
+    fb::corrector_task<T, V, MASK, MODE>(A, strip, blockIdx.y, threadIdx.x & 31);
 }
 
 template <typename T> struct FieldPtrs {
@@ -157,15 +157,26 @@ int launch_jacobi(const fb::JacobiArgs<T>& a, int sweeps, bool mask, int nchunks
 
 template <typename T> int launch_predictor(const fb::PredictorArgs<T>& a, int nchunks, void* stream) {
     constexpr int V = fb::VecWidth<T>::V;
-    predictor_kernel<T, V><<<grid_for(a.g.nstrips, nchunks), kThreads, 0, (cudaStream_t)stream>>>(a);
+    const dim3 grid = grid_for(a.g.nstrips, nchunks);
+    cudaStream_t st = (cudaStream_t)stream;
+    // the arithmetic mode is a compile-time property of the kernel (see Metric::mode); fp64 has only mode 0
+    if (sizeof(T) == 4 && a.m.mode == 2) predictor_kernel<T, V, (sizeof(T) == 4 ? 2 : 0)><<<grid, kThreads, 0, st>>>(a);
+    else if (sizeof(T) == 4 && a.m.mode == 1) predictor_kernel<T, V, (sizeof(T) == 4 ? 1 : 0)><<<grid, kThreads, 0, st>>>(a);
+    else predictor_kernel<T, V, 0><<<grid, kThreads, 0, st>>>(a);
     return rc_of(cudaGetLastError());
 }
 
 template <typename T> int launch_corrector(const fb::CorrectorArgs<T>& a, bool mask, int nchunks, void* stream) {
     constexpr int V = fb::VecWidth<T>::V;
     const dim3 grid = grid_for(a.g.nstrips, nchunks);
-    if (mask) corrector_kernel<T, V, true><<<grid, kThreads, 0, (cudaStream_t)stream>>>(a);
-    else corrector_kernel<T, V, false><<<grid, kThreads, 0, (cudaStream_t)stream>>>(a);
+    cudaStream_t st = (cudaStream_t)stream;
+    const int mode = sizeof(T) == 4 ? a.m.mode : 0;
+    if (mask) {  // the general-BC path is not specialised further
+        if (mode != 0) corrector_kernel<T, V, true, (sizeof(T) == 4 ? 1 : 0)><<<grid, kThreads, 0, st>>>(a);
+        else corrector_kernel<T, V, true, 0><<<grid, kThreads, 0, st>>>(a);
+    } else if (mode == 2) corrector_kernel<T, V, false, (sizeof(T) == 4 ? 2 : 0)><<<grid, kThreads, 0, st>>>(a);
+    else if (mode == 1) corrector_kernel<T, V, false, (sizeof(T) == 4 ? 1 : 0)><<<grid, kThreads, 0, st>>>(a);
+    else corrector_kernel<T, V, false, 0><<<grid, kThreads, 0, st>>>(a);
     return rc_of(cudaGetLastError());
 }
 

@@ -30,20 +30,38 @@ struct Geom {
     int rows_per_chunk;  // x rows written by one warp task
 };
 
-// Grid spacing as the kernels consume it. hx2 = 2*hx (exact). The three reciprocals are in
-// double and only feed the fp32 build's division-free fast path (see Ar<float> in
-// warp_kernels.cuh); hx*hy is exact in double (two 24-bit significands).
+// Grid spacing as the kernels consume it. hx2 = 2*hx (exact). The reciprocals feed the fp32
+// build's division-free arithmetic (see Ar<float> in warp_kernels.cuh); hx*hy is exact in double
+// (two 24-bit significands). `mode` selects that arithmetic: 0 = IEEE divisions (always valid,
+// the only mode of the fp64 build), 1 = division-free with flagged exact fallback, 2 = both
+// spacings are powers of two, divisions are exact scalings.
 template <typename T> struct Metric {
     T hx, hy, hx2, hy2;
     double inv_hx2, inv_hy2, inv_hxhy;
+    float inv_hx2f, inv_hy2f, inv_hxhyf;
+    int mode;
 };
-template <typename T> inline Metric<T> make_metric(T hx, T hy) {
+inline bool metric_is_pow2(double h) {
+    if (!(h > 0)) return false;
+    union { double d; unsigned long long u; } b;
+    b.d = h;
+    return (b.u & 0x000fffffffffffffULL) == 0;
+}
+template <typename T> inline Metric<T> make_metric(T hx, T hy, int forced_mode = -1) {
     Metric<T> m;
     m.hx = hx; m.hy = hy;
     m.hx2 = (T)2 * hx; m.hy2 = (T)2 * hy;
     m.inv_hx2 = 1.0 / (double)m.hx2;
     m.inv_hy2 = 1.0 / (double)m.hy2;
     m.inv_hxhy = 1.0 / ((double)hx * (double)hy);
+    m.inv_hx2f = (float)m.inv_hx2; m.inv_hy2f = (float)m.inv_hy2; m.inv_hxhyf = (float)m.inv_hxhy;
+    m.mode = 0;
+    if (sizeof(T) == 4) {
+        const double lo = 9.094947017729282e-13 /* 2^-40 */, hi = 1099511627776.0 /* 2^40 */;
+        const bool sane = (double)hx >= lo && (double)hx <= hi && (double)hy >= lo && (double)hy <= hi;
+        if (sane) m.mode = (metric_is_pow2((double)hx) && metric_is_pow2((double)hy)) ? 2 : 1;
+        if (forced_mode >= 0 && forced_mode < m.mode) m.mode = forced_mode;  // only ever towards "more exact"
+    }
     return m;
 }
 

@@ -46,19 +46,9 @@ namespace fb {
 // ---------------------------------------------------------------------------------------
 template <typename T> struct Ar;
 
-// Out-of-line exact paths of the fp32 arithmetic (rare; kept out of the hot loops' code).
-FB_DEV_NOINLINE float cdiff_exact_f32(float d, float h2) { return __fdiv_rn(d, h2); }
-FB_DEV_NOINLINE float lap_tail_exact_f32(float s, float c, float hx, float hy) {
-    double d = __fma_rn(-4.0, (double)c, (double)s);
-    d = __ddiv_rn(d, (double)hx);
-    d = __ddiv_rn(d, (double)hy);
-    return __double2float_rn(d);
-}
-
 // float -> double by integer repacking: exact for normal floats and (signed) zero; the caller
 // routes subnormal / inf / nan inputs to the exact path. Keeps the conversion off the XU pipe,
-// which the rounding double -> float conversions already load (ncu: XU was the busiest pipe of
-// the predictor when both directions used F2F).
+// which the rounding double -> float conversions already load.
 FB_DEV double f2d_normal(unsigned bits) {
     const unsigned ab = bits & 0x7fffffffu;
     const unsigned hi_n = (bits & 0x80000000u) | ((ab >> 3) + 0x38000000u);
@@ -71,6 +61,15 @@ FB_DEV bool f32_special(unsigned bits) {
     return ab != 0u && (ab - 0x00800000u) >= 0x7f000000u;
 }
 
+// The two divisions of the path come in three flavours, selected by MODE (Metric::mode):
+//   DIV_EXACT  the reference's operations literally (IEEE divisions);
+//   DIV_FAST   a division-free evaluation that is provably equal except for inputs it flags in
+//              `bad`; the caller recomputes a flagged row with DIV_EXACT. Flags are OR-ed, never
+//              branched on, so the ~40 independent chains of a row can overlap;
+//   DIV_POW2   hx and hy are powers of two (unit spacing, 2^k+1 points on a unit box, ...): every
+//              division is an exact scaling, i.e. one correctly rounded multiplication.
+enum { DIV_EXACT = 0, DIV_FAST = 1, DIV_POW2 = 2 };
+
 template <> struct Ar<float> {
     static FB_DEV float add(float a, float b) { return __fadd_rn(a, b); }
     static FB_DEV float sub(float a, float b) { return __fsub_rn(a, b); }
@@ -79,39 +78,59 @@ template <> struct Ar<float> {
     // division, one rounding to float. 53 >= 2*24+2, so the double rounding is innocuous and
     // the result equals the correctly rounded float quotient d/(2h), d = a-b; h2 = 2h is exact.
     //
-    // Division-free evaluation: q~ = (double)d * RN64(1/h2) is within 2^-52 (relative) of d/h2,
-    // while the quotient of two 24-bit floats is never closer than ~2^-49 (relative) to a
-    // rounding boundary of a NORMAL float result, so RN32(q~) is the correctly rounded quotient.
-    // Results in or near the subnormal range (coarser, absolute rounding grid, exact ties are
-    // possible) and special inputs take the IEEE division. The cost is data independent, unlike
-    // __fdiv_rn whose slow path the mostly-zero fields of an impulsively started cavity hit all
-    // the time.
-    static FB_DEV float cdiff(float a, float b, float h, float h2, double inv_h2) {
+    // DIV_FAST: q~ = (double)d * RN64(1/h2) is within 2^-52 (relative) of d/h2, while the quotient
+    // of two 24-bit floats is never closer than ~2^-49 (relative) to a rounding boundary of a
+    // NORMAL float result, so RN32(q~) is the correctly rounded quotient. Results in or near the
+    // subnormal range (coarser, absolute rounding grid; exact ties are possible) and special
+    // inputs are flagged. The cost is data independent, unlike __fdiv_rn whose slow path the
+    // mostly-zero fields of an impulsively started cavity hit all the time.
+    // DIV_POW2: d * (1/h2) is the same real number as d / h2 and is rounded once, like the division.
+    template <int MODE>
+    static FB_DEV float cdiff(float a, float b, float h, float h2, double inv_h2, float inv_h2f, bool& bad) {
         (void)h;
         const float d = __fsub_rn(a, b);
+        if (MODE == DIV_EXACT) return __fdiv_rn(d, h2);
+        if (MODE == DIV_POW2) return __fmul_rn(d, inv_h2f);
         const unsigned bits = __float_as_uint(d);
-        float r = __double2float_rn(__dmul_rn(f2d_normal(bits), inv_h2));
-        if (f32_special(bits) || ((bits << 1) != 0u && fabsf(r) < 7.52316385e-37f /* 2^-120 */)) r = cdiff_exact_f32(d, h2);
+        const float r = __double2float_rn(__dmul_rn(f2d_normal(bits), inv_h2));
+        bad |= f32_special(bits) || ((bits << 1) != 0u && fabsf(r) < 7.52316385e-37f /* 2^-120 */);
         return r;
     }
     // (s - 4.*c) / hx / hy with s already rounded to float: the one place the fp32 path is
     // observably mixed precision (SerialNavierStokes.cpp:308-311). 4.*c is exact in double, so
     // s - 4.*c is a single rounding == fma(-4, c, s). Reference value: RN32(T), T = RN64(RN64(d/hx)/hy).
     //
-    // Division-free evaluation (Ziv's strategy): q~ = d * RN64(1/(hx*hy)) and T are both within
-    // 2^-52 (relative) of the exact quotient, hence within 4 ulp64 of each other; RN32(q~) = RN32(T)
-    // unless a float rounding boundary lies between them, i.e. unless the 29 bits of q~ below
-    // float precision are within a few units of the midpoint pattern. Those (about 1 in 2^24) and
-    // results near the subnormal range are recomputed with the two IEEE divisions.
-    static FB_DEV float lap_tail(float s, float c, float hx, float hy, double inv_hxhy) {
+    // DIV_FAST (Ziv's strategy): q~ = d * RN64(1/(hx*hy)) and T are both within 2^-52 (relative) of
+    // the exact quotient, hence within 4 ulp64 of each other; RN32(q~) = RN32(T) unless a float
+    // rounding boundary lies between them, i.e. unless the 29 bits of q~ below float precision
+    // are within a few units of the midpoint pattern. Those (about 1 in 2^24), special inputs and
+    // results near the subnormal range are flagged.
+    // DIV_POW2: T = D * 2^k exactly with D = RN64(s - 4c), and for a normal result
+    // RN32(D * 2^k) = RN32(D) * 2^k = fmaf(-4, c, s) * 2^k (double rounding of a float sum is
+    // innocuous); values at the edge of the subnormal range are flagged.
+    template <int MODE>
+    static FB_DEV float lap_tail(float s, float c, float hx, float hy, double inv_hxhy, float inv_hxhyf, bool& bad) {
+        if (MODE == DIV_EXACT) {
+            double t = __fma_rn(-4.0, (double)c, (double)s);
+            t = __ddiv_rn(t, (double)hx);
+            t = __ddiv_rn(t, (double)hy);
+            return __double2float_rn(t);
+        }
+        if (MODE == DIV_POW2) {
+            const float t = __fmaf_rn(-4.0f, c, s);
+            const float r = __fmul_rn(t, inv_hxhyf);
+            // 2^-120 <= |t|, |r| <= 2^120, or t == 0  (one unsigned compare each on the exponent field)
+            const unsigned ta = __float_as_uint(t) & 0x7fffffffu, ra = __float_as_uint(r) & 0x7fffffffu;
+            bad |= (ta != 0u) && ((ta - 0x03800000u) >= 0x78000000u || (ra - 0x03800000u) >= 0x78000000u);
+            return r;
+        }
         const unsigned sb = __float_as_uint(s), cb = __float_as_uint(c);
         const double d = __fma_rn(-4.0, f2d_normal(cb), f2d_normal(sb));
         const double q = __dmul_rn(d, inv_hxhy);
-        float r = __double2float_rn(q);
+        const float r = __double2float_rn(q);
         const unsigned low = (unsigned)__double2loint(q) & 0x1fffffffu;
         const unsigned dist = (low > 0x10000000u) ? low - 0x10000000u : 0x10000000u - low;
-        if (dist <= 16u || f32_special(sb) || f32_special(cb) || (fabsf(r) < 7.52316385e-37f && d != 0.0))
-            r = lap_tail_exact_f32(s, c, hx, hy);
+        bad |= dist <= 16u || f32_special(sb) || f32_special(cb) || (fabsf(r) < 7.52316385e-37f && d != 0.0);
         return r;
     }
     // t *= -0.25 : the double multiply is exact, so this is one float rounding (subnormals).
@@ -122,11 +141,11 @@ template <> struct Ar<double> {
     static FB_DEV double add(double a, double b) { return __dadd_rn(a, b); }
     static FB_DEV double sub(double a, double b) { return __dsub_rn(a, b); }
     static FB_DEV double mul(double a, double b) { return __dmul_rn(a, b); }
-    static FB_DEV double cdiff(double a, double b, double h, double h2, double) {
+    template <int MODE> static FB_DEV double cdiff(double a, double b, double h, double h2, double, double, bool&) {
         (void)h2;
         return __ddiv_rn(__dmul_rn(__dsub_rn(a, b), 0.5), h);  // "/ 2." is an exact halving
     }
-    static FB_DEV double lap_tail(double s, double c, double hx, double hy, double) {
+    template <int MODE> static FB_DEV double lap_tail(double s, double c, double hx, double hy, double, double, bool&) {
         double d = __fma_rn(-4.0, c, s);  // 4.*c exact -> single rounding
         d = __ddiv_rn(d, hx);
         return __ddiv_rn(d, hy);
@@ -506,54 +525,109 @@ FB_DEV void jacobi_task(const JacobiArgs<T>& A, int strip, int chunk, int lane) 
 // (fluid_cpp/cuda/ParallelNavierStokes.cu:113-148, :150-170).
 // =========================================================================================
 
-// u_next, v_next of one interior row strip from rows x-1 (um,vm), x (u0,v0), x+1 (up,vp) of u, v
-// (SerialNavierStokes.cpp:298-322, operand order kept).
-template <typename T, int V>
+// A pair of results per cell (u and v component).
+template <typename T> struct UV {
+    T u, v;
+};
+
+// u_next, v_next of ONE interior cell from its own values (uc, vc) and its four neighbours in u
+// and v (SerialNavierStokes.cpp:298-322, operand order kept). All arguments are scalars so that
+// the out-of-line exact variant below gets them in registers: passing the row vectors by reference
+// would pin them to local memory in the hot loop.
+template <typename T, int MODE>
+FB_DEV UV<T> tentative_cell(const PredictorArgs<T>& A, T uc, T vc, T uxm, T uxp, T uym, T uyp, T vxm, T vxp, T vym,
+                            T vyp, bool& bad) {
+    using A_ = Ar<T>;
+    const T du_dx = A_::template cdiff<MODE>(uxp, uxm, A.m.hx, A.m.hx2, A.m.inv_hx2, A.m.inv_hx2f, bad);
+    const T dv_dx = A_::template cdiff<MODE>(vxp, vxm, A.m.hx, A.m.hx2, A.m.inv_hx2, A.m.inv_hx2f, bad);
+    const T du_dy = A_::template cdiff<MODE>(uyp, uym, A.m.hy, A.m.hy2, A.m.inv_hy2, A.m.inv_hy2f, bad);
+    const T dv_dy = A_::template cdiff<MODE>(vyp, vym, A.m.hy, A.m.hy2, A.m.inv_hy2, A.m.inv_hy2f, bad);
+    const T su = A_::add(A_::add(A_::add(uxm, uxp), uyp), uym);
+    const T sv = A_::add(A_::add(A_::add(vxm, vxp), vyp), vym);
+    const T u_lap = A_::template lap_tail<MODE>(su, uc, A.m.hx, A.m.hy, A.m.inv_hxhy, A.m.inv_hxhyf, bad);
+    const T v_lap = A_::template lap_tail<MODE>(sv, vc, A.m.hx, A.m.hy, A.m.inv_hxhy, A.m.inv_hxhyf, bad);
+    const T du_dt = A_::sub(A_::sub(A_::mul(A.nu, u_lap), A_::mul(uc, du_dx)), A_::mul(vc, du_dy));
+    const T dv_dt = A_::sub(A_::sub(A_::mul(A.nu, v_lap), A_::mul(uc, dv_dx)), A_::mul(vc, dv_dy));
+    UV<T> r;
+    r.u = A_::add(uc, A_::mul(A.dt, du_dt));
+    r.v = A_::add(vc, A_::mul(A.dt, dv_dt));
+    return r;
+}
+template <typename T>
+FB_DEV_NOINLINE UV<T> tentative_cell_exact(const PredictorArgs<T>& A, T uc, T vc, T uxm, T uxp, T uym, T uyp, T vxm,
+                                           T vxp, T vym, T vyp) {
+    bool bad = false;
+    return tentative_cell<T, DIV_EXACT>(A, uc, vc, uxm, uxp, uym, uyp, vxm, vxp, vym, vyp, bad);
+}
+
+// u_next, v_next of one interior row strip from rows x-1 (um,vm), x (u0,v0), x+1 (up,vp) of u, v.
+// All cells are first evaluated in MODE without branching; a cell the division-free arithmetic
+// flagged is then recomputed with IEEE divisions (per lane; the shuffles stay outside).
+template <typename T, int V, int MODE>
 FB_DEV void tentative_row(const PredictorArgs<T>& A, const Vec<T, V>& um, const Vec<T, V>& u0, const Vec<T, V>& up_,
                           const Vec<T, V>& vm, const Vec<T, V>& v0, const Vec<T, V>& vp_, Vec<T, V>& us, Vec<T, V>& vs) {
-    using A_ = Ar<T>;
     Vec<T, V> uym, uyp, vym, vyp;
     y_neighbours<T, V>(u0, uym, uyp);
     y_neighbours<T, V>(v0, vym, vyp);
+    bool bad[V];
 #pragma unroll
     for (int e = 0; e < V; ++e) {
-        const T uc = u0.a[e], vc = v0.a[e];
-        const T uxm = um.a[e], uxp = up_.a[e], vxm = vm.a[e], vxp = vp_.a[e];
-        const T du_dx = A_::cdiff(uxp, uxm, A.m.hx, A.m.hx2, A.m.inv_hx2);
-        const T dv_dx = A_::cdiff(vxp, vxm, A.m.hx, A.m.hx2, A.m.inv_hx2);
-        const T du_dy = A_::cdiff(uyp.a[e], uym.a[e], A.m.hy, A.m.hy2, A.m.inv_hy2);
-        const T dv_dy = A_::cdiff(vyp.a[e], vym.a[e], A.m.hy, A.m.hy2, A.m.inv_hy2);
-        const T su = A_::add(A_::add(A_::add(uxm, uxp), uyp.a[e]), uym.a[e]);
-        const T sv = A_::add(A_::add(A_::add(vxm, vxp), vyp.a[e]), vym.a[e]);
-        const T u_lap = A_::lap_tail(su, uc, A.m.hx, A.m.hy, A.m.inv_hxhy);
-        const T v_lap = A_::lap_tail(sv, vc, A.m.hx, A.m.hy, A.m.inv_hxhy);
-        const T du_dt = A_::sub(A_::sub(A_::mul(A.nu, u_lap), A_::mul(uc, du_dx)), A_::mul(vc, du_dy));
-        const T dv_dt = A_::sub(A_::sub(A_::mul(A.nu, v_lap), A_::mul(uc, dv_dx)), A_::mul(vc, dv_dy));
-        us.a[e] = A_::add(uc, A_::mul(A.dt, du_dt));
-        vs.a[e] = A_::add(vc, A_::mul(A.dt, dv_dt));
+        bad[e] = false;
+        const UV<T> r = tentative_cell<T, MODE>(A, u0.a[e], v0.a[e], um.a[e], up_.a[e], uym.a[e], uyp.a[e], vm.a[e],
+                                                vp_.a[e], vym.a[e], vyp.a[e], bad[e]);
+        us.a[e] = r.u;
+        vs.a[e] = r.v;
+    }
+    if (MODE != DIV_EXACT) {
+#pragma unroll
+        for (int e = 0; e < V; ++e) {
+            if (bad[e]) {
+                const UV<T> r = tentative_cell_exact<T>(A, u0.a[e], v0.a[e], um.a[e], up_.a[e], uym.a[e], uyp.a[e],
+                                                        vm.a[e], vp_.a[e], vym.a[e], vyp.a[e]);
+                us.a[e] = r.u;
+                vs.a[e] = r.v;
+            }
+        }
     }
 }
 
-// right-hand side of one interior row from u_next rows x-1, x+1 and v_next row x
+// right-hand side of one interior cell from u_next at x-1, x+1 and v_next at y-1, y+1
 // (SerialNavierStokes.cpp:325-335)
-template <typename T, int V>
-FB_DEV Vec<T, V> rhs_row(const PredictorArgs<T>& A, const Vec<T, V>& us_m, const Vec<T, V>& us_p, const Vec<T, V>& vs0) {
+template <typename T, int MODE>
+FB_DEV T rhs_cell(const PredictorArgs<T>& A, T us_m, T us_p, T vs_ym, T vs_yp, bool& bad) {
     using A_ = Ar<T>;
+    const T du_next_dx = A_::template cdiff<MODE>(us_p, us_m, A.m.hx, A.m.hx2, A.m.inv_hx2, A.m.inv_hx2f, bad);
+    const T dv_next_dy = A_::template cdiff<MODE>(vs_yp, vs_ym, A.m.hy, A.m.hy2, A.m.inv_hy2, A.m.inv_hy2f, bad);
+    return A_::mul(A.rho_over_dt, A_::add(du_next_dx, dv_next_dy));
+}
+template <typename T>
+FB_DEV_NOINLINE T rhs_cell_exact(const PredictorArgs<T>& A, T us_m, T us_p, T vs_ym, T vs_yp) {
+    bool bad = false;
+    return rhs_cell<T, DIV_EXACT>(A, us_m, us_p, vs_ym, vs_yp, bad);
+}
+template <typename T, int V, int MODE>
+FB_DEV Vec<T, V> rhs_row(const PredictorArgs<T>& A, const Vec<T, V>& us_m, const Vec<T, V>& us_p, const Vec<T, V>& vs0) {
     Vec<T, V> vym, vyp, q;
     y_neighbours<T, V>(vs0, vym, vyp);
+    bool bad[V];
 #pragma unroll
     for (int e = 0; e < V; ++e) {
-        const T du_next_dx = A_::cdiff(us_p.a[e], us_m.a[e], A.m.hx, A.m.hx2, A.m.inv_hx2);
-        const T dv_next_dy = A_::cdiff(vyp.a[e], vym.a[e], A.m.hy, A.m.hy2, A.m.inv_hy2);
-        q.a[e] = A_::mul(A.rho_over_dt, A_::add(du_next_dx, dv_next_dy));
+        bad[e] = false;
+        q.a[e] = rhs_cell<T, MODE>(A, us_m.a[e], us_p.a[e], vym.a[e], vyp.a[e], bad[e]);
+    }
+    if (MODE != DIV_EXACT) {
+#pragma unroll
+        for (int e = 0; e < V; ++e)
+            if (bad[e]) q.a[e] = rhs_cell_exact<T>(A, us_m.a[e], us_p.a[e], vym.a[e], vyp.a[e]);
     }
     return q;
 }
 
+
 // Pipeline: step r loads row r of u, v; level A produces u_next, v_next of row r-1, level B the
 // right-hand side of row r-2 (it needs u_next of rows r-3 and r-1). Interior strips away from the
 // box walls take the FAST path (2 steps per iteration, no range checks).
-template <typename T, int V>
+template <typename T, int V, int MODE>
 FB_DEV void predictor_task(const PredictorArgs<T>& A, int strip, int chunk, int lane) {
     constexpr int H = 4;
     using VT = Vec<T, V>;
@@ -611,7 +685,7 @@ FB_DEV void predictor_task(const PredictorArgs<T>& A, int strip, int chunk, int 
             const int ra = r - 1;
             VT us = vzero<T, V>(), vs = vzero<T, V>();
             if (ra >= 1 && ra <= X - 2) {
-                tentative_row<T, V>(A, wu[0], wu[1], cu, wv[0], wv[1], cv, us, vs);
+                tentative_row<T, V, MODE>(A, wu[0], wu[1], cu, wv[0], wv[1], cv, us, vs);
                 // edge columns of u_next/v_next keep whatever is stored (never written by the
                 // reference); the right-hand side below reads them as y-neighbours
                 const long long ro = (long long)(ra - g.row0) * g.pitch;
@@ -640,7 +714,7 @@ FB_DEV void predictor_task(const PredictorArgs<T>& A, int strip, int chunk, int 
             // ---- level B: rhs of row rb = r-2
             const int rb = r - 2;
             if (rb >= 1 && rb <= X - 2) {
-                const VT q = rhs_row<T, V>(A, wus[0], us, wvs);
+                const VT q = rhs_row<T, V, MODE>(A, wus[0], us, wvs);
                 if (rb >= b0 && rb < b1 && st.st_ok)
                     st_interior<T, V>(A.rhs + (long long)(rb - g.row0) * g.pitch, st.col0, Y, q);
             }
@@ -671,13 +745,13 @@ FB_DEV void predictor_task(const PredictorArgs<T>& A, int strip, int chunk, int 
                 pfu[k] = ld_ro<T, V>(up + (long long)min(r + k + U, pmax) * g.pitch);
                 pfv[k] = ld_ro<T, V>(vp + (long long)min(r + k + U, pmax) * g.pitch);
                 VT us, vs;
-                tentative_row<T, V>(A, wu[0], wu[1], cu, wv[0], wv[1], cv, us, vs);
+                tentative_row<T, V, MODE>(A, wu[0], wu[1], cu, wv[0], wv[1], cv, us, vs);
                 const int ra = r + k - 1, rb = r + k - 2;
                 if (st.st_ok && ra >= s0 && ra < s1) {
                     st_vec<T, V>(uso + (long long)ra * g.pitch, us);
                     st_vec<T, V>(vso + (long long)ra * g.pitch, vs);
                 }
-                const VT q = rhs_row<T, V>(A, wus[0], us, wvs);
+                const VT q = rhs_row<T, V, MODE>(A, wus[0], us, wvs);
                 if (st.st_ok && rb >= b0 && rb < b1) st_vec<T, V>(rho + (long long)rb * g.pitch, q);
                 wu[0] = wu[1]; wu[1] = cu;
                 wv[0] = wv[1]; wv[1] = cv;
@@ -721,24 +795,50 @@ FB_DEV Vec<T, V> velocity_wall_row(const Edges<T>& e, int edge, int x, const Vec
     return r;
 }
 
-// corrected u, v of one interior row from p rows x-1 (pm), x (p0), x+1 (pp_) and u_next, v_next
+// corrected u, v of one interior cell from p at x-1, x+1, y-1, y+1 and u_next, v_next
 // (SerialNavierStokes.cpp:338-350)
-template <typename T, int V>
+template <typename T, int MODE>
+FB_DEV UV<T> correct_cell(const CorrectorArgs<T>& A, T pxm, T pxp, T pym, T pyp, T us, T vs, bool& bad) {
+    using A_ = Ar<T>;
+    const T dp_dx = A_::template cdiff<MODE>(pxp, pxm, A.m.hx, A.m.hx2, A.m.inv_hx2, A.m.inv_hx2f, bad);
+    const T dp_dy = A_::template cdiff<MODE>(pyp, pym, A.m.hy, A.m.hy2, A.m.inv_hy2, A.m.inv_hy2f, bad);
+    UV<T> r;
+    r.u = A_::sub(us, A_::mul(A.dt_over_rho, dp_dx));
+    r.v = A_::sub(vs, A_::mul(A.dt_over_rho, dp_dy));
+    return r;
+}
+template <typename T>
+FB_DEV_NOINLINE UV<T> correct_cell_exact(const CorrectorArgs<T>& A, T pxm, T pxp, T pym, T pyp, T us, T vs) {
+    bool bad = false;
+    return correct_cell<T, DIV_EXACT>(A, pxm, pxp, pym, pyp, us, vs, bad);
+}
+template <typename T, int V, int MODE>
 FB_DEV void correct_row(const CorrectorArgs<T>& A, const Vec<T, V>& pm, const Vec<T, V>& p0, const Vec<T, V>& pp_,
                         const Vec<T, V>& us, const Vec<T, V>& vs, Vec<T, V>& un, Vec<T, V>& vn) {
-    using A_ = Ar<T>;
     Vec<T, V> pym, pyp;
     y_neighbours<T, V>(p0, pym, pyp);
+    bool bad[V];
 #pragma unroll
     for (int e = 0; e < V; ++e) {
-        const T dp_dx = A_::cdiff(pp_.a[e], pm.a[e], A.m.hx, A.m.hx2, A.m.inv_hx2);
-        const T dp_dy = A_::cdiff(pyp.a[e], pym.a[e], A.m.hy, A.m.hy2, A.m.inv_hy2);
-        un.a[e] = A_::sub(us.a[e], A_::mul(A.dt_over_rho, dp_dx));
-        vn.a[e] = A_::sub(vs.a[e], A_::mul(A.dt_over_rho, dp_dy));
+        bad[e] = false;
+        const UV<T> r = correct_cell<T, MODE>(A, pm.a[e], pp_.a[e], pym.a[e], pyp.a[e], us.a[e], vs.a[e], bad[e]);
+        un.a[e] = r.u;
+        vn.a[e] = r.v;
+    }
+    if (MODE != DIV_EXACT) {
+#pragma unroll
+        for (int e = 0; e < V; ++e) {
+            if (bad[e]) {
+                const UV<T> r = correct_cell_exact<T>(A, pm.a[e], pp_.a[e], pym.a[e], pyp.a[e], us.a[e], vs.a[e]);
+                un.a[e] = r.u;
+                vn.a[e] = r.v;
+            }
+        }
     }
 }
 
-template <typename T, int V, bool MASK>
+
+template <typename T, int V, bool MASK, int MODE>
 FB_DEV void corrector_task(const CorrectorArgs<T>& A, int strip, int chunk, int lane) {
     constexpr int H = 4;
     using VT = Vec<T, V>;
@@ -801,7 +901,7 @@ FB_DEV void corrector_task(const CorrectorArgs<T>& A, int strip, int chunk, int 
             const int rr = r - 1;
             if (rr >= i_lo && rr < i_hi) {
                 VT un, vn;
-                correct_row<T, V>(A, wp[0], wp[1], cp, us, vs, un, vn);
+                correct_row<T, V, MODE>(A, wp[0], wp[1], cp, us, vs, un, vn);
                 if (MASK) {  // interior flags (SerialNavierStokes.cpp:224-233)
                     const long long off = (long long)(rr - g.row0) * g.pitch + st.col0;
                     if (st.ld_ok) {
@@ -869,7 +969,7 @@ FB_DEV void corrector_task(const CorrectorArgs<T>& A, int strip, int chunk, int 
                 pfu[k] = ld_ro<T, V>(usp + (long long)min(r + k + U - 1, smax) * g.pitch);
                 pfv[k] = ld_ro<T, V>(vsp + (long long)min(r + k + U - 1, smax) * g.pitch);
                 VT un, vn;
-                correct_row<T, V>(A, wp[0], wp[1], cp, us, vs, un, vn);
+                correct_row<T, V, MODE>(A, wp[0], wp[1], cp, us, vs, un, vn);
                 if (st.st_ok) {
                     st_vec<T, V>(up + (long long)(r + k - 1) * g.pitch, un);
                     st_vec<T, V>(vp + (long long)(r + k - 1) * g.pitch, vn);

@@ -84,13 +84,21 @@ template <typename T> int launch_jacobi(const fb::JacobiArgs<T>& a, int sweeps, 
 }
 template <typename T> int launch_predictor(const fb::PredictorArgs<T>& a, int nchunks, void*) {
     constexpr int V = fb::VecWidth<T>::V;
-    run_grid(a.g.nstrips, nchunks, [&](int s, int c, int l) { fb::predictor_task<T, V>(a, s, c, l); });
+    const int mode = sizeof(T) == 4 ? a.m.mode : 0;
+    if (mode == 2) run_grid(a.g.nstrips, nchunks, [&](int s, int c, int l) { fb::predictor_task<T, V, (sizeof(T) == 4 ? 2 : 0)>(a, s, c, l); });
+    else if (mode == 1) run_grid(a.g.nstrips, nchunks, [&](int s, int c, int l) { fb::predictor_task<T, V, (sizeof(T) == 4 ? 1 : 0)>(a, s, c, l); });
+    else run_grid(a.g.nstrips, nchunks, [&](int s, int c, int l) { fb::predictor_task<T, V, 0>(a, s, c, l); });
     return 0;
 }
 template <typename T> int launch_corrector(const fb::CorrectorArgs<T>& a, bool mask, int nchunks, void*) {
     constexpr int V = fb::VecWidth<T>::V;
-    if (mask) run_grid(a.g.nstrips, nchunks, [&](int s, int c, int l) { fb::corrector_task<T, V, true>(a, s, c, l); });
-    else run_grid(a.g.nstrips, nchunks, [&](int s, int c, int l) { fb::corrector_task<T, V, false>(a, s, c, l); });
+    const int mode = sizeof(T) == 4 ? a.m.mode : 0;
+    if (mask) {
+        if (mode != 0) run_grid(a.g.nstrips, nchunks, [&](int s, int c, int l) { fb::corrector_task<T, V, true, (sizeof(T) == 4 ? 1 : 0)>(a, s, c, l); });
+        else run_grid(a.g.nstrips, nchunks, [&](int s, int c, int l) { fb::corrector_task<T, V, true, 0>(a, s, c, l); });
+    } else if (mode == 2) run_grid(a.g.nstrips, nchunks, [&](int s, int c, int l) { fb::corrector_task<T, V, false, (sizeof(T) == 4 ? 2 : 0)>(a, s, c, l); });
+    else if (mode == 1) run_grid(a.g.nstrips, nchunks, [&](int s, int c, int l) { fb::corrector_task<T, V, false, (sizeof(T) == 4 ? 1 : 0)>(a, s, c, l); });
+    else run_grid(a.g.nstrips, nchunks, [&](int s, int c, int l) { fb::corrector_task<T, V, false, 0>(a, s, c, l); });
     return 0;
 }
 template <typename T>
@@ -118,12 +126,28 @@ extern "C" int fluidb200_poisson_solve_noalloc(const fluidb200_slab*, void*, con
 }
 
 // Test hooks: the product's exact-rounding arithmetic (Ar<float>), element-wise, so that its
-// division-free fast paths can be hammered against the reference formulas in NumPy.
-extern "C" void emu_cdiff_f32(const float* a, const float* b, float h, long long n, float* out) {
+// division-free modes can be hammered against the reference formulas in NumPy. A flagged
+// element is recomputed in DIV_EXACT, like the kernels do per row.
+template <int MODE> static void cdiff_hook(const float* a, const float* b, float h, long long n, float* out) {
     const fb::Metric<float> m = fb::make_metric<float>(h, h);
-    for (long long i = 0; i < n; ++i) out[i] = fb::Ar<float>::cdiff(a[i], b[i], m.hx, m.hx2, m.inv_hx2);
+    for (long long i = 0; i < n; ++i) {
+        bool bad = false;
+        out[i] = fb::Ar<float>::cdiff<MODE>(a[i], b[i], m.hx, m.hx2, m.inv_hx2, m.inv_hx2f, bad);
+        if (bad) out[i] = fb::Ar<float>::cdiff<fb::DIV_EXACT>(a[i], b[i], m.hx, m.hx2, m.inv_hx2, m.inv_hx2f, bad);
+    }
 }
-extern "C" void emu_lap_tail_f32(const float* s, const float* c, float hx, float hy, long long n, float* out) {
+template <int MODE> static void lap_hook(const float* s, const float* c, float hx, float hy, long long n, float* out) {
     const fb::Metric<float> m = fb::make_metric<float>(hx, hy);
-    for (long long i = 0; i < n; ++i) out[i] = fb::Ar<float>::lap_tail(s[i], c[i], m.hx, m.hy, m.inv_hxhy);
+    for (long long i = 0; i < n; ++i) {
+        bool bad = false;
+        out[i] = fb::Ar<float>::lap_tail<MODE>(s[i], c[i], m.hx, m.hy, m.inv_hxhy, m.inv_hxhyf, bad);
+        if (bad) out[i] = fb::Ar<float>::lap_tail<fb::DIV_EXACT>(s[i], c[i], m.hx, m.hy, m.inv_hxhy, m.inv_hxhyf, bad);
+    }
+}
+extern "C" int emu_metric_mode_f32(float hx, float hy) { return fb::make_metric<float>(hx, hy).mode; }
+extern "C" void emu_cdiff_f32(int mode, const float* a, const float* b, float h, long long n, float* out) {
+    if (mode == 2) cdiff_hook<2>(a, b, h, n, out); else if (mode == 1) cdiff_hook<1>(a, b, h, n, out); else cdiff_hook<0>(a, b, h, n, out);
+}
+extern "C" void emu_lap_tail_f32(int mode, const float* s, const float* c, float hx, float hy, long long n, float* out) {
+    if (mode == 2) lap_hook<2>(s, c, hx, hy, n, out); else if (mode == 1) lap_hook<1>(s, c, hx, hy, n, out); else lap_hook<0>(s, c, hx, hy, n, out);
 }

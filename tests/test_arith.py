@@ -18,8 +18,9 @@ from tests import helpers as H
 @pytest.fixture(scope="module")
 def emu():
     lib = C.CDLL(H.build_emu())
-    lib.emu_cdiff_f32.argtypes = [C.c_void_p, C.c_void_p, C.c_float, C.c_longlong, C.c_void_p]
-    lib.emu_lap_tail_f32.argtypes = [C.c_void_p, C.c_void_p, C.c_float, C.c_float, C.c_longlong, C.c_void_p]
+    lib.emu_cdiff_f32.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_float, C.c_longlong, C.c_void_p]
+    lib.emu_lap_tail_f32.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_float, C.c_float, C.c_longlong, C.c_void_p]
+    lib.emu_metric_mode_f32.argtypes = [C.c_float, C.c_float]
     return lib
 
 
@@ -48,29 +49,34 @@ def test_central_difference_matches_reference_formula(emu, h):
     a[n // 2: n // 2 + 2000] = (k * 2.0 ** -149).astype(np.float32)
     b[n // 2: n // 2 + 2000] = 0.0
     h32 = np.float32(h)
-    out = np.empty(n, np.float32)
-    emu.emu_cdiff_f32(a.ctypes.data, b.ctypes.data, h32, n, out.ctypes.data)
     with np.errstate(all="ignore"):
         d = (a - b).astype(np.float32)
         want = (d.astype(np.float64) / 2.0 / np.float64(h32)).astype(np.float32)
-    ok = (out.view(np.uint32) == want.view(np.uint32)) | (np.isnan(out) & np.isnan(want))
-    assert ok.all(), f"h={h}: {np.count_nonzero(~ok)} mismatches, first {a[~ok][:3]}, {b[~ok][:3]}"
+    best = emu.emu_metric_mode_f32(h32, h32)     # the mode the product would pick for this spacing
+    assert best == (2 if h in (1.0, 0.5, 1.0 / 128) else 1)
+    for mode in range(best + 1):                 # ... and every more conservative one
+        out = np.empty(n, np.float32)
+        emu.emu_cdiff_f32(mode, a.ctypes.data, b.ctypes.data, h32, n, out.ctypes.data)
+        ok = (out.view(np.uint32) == want.view(np.uint32)) | (np.isnan(out) & np.isnan(want))
+        assert ok.all(), f"h={h} mode {mode}: {np.count_nonzero(~ok)} mismatches, first {a[~ok][:3]}, {b[~ok][:3]}"
 
 
 @pytest.mark.parametrize("hx,hy", [(1.0, 1.0), (1.0 / 99, 1.0 / 99), (1.0 / 16383, 1.0 / 16383), (0.1, 3.0),
-                                   (1.0 / 128, 1.0 / 40), (7.0 / 3, 1e-3)])
+                                   (1.0 / 128, 1.0 / 40), (7.0 / 3, 1e-3), (1.0 / 128, 1.0 / 256), (4.0, 0.25),
+                                   (2.0 ** -30, 2.0 ** -30), (2.0 ** 20, 2.0 ** 20)])
 def test_laplacian_tail_matches_reference_formula(emu, hx, hy):
     n = 400_000
     c = _inputs(n, 3)
     s = (4.0 * c.astype(np.float64) * (1 + np.random.default_rng(4).normal(0, 1e-3, n))).astype(np.float32)
     s[: n // 3] = _inputs(n // 3, 5)
     hx32, hy32 = np.float32(hx), np.float32(hy)
-    out = np.empty(n, np.float32)
-    emu.emu_lap_tail_f32(s.ctypes.data, c.ctypes.data, hx32, hy32, n, out.ctypes.data)
     with np.errstate(all="ignore"):
         want = ((s.astype(np.float64) - 4.0 * c.astype(np.float64)) / np.float64(hx32) / np.float64(hy32)).astype(np.float32)
-    ok = (out.view(np.uint32) == want.view(np.uint32)) | (np.isnan(out) & np.isnan(want))
-    assert ok.all(), f"{np.count_nonzero(~ok)} mismatches"
+    for mode in range(emu.emu_metric_mode_f32(hx32, hy32) + 1):
+        out = np.empty(n, np.float32)
+        emu.emu_lap_tail_f32(mode, s.ctypes.data, c.ctypes.data, hx32, hy32, n, out.ctypes.data)
+        ok = (out.view(np.uint32) == want.view(np.uint32)) | (np.isnan(out) & np.isnan(want))
+        assert ok.all(), f"mode {mode}: {np.count_nonzero(~ok)} mismatches, e.g. s={s[~ok][:3]} c={c[~ok][:3]}"
 
 
 def test_laplacian_tail_ambiguous_cases_take_the_exact_path(emu):
@@ -84,6 +90,6 @@ def test_laplacian_tail_ambiguous_cases_take_the_exact_path(emu):
     c = np.zeros_like(base)
     s = d.astype(np.float32)                               # d must come from floats: use c = 0, s = RN32(d)
     out = np.empty(s.size, np.float32)
-    emu.emu_lap_tail_f32(s.ctypes.data, c.ctypes.data, hx32, hy32, s.size, out.ctypes.data)
+    emu.emu_lap_tail_f32(1, s.ctypes.data, c.ctypes.data, hx32, hy32, s.size, out.ctypes.data)
     want = (s.astype(np.float64) / np.float64(hx32) / np.float64(hy32)).astype(np.float32)
     assert np.array_equal(out.view(np.uint32), want.view(np.uint32))

@@ -169,3 +169,38 @@ def test_interior_strip_fast_paths(Solver, env, X, Y, K, kmax, dtype, rpc):
     o.solve()
     H.compare_with(s, o, tag=f"fast/{X}x{Y}/k{kmax}")
     s.close()
+
+
+def test_subnormal_front_takes_exact_fallback(Solver):
+    """A tiny diffusion number makes the values at the advancing front underflow through the
+    subnormal range (the reference runs on x86 without flush-to-zero). The fp32 kernels' division-
+    free arithmetic flags those inputs and recomputes the affected rows with IEEE divisions, inside
+    a per-lane branch: this must neither change bits nor deadlock on a warp shuffle."""
+    X, Y, S, K = 40, 300, 9, 2
+    o = Oracle(X, Y).set_cavity()
+    o.time_step, o.num_iterations, o.num_poisson_iterations = 1e-9, S, K
+    s = Solver(X, Y).set_cavity()
+    s.time_step, s.num_iterations, s.num_poisson_iterations = 1e-9, S, K
+    s.migrateSolve()
+    o.solve()
+    tiny = np.finfo(np.float32).tiny
+    assert np.any((np.abs(o.u_next) < tiny) & (o.u_next != 0)), "case no longer produces subnormals"
+    H.compare_with(s, o, tag="subnormal-front")
+    s.close()
+
+
+@pytest.mark.parametrize("X,Y,divmode", [(33, 257, None), (33, 257, 1), (33, 257, 0), (40, 300, 0), (40, 300, 1)])
+def test_division_modes_agree_with_the_reference(Solver, env, X, Y, divmode):
+    """fp32 arithmetic modes of the predictor/corrector (Metric::mode): 2 = power-of-two spacing
+    (33 x 257 points on the unit box), 1 = division-free with flagged exact fallback, 0 = IEEE
+    divisions. FLUIDB200_DIVMODE can only force a more conservative mode."""
+    if divmode is not None:
+        env["FLUIDB200_DIVMODE"] = str(divmode)
+    o = Oracle(X, Y).set_cavity()
+    o.time_step, o.num_iterations, o.num_poisson_iterations = 2e-5, 3, 5
+    s = Solver(X, Y).set_cavity()
+    s.time_step, s.num_iterations, s.num_poisson_iterations = 2e-5, 3, 5
+    s.migrateSolve()
+    o.solve()
+    H.compare_with(s, o, tag=f"divmode{divmode}/{X}x{Y}")
+    s.close()
