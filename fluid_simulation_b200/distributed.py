@@ -1,0 +1,340 @@
+"""Multi-GPU driver: the grid is cut into x-slabs, one process (rank) per GPU.
+
+The reference has no multi-device path at all (no NCCL/MPI/cudaSetDevice anywhere, SURVEY.md
+section 2.2); this is new work on top of the same kernels. Because the pressure solve is true Jacobi
+(``SerialNavierStokes.cpp:140-198``) and every kernel here reproduces the serial arithmetic bit for
+bit, the sharded result is bit-identical to the single-GPU one -- which is the correctness test.
+
+Layout. Row ``x`` is ``pitch`` contiguous elements, so a slab ``[x0, x1)`` is one contiguous range
+and a halo "line" is one contiguous run of ``pitch`` elements. Every rank stores its owned rows
+plus ``H = kmax + 1`` halo rows per interior side; both y-edges (floor, lid) exist on every rank,
+the x = 0 / x = X-1 walls only on the first / last rank, so all boundary rules stay rank-local.
+
+Per timestep, with ``m = ceil(K / kmax)`` Jacobi launches of depth ``k <= kmax``:
+
+  1. exchange u, v halos (depth kmax+1)                                     [1 exchange]
+  2. predictor: u*, v* on owned +- kmax rows, rhs on owned +- (kmax-1) rows  (recomputed, not sent)
+  3. m x { k sweeps on the two k-row edge strips of the owned range -> start sending them;
+           k sweeps on the interior of the owned range, overlapping the transfer;
+           wait for the neighbours' strips }                                 [m exchanges]
+  4. corrector on the owned rows (p halo of depth 1 is already there)
+
+Only point-to-point transfers between neighbours are needed (``torch.distributed`` isend/irecv:
+NCCL over NVLink on GPUs, gloo on CPU for the tests); there is no reduction anywhere because the
+iteration count is fixed. On CPU the "device" library is tests/emu's host build of the same C ABI
+(test infrastructure), selected explicitly by the caller; the product path has no CPU fallback.
+"""
+from __future__ import annotations
+
+import ctypes as C
+
+import numpy as np
+
+from . import _lib
+
+_FIELDS = ("u", "v", "p", "u_next", "v_next", "p_next", "rhs")
+
+
+def slab_bounds(X, world, rank):
+    """Owned rows [x0, x1) of `rank`: contiguous, sizes differ by at most one row."""
+    return (rank * X) // world, ((rank + 1) * X) // world
+
+
+class SlabSolver:
+    """One rank's slab of a lid-driven cavity (boundary set-up of fluid_cpp/main.cpp:43-55)."""
+
+    def __init__(self, X, Y, domain_x, domain_y, dtype=np.float32, *, rank=0, world=1, group=None,
+                 device="cuda", kmax=4, libpath=None, overlap=True):
+        import torch
+        self.torch = torch
+        self.dist = torch.distributed if world > 1 else None
+        self.group = group
+        self.X, self.Y, self.rank, self.world = int(X), int(Y), int(rank), int(world)
+        self.npdt = np.dtype(dtype)
+        self.tdt = torch.float32 if self.npdt == np.float32 else torch.float64
+        self.device = torch.device(device)
+        self.on_gpu = self.device.type == "cuda"
+        self.lib = _lib.load(libpath)
+        if self.on_gpu:
+            _lib.check(self.lib, self.lib.fluidb200_set_device(self.device.index or 0))
+        self.kmax = int(kmax)
+        self.overlap = bool(overlap) and self.on_gpu
+        self.x0, self.x1 = slab_bounds(self.X, self.world, self.rank)
+        self.H = self.kmax + 1
+        if world > 1 and (self.x1 - self.x0) < 2 * self.H:
+            raise ValueError(f"slab of {self.x1 - self.x0} rows is too thin for halo depth {self.H}")
+        self.lo, self.hi = max(0, self.x0 - self.H), min(self.X, self.x1 + self.H)
+        self.rows = self.hi - self.lo
+        self.pitch = (self.Y + 31) // 32 * 32
+        dt = int(self.npdt == np.float64)
+        hx = self.lib.fluidb200_element_length(dt, float(domain_x), self.X)
+        hy = self.lib.fluidb200_element_length(dt, float(domain_y), self.Y)
+        self.slab = _lib.Slab(dt, self.X, self.Y, self.pitch, self.lo, self.rows, hx, hy)
+        self.f = {n: torch.zeros((self.rows, self.pitch), dtype=self.tdt, device=self.device) for n in _FIELDS}
+        self.edges = {}
+        self.time_step, self.kinematic_viscosity, self.density = 0.001, 0.1, 1.0
+        self.num_poisson_iterations, self.num_iterations = 50, 1
+        self.lid_velocity = 1.0
+        self.launches = 0
+        self.halo_bytes = 0
+        if self.on_gpu:
+            self.main = torch.cuda.current_stream(self.device)
+            self.comm = torch.cuda.Stream(self.device)
+        else:
+            self.main = self.comm = None
+        self._set_edges(1.0)
+
+    # ------------------------------------------------------------------------------------------
+    def _set_edges(self, lid):
+        for name in ("u", "v", "p"):
+            e = _lib.Edges()
+            _lib.check(self.lib, self.lib.fluidb200_cavity_edges(name.encode(), float(lid), C.byref(e)))
+            self.edges[name] = e
+
+    def _stream(self):
+        return C.c_void_p(self.main.cuda_stream) if self.on_gpu else None
+
+    def _ptr(self, name):
+        return C.c_void_p(self.f[name].data_ptr())
+
+    def init_cavity(self, lid_velocity=1.0):
+        """Zero state + cavity boundary values on this rank's rows (device-side, no host arrays)."""
+        self.lid_velocity = float(lid_velocity)
+        self._set_edges(lid_velocity)
+        _lib.check(self.lib, self.lib.fluidb200_init_cavity(
+            C.byref(self.slab), *[self._ptr(n) for n in _FIELDS], float(lid_velocity), self._stream()))
+        self.launches += 1
+
+    # -- halo exchange ---------------------------------------------------------------------------
+    def _rows(self, name, g0, g1):
+        """Contiguous view of global rows [g0, g1) of a field."""
+        return self.f[name][g0 - self.lo: g1 - self.lo]
+
+    def _post_exchange(self, names, depth):
+        """Start sending the `depth` outermost owned rows of each field to both neighbours and
+        receiving theirs into the halo rows. Returns the list of work handles."""
+        if self.world == 1:
+            return []
+        dist = self.dist
+        ops = []
+        for n in names:
+            if self.rank > 0:
+                ops.append(dist.P2POp(dist.isend, self._rows(n, self.x0, self.x0 + depth), self.rank - 1, self.group))
+                ops.append(dist.P2POp(dist.irecv, self._rows(n, self.x0 - depth, self.x0), self.rank - 1, self.group))
+            if self.rank < self.world - 1:
+                ops.append(dist.P2POp(dist.isend, self._rows(n, self.x1 - depth, self.x1), self.rank + 1, self.group))
+                ops.append(dist.P2POp(dist.irecv, self._rows(n, self.x1, self.x1 + depth), self.rank + 1, self.group))
+        per_row = self.pitch * self.npdt.itemsize
+        self.halo_bytes += sum(1 for o in ops if o.op is dist.isend) * depth * per_row
+        return dist.batch_isend_irecv(ops) if ops else []
+
+    @staticmethod
+    def _wait(works):
+        for w in works:
+            w.wait()
+
+    def exchange(self, names, depth):
+        self._wait(self._post_exchange(names, depth))
+
+    # -- phases ----------------------------------------------------------------------------------
+    def _params(self):
+        T = self.npdt.type
+        return float(T(self.time_step)), float(T(self.kinematic_viscosity)), float(T(self.density))
+
+    def predictor(self):
+        dt, nu, rho = self._params()
+        k = self.kmax
+        star_lo, star_hi = max(0, self.x0 - k), min(self.X, self.x1 + k)
+        rhs_lo, rhs_hi = max(0, self.x0 - k + 1), min(self.X, self.x1 + k - 1)
+        if self.world == 1:
+            star_lo, star_hi, rhs_lo, rhs_hi = 0, self.X, 0, self.X
+        _lib.check(self.lib, self.lib.fluidb200_predictor(
+            C.byref(self.slab), self._ptr("u"), self._ptr("v"), self._ptr("u_next"), self._ptr("v_next"),
+            self._ptr("rhs"), dt, nu, rho, star_lo, star_hi, rhs_lo, rhs_hi, self._stream()))
+        self.launches += 1
+
+    def _sweeps(self, k, lo, hi):
+        """k sweeps: reads f['p'], writes global rows [lo, hi) of f['p_next']."""
+        _lib.check(self.lib, self.lib.fluidb200_poisson_sweeps(
+            C.byref(self.slab), self._ptr("p"), self._ptr("p_next"), self._ptr("rhs"), C.byref(self.edges["p"]),
+            None, k, lo, hi, self._stream()))
+        self.launches += 1
+
+    def _swap_p(self):
+        self.f["p"], self.f["p_next"] = self.f["p_next"], self.f["p"]   # ping-pong instead of p = p_next
+
+    def poisson(self, sweeps):
+        """`sweeps` Jacobi sweeps, at most kmax per launch, one halo exchange after every launch.
+        The exchange always moves kmax rows: enough for whatever depth the next launch uses, and for
+        the corrector's p[x +- 1]."""
+        torch = self.torch
+        left = int(sweeps)
+        d = self.kmax
+        x0, x1 = self.x0, self.x1
+        while left > 0:
+            k = min(self.kmax, left)
+            left -= k
+            if self.world == 1:
+                self._sweeps(k, 0, self.X)
+                self._swap_p()
+                continue
+            if not self.overlap:
+                self._sweeps(k, x0, x1)
+                self.exchange(["p_next"], d)
+                self._swap_p()
+                continue
+            # 1. the d-row strips the neighbours are waiting for (none on a wall side)
+            lo_strip = (x0, x0 + d) if self.rank > 0 else None
+            hi_strip = (x1 - d, x1) if self.rank < self.world - 1 else None
+            for strip in (lo_strip, hi_strip):
+                if strip:
+                    self._sweeps(k, *strip)
+            ready = torch.cuda.Event()
+            ready.record(self.main)
+            # 2. ship them on the communication stream ...
+            self.comm.wait_event(ready)
+            with torch.cuda.stream(self.comm):
+                works = self._post_exchange(["p_next"], d)
+            # 3. ... while the interior of the owned range is swept on the main stream
+            self._sweeps(k, lo_strip[1] if lo_strip else x0, hi_strip[0] if hi_strip else x1)
+            with torch.cuda.stream(self.comm):
+                self._wait(works)
+                done = torch.cuda.Event()
+                done.record(self.comm)
+            self.main.wait_event(done)
+            self._swap_p()
+
+    def corrector(self):
+        dt, _, rho = self._params()
+        lo, hi = (0, self.X) if self.world == 1 else (self.x0, self.x1)
+        _lib.check(self.lib, self.lib.fluidb200_corrector(
+            C.byref(self.slab), self._ptr("p"), self._ptr("u_next"), self._ptr("v_next"), self._ptr("u"),
+            self._ptr("v"), C.byref(self.edges["u"]), C.byref(self.edges["v"]), None, None, dt, rho, lo, hi,
+            self._stream()))
+        self.launches += 1
+
+    def step(self):
+        """One projection timestep (phase order of SerialNavierStokes.cpp:49-67)."""
+        if self.world > 1:
+            self.exchange(["u", "v"], self.H)
+        self.predictor()
+        self.poisson(self.num_poisson_iterations)
+        self.corrector()
+
+    def solve(self):
+        for _ in range(int(self.num_iterations)):
+            self.step()
+
+    def synchronize(self):
+        if self.on_gpu:
+            self.torch.cuda.synchronize(self.device)
+
+    # -- results ---------------------------------------------------------------------------------
+    def owned(self, name):
+        """This rank's owned rows of a field as a dense (x1-x0, Y) NumPy array."""
+        self.synchronize()
+        return self._rows(name, self.x0, self.x1)[:, : self.Y].cpu().numpy()
+
+    def gather(self, name, dst=0):
+        """The whole field on rank `dst` (None elsewhere); for tests and small grids."""
+        mine = self.owned(name)
+        if self.world == 1:
+            return mine
+        out = [None] * self.world if self.rank == dst else None
+        self.dist.gather_object(mine, out, dst=dst, group=self.group)
+        return np.concatenate(out, axis=0) if self.rank == dst else None
+
+    def upload_owned(self, name, host_tensor):
+        """Host (pinned) tensor of this rank's owned rows, shape (x1-x0, Y) -> device slab."""
+        self._rows(name, self.x0, self.x1)[:, : self.Y].copy_(host_tensor, non_blocking=True)
+
+    def download_owned(self, name, host_tensor):
+        host_tensor.copy_(self._rows(name, self.x0, self.x1)[:, : self.Y], non_blocking=True)
+
+
+# ---------------------------------------------------------------------------------------------
+def bench_distributed(args, grid, sweeps, kmax, prm, metric, unit):
+    """bench.py's N > 1 arm: weak scaling, `grid` rows per GPU (X = grid * N, Y = grid)."""
+    import os
+    import time
+
+    import torch
+    import torch.distributed as dist
+
+    rank = int(os.environ.get("RANK", 0))
+    world = int(os.environ.get("WORLD_SIZE", 1))
+    local = int(os.environ.get("LOCAL_RANK", rank))
+    torch.cuda.set_device(local)
+    dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    X, Y = grid * world, grid
+    s = SlabSolver(X, Y, float(X - 1), float(Y - 1), np.float32, rank=rank, world=world,
+                   device=f"cuda:{local}", kmax=kmax)
+    s.time_step, s.kinematic_viscosity, s.density = prm["dt"], prm["nu"], prm["rho"]
+    s.num_poisson_iterations, s.num_iterations = sweeps, 1
+    s.init_cavity(prm["lid"])
+    warm = max(args.warmup, 3)
+    for _ in range(warm):
+        s.step()
+    torch.cuda.synchronize()
+    dist.barrier()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    l0, hb0 = s.launches, s.halo_bytes
+    e0.record(s.main)
+    for _ in range(args.steps):
+        s.step()
+    e1.record(s.main)
+    torch.cuda.synchronize()
+    dist.barrier()
+    ms = torch.tensor([e0.elapsed_time(e1)], device=s.device)
+    dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+    total_ms = float(ms.item())
+    launches = torch.tensor([s.launches - l0], device=s.device)
+    dist.all_reduce(launches)
+    cells = X * Y
+
+    # e2e: every step each rank uploads its owned u, v, p from pinned host memory and reads them back
+    own = s.x1 - s.x0
+    host = [torch.zeros((own, Y), dtype=torch.float32).pin_memory() for _ in range(3)]
+    host[0][:, Y - 1] = prm["lid"]
+    e2e_steps = max(1, min(args.steps, int(os.environ.get("FLUIDB200_E2E_STEPS", 3))))
+
+    def e2e_step():
+        for n, h in zip(("u", "v", "p"), host):
+            s.upload_owned(n, h)
+        s.step()
+        for n, h in zip(("u", "v", "p"), host):
+            s.download_owned(n, h)
+        torch.cuda.synchronize()
+
+    e2e_step()
+    dist.barrier()
+    t0 = time.perf_counter()
+    for _ in range(e2e_steps):
+        e2e_step()
+    dist.barrier()
+    t = torch.tensor([time.perf_counter() - t0], device=s.device)
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    e2e_s = float(t.item())
+    finite = torch.tensor([int(bool(torch.isfinite(host[0]).all()))], device=s.device)
+    dist.all_reduce(finite, op=dist.ReduceOp.MIN)
+    assert int(finite.item()) == 1, "non-finite field after the e2e steps"
+    halo_per_step = (s.halo_bytes - hb0) / max(1, args.steps + e2e_steps + 1)
+    dist.destroy_process_group()
+    if rank != 0:
+        return None
+    return {
+        "metric": metric, "value": cells * args.steps / (total_ms * 1e-3) / 1e9, "unit": unit, "n_gpus": world,
+        "steps": args.steps, "warmup": warm, "ms_per_step": total_ms / args.steps, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": f"cavity {X}x{Y} fp32 ({grid} rows per GPU, x-slabs), {sweeps} Poisson sweeps/step",
+                   "dt": prm["dt"], "nu": prm["nu"], "rho": prm["rho"], "hx": 1.0, "hy": 1.0, "sweeps_per_launch": kmax,
+                   "parallelism": f"x-slabs x{world}, halo depth {kmax + 1}, NCCL send/recv overlapped with interior sweeps",
+                   "halo_bytes_per_rank_per_step": halo_per_step,
+                   "l2": "fields are 1.07 GB per GPU, >> 126 MB L2, no flush needed"},
+        "roofline": None, "cpu_baseline": None,
+        "e2e": {"value": cells * e2e_steps / e2e_s / 1e9, "unit": unit, "h2d_bytes_per_step": 3 * cells * 4,
+                "d2h_bytes_per_step": 3 * cells * 4, "steps": e2e_steps, "ms_per_step": e2e_s / e2e_steps * 1e3,
+                "api": "per rank: copy owned u,v,p from pinned host + SlabSolver.step() + copy back"},
+        "gpu_launches": int(launches.item()), "clocks": None,
+    }
