@@ -98,8 +98,9 @@ def test_slab_arithmetic_on_one_gpu_serial_ranks():
     from fluid_simulation_b200 import _lib
     from fluid_simulation_b200.distributed import SlabSolver
     X, Y, K, kmax, world = 400, 700, 9, 4, 3
-    ranks = [SlabSolver(X, Y, 1.0, 1.0, np.float32, rank=r, world=1, device="cuda:0", kmax=kmax) for r in range(world)]
-    # re-shape each into rank r of `world` without a process group: exchange by direct copies below
+    base = SlabSolver(X, Y, 1.0, 1.0, np.float32, rank=0, world=1, device="cuda:0", kmax=kmax)
+    ranks = [base]
+    # clone it into rank r of `world` without a process group: exchange by direct copies below
     from fluid_simulation_b200.distributed import slab_bounds
     slabs = []
     for r in range(world):
