@@ -32,7 +32,7 @@ template <typename T, int V, int K, bool MASK>
 __global__ void __launch_bounds__(kThreads, FLUIDB200_JACOBI_MIN_BLOCKS(K)) jacobi_kernel(const __grid_constant__ fb::JacobiArgs<T> A) {
     const int strip = blockIdx.x * fb::kWarpsPerCta + (threadIdx.x >> 5);
     if (strip >= A.g.nstrips) return;  // whole warps only; the tasks use no block barrier
-    fb::jacobi_task<T, V, K, MASK>(A, strip, blockIdx.y, threadIdx.x & 31);
+    fb::jacobi_task<T, V, K, MASK>(A, strip, blockIdx.y, threadIdx.x & 31, threadIdx.x, kThreads);
 }
 
 template <typename T, int V, int MODE>
@@ -72,8 +72,10 @@ inline dim3 grid_for(int nstrips, int nchunks) {
 template <typename T, int K> int launch_jacobi_k(const fb::JacobiArgs<T>& a, bool mask, int nchunks, cudaStream_t st) {
     constexpr int V = fb::VecWidth<T>::V;
     const dim3 grid = grid_for(a.g.nstrips, nchunks);
-    if (K == 1 && mask) jacobi_kernel<T, V, 1, true><<<grid, kThreads, 0, st>>>(a);
-    else jacobi_kernel<T, V, K, false><<<grid, kThreads, 0, st>>>(a);
+    // dynamic shared memory: the per-lane cp.async prefetch ring (D slots x 2 arrays x 16 B per thread)
+    const size_t smem = (size_t)fb::JacobiRing<K>::D * 2 * 16 * kThreads;
+    if (K == 1 && mask) jacobi_kernel<T, V, 1, true><<<grid, kThreads, smem, st>>>(a);
+    else jacobi_kernel<T, V, K, false><<<grid, kThreads, smem, st>>>(a);
     return rc_of(cudaGetLastError());
 }
 

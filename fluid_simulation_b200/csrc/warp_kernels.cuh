@@ -37,6 +37,7 @@
 #include <cuda_runtime.h>
 #define FB_DEV __device__ __forceinline__
 #define FB_DEV_NOINLINE __device__ __noinline__
+#define FB_EMU_CHECK(p, n, what) ((void)0)
 #endif
 
 namespace fb {
@@ -172,6 +173,7 @@ template <typename T, int V> FB_DEV Vec<T, V> vzero() {
 // read-only streaming load (inputs never alias outputs in the kernels that use it)
 template <typename T, int V> FB_DEV Vec<T, V> ld_ro(const T* p) {
 #ifdef FLUIDB200_HOST_EMU
+    FB_EMU_CHECK(p, sizeof(Vec<T, V>), "load");
     return *reinterpret_cast<const Vec<T, V>*>(p);
 #else
     const int4 r = __ldg(reinterpret_cast<const int4*>(p));
@@ -181,9 +183,11 @@ template <typename T, int V> FB_DEV Vec<T, V> ld_ro(const T* p) {
 #endif
 }
 template <typename T, int V> FB_DEV Vec<T, V> ld_rw(const T* p) {
+    FB_EMU_CHECK(p, sizeof(Vec<T, V>), "load");
     return *reinterpret_cast<const Vec<T, V>*>(p);
 }
 template <typename T, int V> FB_DEV void st_vec(T* p, const Vec<T, V>& v) {
+    FB_EMU_CHECK(p, sizeof(Vec<T, V>), "store");
     *reinterpret_cast<Vec<T, V>*>(p) = v;
 }
 
@@ -297,6 +301,51 @@ FB_DEV void st_interior(T* rowp, int col0, int Y, const Vec<T, V>& v) {
     }
 }
 
+// ---------------------------------------------------------------------------------------
+// Per-lane asynchronous prefetch ring (cp.async / LDGSTS into shared memory).
+// Every lane copies its OWN 16 bytes of a row into its own slot and later reads the same 16 bytes
+// back, so completion is tracked per thread (cp.async.wait_group) and no barrier of any kind is
+// needed. Register prefetching did not survive the compiler: under the register cap ptxas sank
+// the LDGs to just before their first use (ncu: 43 % of all stall samples sat on that first use),
+// whereas an asynchronous copy is issued where it is written and holds no registers in flight.
+// D slots x 2 arrays x 16 B per thread.
+// ---------------------------------------------------------------------------------------
+template <typename T, int V, int D> struct LaneRing {
+#ifdef FLUIDB200_HOST_EMU
+    Vec<T, V> buf[D][2];
+    FB_DEV void init(int, int) {}
+    FB_DEV void fetch(int slot, int arr, const T* src) {
+        FB_EMU_CHECK(src, sizeof(Vec<T, V>), "prefetch");
+        buf[slot][arr] = *reinterpret_cast<const Vec<T, V>*>(src);
+    }
+    FB_DEV Vec<T, V> read(int slot, int arr) const { return buf[slot][arr]; }
+    static FB_DEV void commit() {}
+    template <int N> static FB_DEV void wait() {}
+#else
+    unsigned char* mine;   // generic address of this thread's 16 bytes in slot 0, array 0
+    unsigned stride;       // bytes between consecutive (slot, array) planes
+    FB_DEV void init(int tid, int nthreads) {
+        extern __shared__ __align__(16) unsigned char fb_ring_smem[];
+        mine = fb_ring_smem + tid * 16;
+        stride = (unsigned)nthreads * 16u;
+    }
+    FB_DEV void fetch(int slot, int arr, const T* src) {
+        const unsigned dst = (unsigned)__cvta_generic_to_shared(mine + (slot * 2 + arr) * stride);
+        asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst), "l"(src) : "memory");
+    }
+    FB_DEV Vec<T, V> read(int slot, int arr) const {
+        return *reinterpret_cast<const Vec<T, V>*>(mine + (slot * 2 + arr) * stride);
+    }
+    static FB_DEV void commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+    template <int N> static FB_DEV void wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
+#endif
+};
+// ring depth used by the Jacobi fast path for blocking depth K (U = steps per unrolled iteration)
+template <int K> struct JacobiRing {
+    static constexpr int U = (K + 1) & ~1;
+    static constexpr int D = U < 4 ? 4 : U;
+};
+
 // =========================================================================================
 // Jacobi pressure-Poisson sweeps, K sweeps per launch, boundary rows fused in.
 // Replaces poisson_step_kernel + enforce_pressure_BC_kernel + update_pressure_kernel
@@ -367,7 +416,7 @@ FB_DEV Vec<T, V> jacobi_row(const Vec<T, V>& xm, const Vec<T, V>& c, const Vec<T
 // the FAST path (no per-level range checks, no wall logic); pipeline fill/drain at the box walls
 // and masked sweeps take the GENERAL path. Both act on the same register state.
 template <typename T, int V, int K, bool MASK>
-FB_DEV void jacobi_task(const JacobiArgs<T>& A, int strip, int chunk, int lane) {
+FB_DEV void jacobi_task(const JacobiArgs<T>& A, int strip, int chunk, int lane, int tid, int nthreads) {
     constexpr int H = (K + 3) & ~3;
     using A_ = Ar<T>;
     using VT = Vec<T, V>;
@@ -458,7 +507,7 @@ FB_DEV void jacobi_task(const JacobiArgs<T>& A, int strip, int chunk, int lane) 
                     out = jacobi_row<T, V>(xm, c, xp, bw[t - 1]);
                     if (MASK) {  // interior flags (:154-160)
                         const long long off = (long long)(rr - g.row0) * g.pitch + st.col0;
-                        if (st.ld_ok) {
+                        if (st.ld_ok && rr >= r_begin && rr < load_hi) {
 #pragma unroll
                             for (int e = 0; e < V; ++e) {
                                 const int col = st.col0 + e;
@@ -486,24 +535,34 @@ FB_DEV void jacobi_task(const JacobiArgs<T>& A, int strip, int chunk, int lane) 
         }
         if (phase == 1 || nfast == 0) break;
         // ---------------- FAST path: [fast_lo, fast_hi], U steps per iteration ----------------
-        const int pmax = load_hi - 1, bmax = min(load_hi - 1, X - 2);  // prefetch clamps (never consumed)
-        VT pfp[U], pfb[U];
-        pfp[0] = nxt_p;
-        pfb[0] = nxt_b;
+        // Rows are prefetched D steps ahead through the per-lane cp.async ring; one commit group per
+        // step = {p row of that step, rhs row of the step before}. Row indices are clamped into the
+        // loaded range: the groups issued for steps beyond fast_hi are never consumed by this loop.
+        constexpr int D = JacobiRing<K>::D;
+        static_assert(D % U == 0, "ring depth must be a multiple of the unroll factor");
+        const int pmax = load_hi - 1, bmax = min(load_hi - 1, X - 2);
+        LaneRing<T, V, D> ring;
+        ring.init(tid, nthreads);
 #pragma unroll
-        for (int u = 1; u < U; ++u) {
-            pfp[u] = ld_ro<T, V>(pin + (long long)min(r + u, pmax) * g.pitch);
-            pfb[u] = ld_ro<T, V>(rin + (long long)min(r + u - 1, bmax) * g.pitch);
+        for (int j = 0; j < D; ++j) {
+            ring.fetch(j, 0, pin + (long long)min(r + j, pmax) * g.pitch);
+            ring.fetch(j, 1, rin + (long long)max(min(r + j - 1, bmax), r_begin) * g.pitch);
+            ring.commit();
         }
+        (void)nxt_p; (void)nxt_b;  // the ring re-reads rows r and r-1; the register copies are dropped
         const int first_store = c0 + K;  // step at which level K reaches row c0
+        int sbase = 0;                   // ring slot of step r (advances by U per iteration, mod D)
 #pragma unroll 1
         for (; r <= fast_hi; r += U) {
 #pragma unroll
             for (int u = 0; u < U; ++u) {
-                VT cur = pfp[u];
-                push_b(pfb[u]);
-                pfp[u] = ld_ro<T, V>(pin + (long long)min(r + u + U, pmax) * g.pitch);
-                pfb[u] = ld_ro<T, V>(rin + (long long)min(r + u + U - 1, bmax) * g.pitch);
+                const int slot = (D == U) ? u : sbase + u;
+                ring.template wait<D - 1>();          // the oldest group = this step's rows has landed
+                VT cur = ring.read(slot, 0);
+                push_b(ring.read(slot, 1));
+                ring.fetch(slot, 0, pin + (long long)min(r + u + D, pmax) * g.pitch);
+                ring.fetch(slot, 1, rin + (long long)min(r + u + D - 1, bmax) * g.pitch);
+                ring.commit();
 #pragma unroll
                 for (int t = 1; t <= K; ++t) {
                     const VT out = jacobi_row<T, V>(w[t - 1][0], w[t - 1][1], cur, bw[t - 1]);
@@ -513,9 +572,15 @@ FB_DEV void jacobi_task(const JacobiArgs<T>& A, int strip, int chunk, int lane) 
                 }
                 if (st.st_ok && r + u >= first_store) st_vec<T, V>(pout + (long long)(r + u - K) * g.pitch, cur);
             }
+            if (D != U) sbase = (sbase + U) % D;
         }
-        nxt_p = pfp[0];
-        nxt_b = pfb[0];
+        // hand over to the general path: rows r (p) and r-1 (rhs) are the oldest group in the ring
+        ring.template wait<0>();
+        {
+            const int slot = (D == U) ? 0 : sbase;
+            nxt_p = (r < load_hi) ? ring.read(slot, 0) : vzero<T, V>();
+            nxt_b = (r - 1 >= 1 && r - 1 <= X - 2 && r - 1 < load_hi) ? ring.read(slot, 1) : vzero<T, V>();
+        }
     }
 }
 
@@ -688,13 +753,17 @@ FB_DEV void predictor_task(const PredictorArgs<T>& A, int strip, int chunk, int 
                 tentative_row<T, V, MODE>(A, wu[0], wu[1], cu, wv[0], wv[1], cv, us, vs);
                 // edge columns of u_next/v_next keep whatever is stored (never written by the
                 // reference); the right-hand side below reads them as y-neighbours
-                const long long ro = (long long)(ra - g.row0) * g.pitch;
-                if (st.has_bottom) {
+                // (rows outside the loaded range only feed discarded pipeline-fill values: skip the loads)
+                const bool in_slab = ra >= r_begin && ra < load_hi;
+                const long long ro = in_slab ? (long long)(ra - g.row0) * g.pitch : 0;
+                if (st.has_bottom && in_slab) {
+                    FB_EMU_CHECK(A.us + ro, sizeof(T), "edge load");
                     const T ue = A.us[ro], ve = A.vs[ro];
                     us.a[0] = (lane == 0) ? ue : us.a[0];
                     vs.a[0] = (lane == 0) ? ve : vs.a[0];
                 }
-                if (st.has_top) {
+                if (st.has_top && in_slab) {
+                    FB_EMU_CHECK(A.us + ro + (Y - 1), sizeof(T), "edge load");
                     const T ue = A.us[ro + (Y - 1)], ve = A.vs[ro + (Y - 1)];
 #pragma unroll
                     for (int e = 0; e < V; ++e) {

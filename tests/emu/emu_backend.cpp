@@ -60,13 +60,19 @@ int be_graph_end(void*, void**) { return -1; }
 int be_graph_launch(void*, void*) { return -1; }
 int be_graph_destroy(void*) { return 0; }
 
+static void set_ranges(std::initializer_list<const void*> ptrs, size_t bytes) {
+    emu_nranges = 0;
+    for (const void* p : ptrs)
+        if (p) emu_ranges[emu_nranges++] = {(const char*)p, (const char*)p + bytes};
+}
 template <typename T, int K>
 static void jac_k(const fb::JacobiArgs<T>& a, bool mask, int nchunks) {
+    set_ranges({a.p_in, a.p_out, a.rhs}, (size_t)a.g.rows * a.g.pitch * sizeof(T));
     constexpr int V = fb::VecWidth<T>::V;
     if (K == 1 && mask)
-        run_grid(a.g.nstrips, nchunks, [&](int s, int c, int l) { fb::jacobi_task<T, V, 1, true>(a, s, c, l); });
+        run_grid(a.g.nstrips, nchunks, [&](int s, int c, int l) { fb::jacobi_task<T, V, 1, true>(a, s, c, l, l, 32); });
     else
-        run_grid(a.g.nstrips, nchunks, [&](int s, int c, int l) { fb::jacobi_task<T, V, K, false>(a, s, c, l); });
+        run_grid(a.g.nstrips, nchunks, [&](int s, int c, int l) { fb::jacobi_task<T, V, K, false>(a, s, c, l, l, 32); });
 }
 template <typename T> int launch_jacobi(const fb::JacobiArgs<T>& a, int sweeps, bool mask, int nchunks, void*) {
     switch (sweeps) {
@@ -84,6 +90,7 @@ template <typename T> int launch_jacobi(const fb::JacobiArgs<T>& a, int sweeps, 
 }
 template <typename T> int launch_predictor(const fb::PredictorArgs<T>& a, int nchunks, void*) {
     constexpr int V = fb::VecWidth<T>::V;
+    set_ranges({a.u, a.v, a.us, a.vs, a.rhs}, (size_t)a.g.rows * a.g.pitch * sizeof(T));
     const int mode = sizeof(T) == 4 ? a.m.mode : 0;
     if (mode == 2) run_grid(a.g.nstrips, nchunks, [&](int s, int c, int l) { fb::predictor_task<T, V, (sizeof(T) == 4 ? 2 : 0)>(a, s, c, l); });
     else if (mode == 1) run_grid(a.g.nstrips, nchunks, [&](int s, int c, int l) { fb::predictor_task<T, V, (sizeof(T) == 4 ? 1 : 0)>(a, s, c, l); });
@@ -92,6 +99,7 @@ template <typename T> int launch_predictor(const fb::PredictorArgs<T>& a, int nc
 }
 template <typename T> int launch_corrector(const fb::CorrectorArgs<T>& a, bool mask, int nchunks, void*) {
     constexpr int V = fb::VecWidth<T>::V;
+    set_ranges({a.p, a.us, a.vs, a.u, a.v}, (size_t)a.g.rows * a.g.pitch * sizeof(T));
     const int mode = sizeof(T) == 4 ? a.m.mode : 0;
     if (mask) {
         if (mode != 0) run_grid(a.g.nstrips, nchunks, [&](int s, int c, int l) { fb::corrector_task<T, V, true, (sizeof(T) == 4 ? 1 : 0)>(a, s, c, l); });

@@ -16,6 +16,24 @@
 using std::max;
 using std::min;
 
+// Bounds checking: the emulation backend registers the arrays of the launch being emulated and every
+// vector load/store/prefetch of the kernels is checked against them (compute-sanitizer is not
+// available on the GPU pool, so this is the memcheck of this repository).
+#include <cstdio>
+#include <cstdlib>
+struct EmuRange { const char* lo; const char* hi; };
+inline EmuRange emu_ranges[16];
+inline int emu_nranges = 0;
+inline void emu_check(const void* p, size_t n, const char* what) {
+    if (emu_nranges == 0) return;
+    const char* c = (const char*)p;
+    for (int i = 0; i < emu_nranges; ++i)
+        if (c >= emu_ranges[i].lo && c + n <= emu_ranges[i].hi) return;
+    std::fprintf(stderr, "EMU: out-of-bounds %s of %zu bytes at %p\n", what, n, p);
+    std::abort();
+}
+#define FB_EMU_CHECK(p, n, what) emu_check((p), (n), (what))
+
 struct EmuWarp {
     std::barrier<> bar{32};
     alignas(8) unsigned char slot[32][8];
