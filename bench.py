@@ -35,7 +35,7 @@ import numpy as np  # noqa: E402
 
 GRID = int(os.environ.get("FLUIDB200_BENCH_GRID", 16384))
 SWEEPS = int(os.environ.get("FLUIDB200_BENCH_SWEEPS", 100))
-KMAX = int(os.environ.get("FLUIDB200_KMAX", 4))
+KMAX = int(os.environ.get("FLUIDB200_KMAX", 5))
 METRIC = "Gcell-updates/s per timestep (cavity 16384x16384 fp32, 100 Poisson sweeps/step)"
 UNIT = "Gcell-updates/s"
 # stable, well-conditioned parameters for a 16384^2 grid: hx = hy = 1
@@ -246,6 +246,31 @@ def run_single(args):
     assert bool(torch.isfinite(host[0]).all()), "non-finite field after the e2e steps"
     s.close()
 
+    # ---- BASELINE.json configs[1], for the record: 1000 x 1000, 1000 timesteps, 50 sweeps each (the shape the
+    # reference publishes 1.23 min for on an RTX 2080 Super), launch-bound, so replayed as CUDA graphs. A stable
+    # dt is used (the reference's dt = 0.001 diverges to NaN at this resolution).
+    small = None
+    if not os.environ.get("FLUIDB200_SKIP_SMALL"):
+        n = 1000
+        sm = ParallelNavierStokes(n, n, 1.0, 1.0, dtype=np.float32)   # on its own stream: the legacy
+        sm.time_step = float(np.float32(0.125) * np.float32(1.0 / (n - 1)) ** 2 / np.float32(0.1))  # stream cannot be captured
+        sm.num_poisson_iterations, sm.num_iterations = 50, 1000
+        small = {"grid": f"{n}x{n}", "timesteps": 1000, "sweeps_per_step": 50, "dt": sm.time_step,
+                 "timing": "host clock around solve() + synchronize()"}
+        for graph in (False, True):
+            sm.set_use_graph(graph)
+            sm.upload_cavity(LID)
+            sm.num_iterations = 10
+            sm.solve(); sm.synchronize()      # warm-up (and graph capture)
+            sm.num_iterations = 1000
+            t0 = time.perf_counter()
+            sm.solve()
+            sm.synchronize()
+            ms = (time.perf_counter() - t0) * 1e3
+            small["ms_total_graph" if graph else "ms_total_plain"] = ms
+            small["gcell_updates_per_s_graph" if graph else "gcell_updates_per_s_plain"] = n * n * 1000 / (ms * 1e-3) / 1e9
+        sm.close()
+
     # ---- cpu baseline: bounded sample of the same workload on the host cores ---------------
     try:
         cv, _, cdesc = cpu_reference_run(int(os.environ.get("FLUIDB200_CPU_GRID", 1536)), SWEEPS, 2)
@@ -262,6 +287,7 @@ def run_single(args):
                    "l2": "fields are 1.07 GB each, >> 126 MB L2, no flush needed",
                    "effective_GBps_step": (40 + 12 * SWEEPS) * cells * args.steps / (total_ms * 1e-3) / 1e9},
         "roofline": roofline, "cpu_baseline": cdesc, "e2e": e2e, "gpu_launches": int(launches), "clocks": clk,
+        "config1_1000x1000": small,
     }
 
 

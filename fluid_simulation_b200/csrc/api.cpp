@@ -49,18 +49,28 @@ template <typename T> int num_strips(int Y, int H) {
     return n < 1 ? 1 : n;
 }
 
+// Warp tasks aimed for per launch (measured on B200 at 16384^2): the Jacobi pipeline pays K halo rows
+// per chunk end and is best around 12 waves; the two one-pass kernels have a 1-2 row halo and keep
+// improving up to ~40 waves.
+constexpr int kJacobiTasks = 148 * 16 * 12, kLightTasks = 148 * 16 * 40;
+
 // Split `n` output rows into chunks. More chunks = more warps in flight and a smaller tail, but
 // every chunk recomputes `halo` rows at each end. The chunk count is chosen so that the grid is
 // (just under) a whole number of waves over the SMs: `ctas_per_sm` is the occupancy the kernel is
 // compiled for, and a partial last wave showed up as a 10-15 % loss at 16384^2. A chunk that
 // touches a wall must hold >= 2 rows because the wall row is derived while its neighbour row is
 // produced.
-void plan_chunks(int n, int halo, int nstrips, int ctas_per_sm, int* rpc_out, int* nchunks_out) {
-    const long long target_tasks = env_int("FLUIDB200_TARGET_TASKS", 148 * 16 * 10);
+void plan_chunks(int n, int halo, int nstrips, int ctas_per_sm, int default_tasks, int* rpc_out, int* nchunks_out) {
+    const long long target_tasks = env_int("FLUIDB200_TARGET_TASKS", default_tasks);
     int min_rpc = env_int("FLUIDB200_MIN_RPC", 0);
-    if (min_rpc <= 0) min_rpc = std::max(8, 8 * halo);
     const long long ctas_x = (nstrips + fb::kWarpsPerCta - 1) / fb::kWarpsPerCta;
     const long long slots = (long long)fbk::be_sm_count() * std::max(1, ctas_per_sm);
+    if (min_rpc <= 0) {
+        // Large grids: keep the recomputed halo below ~25 % of a chunk. Small grids (not even one wave
+        // of CTAs at that chunk length) are latency bound, so trade redundant rows for parallelism.
+        min_rpc = std::max(8, 8 * halo);
+        if ((long long)((n + min_rpc - 1) / min_rpc) * ctas_x < slots) min_rpc = std::max(4, 2 * halo);
+    }
     long long want_chunks = std::max(1LL, (target_tasks + nstrips - 1) / nstrips);
     long long waves = std::max(1LL, (want_chunks * ctas_x + slots / 2) / slots);
     long long aligned = (waves * slots) / ctas_x;  // chunks that fill `waves` waves exactly (rounded down)
@@ -161,7 +171,7 @@ int predictor_t(const fluidb200_slab* g, const void* u, const void* v, void* us,
     a.hi = std::max(star_hi, rhs_hi);
     const int nstrips = num_strips<T>(g->Y, 4);
     int rpc, nchunks;
-    plan_chunks(a.hi - a.lo, 2, nstrips, 4, &rpc, &nchunks);
+    plan_chunks(a.hi - a.lo, 2, nstrips, 4, kLightTasks, &rpc, &nchunks);
     a.g = make_geom(g, nstrips, rpc);
     BE_CHECK(fbk::launch_predictor<T>(a, nchunks, stream), "predictor launch");
     return 0;
@@ -181,7 +191,7 @@ int poisson_t(const fluidb200_slab* g, const void* p_in, void* p_out, const void
     a.e = to_dev_edges<T>(e);
     const int nstrips = num_strips<T>(g->Y, halo_cols(sweeps));
     int rpc, nchunks;
-    plan_chunks(out_hi - out_lo, sweeps, nstrips, sweeps <= 2 ? 5 : sweeps <= 4 ? 4 : 2, &rpc, &nchunks);
+    plan_chunks(out_hi - out_lo, sweeps, nstrips, sweeps <= 2 ? 5 : sweeps <= 4 ? 4 : sweeps <= 6 ? 3 : 2, kJacobiTasks, &rpc, &nchunks);
     a.g = make_geom(g, nstrips, rpc);
     BE_CHECK(fbk::launch_jacobi<T>(a, sweeps, use_mask, nchunks, stream), "poisson launch");
     return 0;
@@ -204,7 +214,7 @@ int corrector_t(const fluidb200_slab* g, const void* p, const void* us, const vo
     a.ev = to_dev_edges<T>(ev);
     const int nstrips = num_strips<T>(g->Y, 4);
     int rpc, nchunks;
-    plan_chunks(out_hi - out_lo, 1, nstrips, 4, &rpc, &nchunks);
+    plan_chunks(out_hi - out_lo, 1, nstrips, 4, kLightTasks, &rpc, &nchunks);
     a.g = make_geom(g, nstrips, rpc);
     BE_CHECK(fbk::launch_corrector<T>(a, um || vm, nchunks, stream), "corrector launch");
     return 0;
@@ -497,7 +507,7 @@ extern "C" int fluidb200_create(fluidb200_solver** out, int dtype, int X, int Y,
     s->dtype = dtype; s->X = X; s->Y = Y;
     s->esize = dtype == FLUIDB200_F32 ? 4 : 8;
     s->pitch = ((int64_t)Y + 31) / 32 * 32;
-    s->kmax = env_int("FLUIDB200_KMAX", 4);
+    s->kmax = env_int("FLUIDB200_KMAX", 5);
     fluidb200_set_domain(s, domain_x, domain_y);
     if (fbk::be_stream_create(&s->stream) != 0) {
         delete s;

@@ -26,7 +26,7 @@ constexpr int kThreads = fb::kWarpsPerCta * 32;
 // Resident CTAs per SM the register allocator must leave room for: the pipeline is latency bound
 // (ncu: ~50 % issue, ~50 % DRAM at 12 warps/SM), so shallow depths trade registers for warps.
 #ifndef FLUIDB200_JACOBI_MIN_BLOCKS
-#define FLUIDB200_JACOBI_MIN_BLOCKS(K) ((K) <= 2 ? 5 : (K) <= 4 ? 4 : (K) <= 6 ? 2 : 2)
+#define FLUIDB200_JACOBI_MIN_BLOCKS(K) ((K) <= 2 ? 5 : (K) <= 4 ? 4 : (K) <= 6 ? 3 : 2)
 #endif
 template <typename T, int V, int K, bool MASK>
 __global__ void __launch_bounds__(kThreads, FLUIDB200_JACOBI_MIN_BLOCKS(K)) jacobi_kernel(const __grid_constant__ fb::JacobiArgs<T> A) {
