@@ -254,7 +254,9 @@ class SlabSolver:
 
 # ---------------------------------------------------------------------------------------------
 def bench_distributed(args, grid, sweeps, kmax, prm, metric, unit):
-    """bench.py's N > 1 arm: weak scaling, `grid` rows per GPU (X = grid * N, Y = grid)."""
+    """bench.py's N > 1 arm. Default: weak scaling, `grid` rows per GPU (X = grid * N, Y = grid).
+    FLUIDB200_SCALING=strong fixes the total at FLUIDB200_STRONG_GRID^2 (default 32768^2,
+    BASELINE.json configs[3]) and splits its rows over the N ranks."""
     import os
     import time
 
@@ -266,7 +268,11 @@ def bench_distributed(args, grid, sweeps, kmax, prm, metric, unit):
     local = int(os.environ.get("LOCAL_RANK", rank))
     torch.cuda.set_device(local)
     dist.init_process_group("nccl", device_id=torch.device("cuda", local))
-    X, Y = grid * world, grid
+    strong = os.environ.get("FLUIDB200_SCALING", "weak") == "strong"
+    if strong:
+        X = Y = int(os.environ.get("FLUIDB200_STRONG_GRID", 32768))
+    else:
+        X, Y = grid * world, grid
     s = SlabSolver(X, Y, float(X - 1), float(Y - 1), np.float32, rank=rank, world=world,
                    device=f"cuda:{local}", kmax=kmax)
     s.time_step, s.kinematic_viscosity, s.density = prm["dt"], prm["nu"], prm["rho"]
@@ -326,12 +332,12 @@ def bench_distributed(args, grid, sweeps, kmax, prm, metric, unit):
     return {
         "metric": metric, "value": cells * args.steps / (total_ms * 1e-3) / 1e9, "unit": unit, "n_gpus": world,
         "steps": args.steps, "warmup": warm, "ms_per_step": total_ms / args.steps, "higher_is_better": True,
-        "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": f"cavity {X}x{Y} fp32 ({grid} rows per GPU, x-slabs), {sweeps} Poisson sweeps/step",
+        "scaling": "strong" if strong else "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": f"cavity {X}x{Y} fp32 ({s.x1 - s.x0} rows per GPU, x-slabs), {sweeps} Poisson sweeps/step",
                    "dt": prm["dt"], "nu": prm["nu"], "rho": prm["rho"], "hx": 1.0, "hy": 1.0, "sweeps_per_launch": kmax,
                    "parallelism": f"x-slabs x{world}, halo depth {kmax + 1}, NCCL send/recv overlapped with interior sweeps",
                    "halo_bytes_per_rank_per_step": halo_per_step,
-                   "l2": "fields are 1.07 GB per GPU, >> 126 MB L2, no flush needed"},
+                   "l2": f"fields are {(s.x1 - s.x0) * Y * 4 / 1e9:.2f} GB per GPU, >> 126 MB L2, no flush needed"},
         "roofline": None, "cpu_baseline": None,
         "e2e": {"value": cells * e2e_steps / e2e_s / 1e9, "unit": unit, "h2d_bytes_per_step": 3 * cells * 4,
                 "d2h_bytes_per_step": 3 * cells * 4, "steps": e2e_steps, "ms_per_step": e2e_s / e2e_steps * 1e3,

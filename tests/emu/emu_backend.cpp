@@ -6,6 +6,9 @@
 #include <stdlib.h>
 #include <string.h>
 
+#include <algorithm>
+#include <atomic>
+#include <functional>
 #include <thread>
 #include <vector>
 
@@ -14,24 +17,81 @@
 #include "warp_kernels.cuh"
 
 namespace {
-// run fn(strip, chunk, lane) for every warp task; a warp = 32 lockstep-capable threads
-template <typename F> void run_grid(int nstrips, int nchunks, F fn) {
-    struct Job { int strip, chunk; };
-    std::vector<Job> jobs;
-    for (int c = 0; c < nchunks; ++c)
-        for (int s = 0; s < nstrips; ++s) jobs.push_back({s, c});
-    // one warp at a time (32 threads); tasks are independent so order does not matter
-    for (const Job& j : jobs) {
-        EmuWarp w;
-        std::vector<std::thread> lanes;
-        for (int l = 0; l < 32; ++l)
-            lanes.emplace_back([&, l] {
-                emu_warp = &w;
+
+constexpr size_t kFiberStack = 256 * 1024;
+
+struct WarpRunner {
+    EmuWarp w;
+    std::vector<char> stacks;
+    std::function<void(int)>* body = nullptr;
+    WarpRunner() : stacks(32 * kFiberStack) {}
+
+    static void trampoline(unsigned lo, unsigned hi, int lane) {
+        WarpRunner* self = (WarpRunner*)(((uintptr_t)hi << 32) | (uintptr_t)lo);
+        (*self->body)(lane);
+        self->w.done[lane] = true;
+        // returning switches to uc_link = the scheduler
+    }
+
+    // run one warp task: body(lane) for 32 lanes in lock step
+    void run(std::function<void(int)>& fn) {
+        body = &fn;
+        emu_warp = &w;
+        w.arrived = 0;
+        for (int l = 0; l < 32; ++l) {
+            w.par[l] = 0;
+            w.waiting[l] = false;
+            w.done[l] = false;
+            getcontext(&w.ctx[l]);
+            w.ctx[l].uc_stack.ss_sp = stacks.data() + (size_t)l * kFiberStack;
+            w.ctx[l].uc_stack.ss_size = kFiberStack;
+            w.ctx[l].uc_link = &w.sched;
+            const uintptr_t p = (uintptr_t)this;
+            makecontext(&w.ctx[l], (void (*)())trampoline, 3, (unsigned)(p & 0xffffffffu), (unsigned)(p >> 32), l);
+        }
+        for (;;) {
+            int live = 0;
+            for (int l = 0; l < 32; ++l) {
+                if (w.done[l] || w.waiting[l]) continue;
                 emu_lane = l;
-                fn(j.strip, j.chunk, l);
-                w.bar.arrive_and_drop();
-            });
-        for (auto& t : lanes) t.join();
+                swapcontext(&w.sched, &w.ctx[l]);  // until the lane reaches a shuffle or returns
+            }
+            for (int l = 0; l < 32; ++l) live += !w.done[l];
+            if (live == 0) break;
+            if (w.arrived != live || live != 32) {
+                // on the GPU this is a shuffle executed by only part of the warp: undefined behaviour
+                std::fprintf(stderr, "EMU: divergent warp shuffle (%d of 32 lanes arrived, %d live)\n", w.arrived, live);
+                std::abort();
+            }
+            w.arrived = 0;
+            for (int l = 0; l < 32; ++l) w.waiting[l] = false;
+        }
+    }
+};
+
+// run fn(strip, chunk, lane) for every warp task. Tasks are independent (disjoint outputs), so they
+// are spread over the host cores; each OS thread emulates one warp at a time.
+template <typename F> void run_grid(int nstrips, int nchunks, F fn) {
+    const int njobs = nstrips * nchunks;
+    std::atomic<int> next{0};
+    auto worker = [&] {
+        WarpRunner runner;
+        for (;;) {
+            const int j = next.fetch_add(1);
+            if (j >= njobs) break;
+            const int strip = j % nstrips, chunk = j / nstrips;
+            std::function<void(int)> body = [&, strip, chunk](int lane) { fn(strip, chunk, lane); };
+            runner.run(body);
+        }
+    };
+    int nthreads = (int)std::thread::hardware_concurrency();
+    nthreads = std::max(1, std::min(nthreads, std::min(njobs, 16)));
+    if (nthreads == 1) {
+        worker();
+    } else {
+        std::vector<std::thread> pool;
+        for (int t = 0; t < nthreads; ++t) pool.emplace_back(worker);
+        for (auto& t : pool) t.join();
     }
 }
 }  // namespace

@@ -6,7 +6,6 @@
 // Build with -ffp-contract=off so the *_rn shims below are never fused.
 #pragma once
 #include <algorithm>
-#include <barrier>
 #include <cmath>
 #include <cstdint>
 #include <cstring>
@@ -34,19 +33,36 @@ inline void emu_check(const void* p, size_t n, const char* what) {
 }
 #define FB_EMU_CHECK(p, n, what) emu_check((p), (n), (what))
 
+// A warp is 32 user-level fibers (ucontext) on ONE OS thread, run in lock step by a small
+// scheduler: a lane runs until it reaches a shuffle (or returns); when every live lane has
+// published its value the scheduler resumes them one by one to read their source lane's value.
+// Values are double buffered by shuffle parity, so a resumed lane may already publish for the
+// NEXT shuffle while later lanes still read this one. No kernel calls are involved (the earlier
+// std::thread + std::barrier version spent minutes in futexes).
+#include <ucontext.h>
 struct EmuWarp {
-    std::barrier<> bar{32};
-    alignas(8) unsigned char slot[32][8];
+    ucontext_t sched;
+    ucontext_t ctx[32];
+    alignas(8) unsigned char slot[2][32][8];
+    unsigned char par[32];
+    bool waiting[32];
+    bool done[32];
+    int arrived;
 };
 inline thread_local EmuWarp* emu_warp = nullptr;
 inline thread_local int emu_lane = 0;
 
 template <typename T> inline T emu_exchange(T x, int src) {
-    std::memcpy(emu_warp->slot[emu_lane], &x, sizeof(T));
-    emu_warp->bar.arrive_and_wait();
+    EmuWarp* w = emu_warp;
+    const int lane = emu_lane;
+    const int par = w->par[lane];
+    w->par[lane] ^= 1;
+    std::memcpy(w->slot[par][lane], &x, sizeof(T));
+    w->arrived++;
+    w->waiting[lane] = true;
+    swapcontext(&w->ctx[lane], &w->sched);  // resumed once every live lane has published
     T r;
-    std::memcpy(&r, emu_warp->slot[src], sizeof(T));
-    emu_warp->bar.arrive_and_wait();
+    std::memcpy(&r, w->slot[par][src], sizeof(T));
     return r;
 }
 template <typename T> inline T __shfl_up_sync(unsigned, T x, int d) {

@@ -43,7 +43,8 @@ def _worker(rank, world, port, X, Y, S, K, kmax, dtype, q):
 
 
 @pytest.mark.parametrize("world,X,Y,K,kmax,dtype", [(2, 40, 50, 7, 3, "float32"), (3, 61, 140, 5, 2, "float32"),
-                                                     (2, 36, 40, 4, 4, "float64")])
+                                                     (2, 36, 40, 4, 4, "float64"), (3, 200, 420, 12, 5, "float32"),
+                                                     (4, 130, 300, 9, 4, "float32")])
 def test_gloo_slabs_bit_identical_to_oracle(world, X, Y, K, kmax, dtype):
     H.build_emu()
     S = 2
