@@ -47,21 +47,6 @@ namespace fb {
 // ---------------------------------------------------------------------------------------
 template <typename T> struct Ar;
 
-// float -> double by integer repacking: exact for normal floats and (signed) zero; the caller
-// routes subnormal / inf / nan inputs to the exact path. Keeps the conversion off the XU pipe,
-// which the rounding double -> float conversions already load.
-FB_DEV double f2d_normal(unsigned bits) {
-    const unsigned ab = bits & 0x7fffffffu;
-    const unsigned hi_n = (bits & 0x80000000u) | ((ab >> 3) + 0x38000000u);
-    const unsigned hi = (ab == 0u) ? bits : hi_n;
-    return __hiloint2double((int)hi, (int)(bits << 29));
-}
-// true for subnormal, inf and nan bit patterns (NOT for zero)
-FB_DEV bool f32_special(unsigned bits) {
-    const unsigned ab = bits & 0x7fffffffu;
-    return ab != 0u && (ab - 0x00800000u) >= 0x7f000000u;
-}
-
 // The two divisions of the path come in three flavours, selected by MODE (Metric::mode):
 //   DIV_EXACT  the reference's operations literally (IEEE divisions);
 //   DIV_FAST   a division-free evaluation that is provably equal except for inputs it flags in
@@ -82,8 +67,8 @@ template <> struct Ar<float> {
     // DIV_FAST: q~ = (double)d * RN64(1/h2) is within 2^-52 (relative) of d/h2, while the quotient
     // of two 24-bit floats is never closer than ~2^-49 (relative) to a rounding boundary of a
     // NORMAL float result, so RN32(q~) is the correctly rounded quotient. Results in or near the
-    // subnormal range (coarser, absolute rounding grid; exact ties are possible) and special
-    // inputs are flagged. The cost is data independent, unlike __fdiv_rn whose slow path the
+    // subnormal range (coarser, absolute rounding grid; exact ties are possible) are
+    // flagged. The cost is data independent, unlike __fdiv_rn whose slow path the
     // mostly-zero fields of an impulsively started cavity hit all the time.
     // DIV_POW2: d * (1/h2) is the same real number as d / h2 and is rounded once, like the division.
     template <int MODE>
@@ -92,9 +77,9 @@ template <> struct Ar<float> {
         const float d = __fsub_rn(a, b);
         if (MODE == DIV_EXACT) return __fdiv_rn(d, h2);
         if (MODE == DIV_POW2) return __fmul_rn(d, inv_h2f);
-        const unsigned bits = __float_as_uint(d);
-        const float r = __double2float_rn(__dmul_rn(f2d_normal(bits), inv_h2));
-        bad |= f32_special(bits) || ((bits << 1) != 0u && fabsf(r) < 7.52316385e-37f /* 2^-120 */);
+        // (float -> double is exact for every input, subnormals included; inf/nan propagate like the division)
+        const float r = __double2float_rn(__dmul_rn((double)d, inv_h2));
+        bad |= (d != 0.0f) && (fabsf(r) < 7.52316385e-37f /* 2^-120 */);
         return r;
     }
     // (s - 4.*c) / hx / hy with s already rounded to float: the one place the fp32 path is
@@ -125,13 +110,12 @@ template <> struct Ar<float> {
             bad |= (ta != 0u) && ((ta - 0x03800000u) >= 0x78000000u || (ra - 0x03800000u) >= 0x78000000u);
             return r;
         }
-        const unsigned sb = __float_as_uint(s), cb = __float_as_uint(c);
-        const double d = __fma_rn(-4.0, f2d_normal(cb), f2d_normal(sb));
+        const double d = __fma_rn(-4.0, (double)c, (double)s);
         const double q = __dmul_rn(d, inv_hxhy);
         const float r = __double2float_rn(q);
+        // distance of the 29 sub-float bits of q from the midpoint pattern, as one unsigned compare
         const unsigned low = (unsigned)__double2loint(q) & 0x1fffffffu;
-        const unsigned dist = (low > 0x10000000u) ? low - 0x10000000u : 0x10000000u - low;
-        bad |= dist <= 16u || f32_special(sb) || f32_special(cb) || (fabsf(r) < 7.52316385e-37f && d != 0.0);
+        bad |= (low - 0x0ffffff0u) <= 32u || (fabsf(r) < 7.52316385e-37f && d != 0.0);
         return r;
     }
     // t *= -0.25 : the double multiply is exact, so this is one float rounding (subnormals).
