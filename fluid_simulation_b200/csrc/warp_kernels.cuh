@@ -440,10 +440,14 @@ FB_DEV void jacobi_task(const JacobiArgs<T>& A, int strip, int chunk, int lane, 
         if (r >= r_begin && r < load_hi && r >= 1 && r <= X - 2) return ld_ro<T, V>(rin + (long long)r * g.pitch);
         return vzero<T, V>();
     };
-    // (rhs * hx) * hy, SerialNavierStokes.cpp:144 -- once per row, reused by all K levels
+    // (rhs * hx) * hy, SerialNavierStokes.cpp:144 -- once per row, reused by all K levels; with unit
+    // spacing both multiplications are by 1 and exact, so they are skipped (warp-uniform branch)
+    const bool scale_b = !(A.hx == T(1) && A.hy == T(1));
     auto push_b = [&](VT bnew) {
+        if (scale_b) {
 #pragma unroll
-        for (int e = 0; e < V; ++e) bnew.a[e] = A_::mul(A_::mul(bnew.a[e], A.hx), A.hy);
+            for (int e = 0; e < V; ++e) bnew.a[e] = A_::mul(A_::mul(bnew.a[e], A.hx), A.hy);
+        }
 #pragma unroll
         for (int t = K - 1; t > 0; --t) bw[t] = bw[t - 1];
         bw[0] = bnew;
@@ -458,6 +462,7 @@ FB_DEV void jacobi_task(const JacobiArgs<T>& A, int strip, int chunk, int lane, 
     const int fast_lo = max(r_begin, K + 2);
     int nfast = min(r_end, X - 2) - fast_lo + 1;
     if (MASK || y_edges || nfast < 0) nfast = 0;
+    if ((long long)(load_hi - r_begin + 1) * g.pitch >= (1LL << 31)) nfast = 0;  // 32-bit offsets in the fast loop
     nfast -= nfast % U;
     const int fast_hi = fast_lo + nfast - 1;
 
@@ -527,6 +532,14 @@ FB_DEV void jacobi_task(const JacobiArgs<T>& A, int strip, int chunk, int lane, 
         const int pmax = load_hi - 1, bmax = min(load_hi - 1, X - 2);
         LaneRing<T, V, D> ring;
         ring.init(tid, nthreads);
+        // Addresses inside the loop are 32-bit element offsets from row r_begin of this chunk (the
+        // host keeps a chunk below 2^31 elements), advanced by one pitch per step and clamped.
+        const T* pbase = pin + (long long)r_begin * g.pitch;
+        const T* bbase = rin + (long long)r_begin * g.pitch;
+        T* obase = pout + (long long)r_begin * g.pitch;
+        const unsigned pitch32 = (unsigned)g.pitch;
+        const unsigned pmax_off = (unsigned)(pmax - r_begin) * pitch32;
+        const unsigned bmax_off = (unsigned)(bmax - r_begin) * pitch32;
 #pragma unroll
         for (int j = 0; j < D; ++j) {
             ring.fetch(j, 0, pin + (long long)min(r + j, pmax) * g.pitch);
@@ -534,6 +547,9 @@ FB_DEV void jacobi_task(const JacobiArgs<T>& A, int strip, int chunk, int lane, 
             ring.commit();
         }
         (void)nxt_p; (void)nxt_b;  // the ring re-reads rows r and r-1; the register copies are dropped
+        unsigned poff = (unsigned)(min(r + D, pmax) - r_begin) * pitch32;          // next p row to fetch
+        unsigned boff = (unsigned)(min(r + D - 1, bmax) - r_begin) * pitch32;      // next rhs row to fetch
+        int soff = (r - K - r_begin) * (int)pitch32;                               // row stored by this step
         const int first_store = c0 + K;  // step at which level K reaches row c0
         int sbase = 0;                   // ring slot of step r (advances by U per iteration, mod D)
 #pragma unroll 1
@@ -544,9 +560,11 @@ FB_DEV void jacobi_task(const JacobiArgs<T>& A, int strip, int chunk, int lane, 
                 ring.template wait<D - 1>();          // the oldest group = this step's rows has landed
                 VT cur = ring.read(slot, 0);
                 push_b(ring.read(slot, 1));
-                ring.fetch(slot, 0, pin + (long long)min(r + u + D, pmax) * g.pitch);
-                ring.fetch(slot, 1, rin + (long long)min(r + u + D - 1, bmax) * g.pitch);
+                ring.fetch(slot, 0, pbase + poff);
+                ring.fetch(slot, 1, bbase + boff);
                 ring.commit();
+                poff = min(poff + pitch32, pmax_off);
+                boff = min(boff + pitch32, bmax_off);
 #pragma unroll
                 for (int t = 1; t <= K; ++t) {
                     const VT out = jacobi_row<T, V>(w[t - 1][0], w[t - 1][1], cur, bw[t - 1]);
@@ -554,7 +572,8 @@ FB_DEV void jacobi_task(const JacobiArgs<T>& A, int strip, int chunk, int lane, 
                     w[t - 1][1] = cur;
                     cur = out;
                 }
-                if (st.st_ok && r + u >= first_store) st_vec<T, V>(pout + (long long)(r + u - K) * g.pitch, cur);
+                if (st.st_ok && r + u >= first_store) st_vec<T, V>(obase + soff, cur);
+                soff += (int)pitch32;
             }
             if (D != U) sbase = (sbase + U) % D;
         }

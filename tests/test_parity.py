@@ -204,3 +204,19 @@ def test_division_modes_agree_with_the_reference(Solver, env, X, Y, divmode):
     o.solve()
     H.compare_with(s, o, tag=f"divmode{divmode}/{X}x{Y}")
     s.close()
+
+
+@pytest.mark.parametrize("kmax", [2, 5])
+def test_unit_spacing(Solver, kmax):
+    """domain = (X-1, Y-1) => hx = hy = 1: the benchmark's spacing (power-of-two arithmetic mode, and
+    the Jacobi kernel skips the exact multiplications of rhs by hx and hy)."""
+    X, Y = 48, 300
+    o = Oracle(X, Y, float(X - 1), float(Y - 1)).set_cavity()
+    o.time_step, o.num_iterations, o.num_poisson_iterations = 0.001, 3, 7
+    s = Solver(X, Y, float(X - 1), float(Y - 1)).set_cavity()
+    s.time_step, s.num_iterations, s.num_poisson_iterations = 0.001, 3, 7
+    s.set_sweeps_per_launch(kmax)
+    s.migrateSolve()
+    o.solve()
+    H.compare_with(s, o, tag=f"unit/k{kmax}")
+    s.close()
