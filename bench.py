@@ -208,8 +208,17 @@ def run_single(args):
     alg_bytes = 12.0 * cells * KMAX
     achieved = alg_bytes / (jac_launch_ms * 1e-3) / 1e9
     peak, peak_src = peaks()
-    roofline = {"bound": "hbm", "kernel": f"jacobi_kernel<float,4,{KMAX},false>", "achieved": achieved, "peak": peak,
-                "unit": "GB/s", "frac": achieved / peak, "traffic": None,
+    kernel = f"jacobi_kernel<float,4,{KMAX},false>"
+    traffic = None   # ncu dram bytes per launch for exactly this kernel and grid, when a capture is on file
+    try:
+        with open(os.path.join(ROOT, "profiles", "ncu_traffic_r1.json")) as f:
+            traffic = json.load(f).get(f"{kernel}@{X}x{Y}")
+    except Exception:
+        pass
+    roofline = {"bound": "hbm", "kernel": kernel, "achieved": achieved, "peak": peak,
+                "unit": "GB/s", "frac": achieved / peak, "traffic": traffic,
+                "dram_GBps": traffic / (jac_launch_ms * 1e-3) / 1e9 if traffic else None,
+                "dram_frac": traffic / (jac_launch_ms * 1e-3) / 1e9 / peak if traffic else None,
                 "peak_source": peak_src, "sweeps_per_launch": KMAX,
                 "launch_ms": jac_launch_ms, "algorithmic_bytes_per_launch": alg_bytes,
                 "gcell_sweeps_per_s": cells * SWEEPS * args.steps / (jac_ms * 1e-3) / 1e9,
@@ -284,6 +293,8 @@ def run_single(args):
         "dtype": "f32", "data": "synthetic",
         "config": {"workload": f"cavity {X}x{Y} fp32, {SWEEPS} Poisson sweeps/step, 1 GPU (BASELINE.json configs[2])",
                    "dt": DT, "nu": NU, "rho": RHO, "hx": 1.0, "hy": 1.0, "sweeps_per_launch": KMAX,
+                   "division_mode": os.environ.get("FLUIDB200_DIVMODE", "2 (power-of-two spacing: exact scalings; "
+                                                   "FLUIDB200_DIVMODE=1 forces the general division-free mode)"),
                    "l2": "fields are 1.07 GB each, >> 126 MB L2, no flush needed",
                    "effective_GBps_step": (40 + 12 * SWEEPS) * cells * args.steps / (total_ms * 1e-3) / 1e9},
         "roofline": roofline, "cpu_baseline": cdesc, "e2e": e2e, "gpu_launches": int(launches), "clocks": clk,

@@ -39,7 +39,7 @@ template <typename T, int V, int MODE>
 __global__ void __launch_bounds__(kThreads) predictor_kernel(const __grid_constant__ fb::PredictorArgs<T> A) {
     const int strip = blockIdx.x * fb::kWarpsPerCta + (threadIdx.x >> 5);
     if (strip >= A.g.nstrips) return;
-    fb::predictor_task<T, V, MODE>(A, strip, blockIdx.y, threadIdx.x & 31);
+    fb::predictor_task<T, V, MODE>(A, strip, blockIdx.y, threadIdx.x & 31, threadIdx.x, kThreads);
 }
 
 template <typename T, int V, bool MASK, int MODE>
@@ -162,9 +162,10 @@ template <typename T> int launch_predictor(const fb::PredictorArgs<T>& a, int nc
     const dim3 grid = grid_for(a.g.nstrips, nchunks);
     cudaStream_t st = (cudaStream_t)stream;
     // the arithmetic mode is a compile-time property of the kernel (see Metric::mode); fp64 has only mode 0
-    if (sizeof(T) == 4 && a.m.mode == 2) predictor_kernel<T, V, (sizeof(T) == 4 ? 2 : 0)><<<grid, kThreads, 0, st>>>(a);
-    else if (sizeof(T) == 4 && a.m.mode == 1) predictor_kernel<T, V, (sizeof(T) == 4 ? 1 : 0)><<<grid, kThreads, 0, st>>>(a);
-    else predictor_kernel<T, V, 0><<<grid, kThreads, 0, st>>>(a);
+    const size_t smem = (size_t)4 * 2 * 16 * kThreads;  // per-lane cp.async ring: 4 slots x {u, v} x 16 B
+    if (sizeof(T) == 4 && a.m.mode == 2) predictor_kernel<T, V, (sizeof(T) == 4 ? 2 : 0)><<<grid, kThreads, smem, st>>>(a);
+    else if (sizeof(T) == 4 && a.m.mode == 1) predictor_kernel<T, V, (sizeof(T) == 4 ? 1 : 0)><<<grid, kThreads, smem, st>>>(a);
+    else predictor_kernel<T, V, 0><<<grid, kThreads, smem, st>>>(a);
     return rc_of(cudaGetLastError());
 }
 

@@ -696,7 +696,7 @@ FB_DEV Vec<T, V> rhs_row(const PredictorArgs<T>& A, const Vec<T, V>& us_m, const
 // right-hand side of row r-2 (it needs u_next of rows r-3 and r-1). Interior strips away from the
 // box walls take the FAST path (2 steps per iteration, no range checks).
 template <typename T, int V, int MODE>
-FB_DEV void predictor_task(const PredictorArgs<T>& A, int strip, int chunk, int lane) {
+FB_DEV void predictor_task(const PredictorArgs<T>& A, int strip, int chunk, int lane, int tid, int nthreads) {
     constexpr int H = 4;
     using VT = Vec<T, V>;
     const Geom& g = A.g;
@@ -798,24 +798,32 @@ FB_DEV void predictor_task(const PredictorArgs<T>& A, int strip, int chunk, int 
         if (phase == 1 || nfast == 0) break;
         // ---------------- FAST path ----------------
         const int pmax = load_hi - 1;
-        VT pfu[U], pfv[U];
-        pfu[0] = nu_;
-        pfv[0] = nv_;
+        // rows of u and v are prefetched D steps ahead through the per-lane cp.async ring
+        constexpr int D = 4;
+        static_assert(D % U == 0, "ring depth must be a multiple of the unroll factor");
+        LaneRing<T, V, D> ring;
+        ring.init(tid, nthreads);
 #pragma unroll
-        for (int k = 1; k < U; ++k) {
-            pfu[k] = ld_ro<T, V>(up + (long long)min(r + k, pmax) * g.pitch);
-            pfv[k] = ld_ro<T, V>(vp + (long long)min(r + k, pmax) * g.pitch);
+        for (int j = 0; j < D; ++j) {
+            ring.fetch(j, 0, up + (long long)min(r + j, pmax) * g.pitch);
+            ring.fetch(j, 1, vp + (long long)min(r + j, pmax) * g.pitch);
+            ring.commit();
         }
         T* uso = A.us + sbase;
         T* vso = A.vs + sbase;
         T* rho = A.rhs + sbase;
+        int ring_pos = 0;
 #pragma unroll 1
         for (; r <= fast_hi; r += U) {
 #pragma unroll
             for (int k = 0; k < U; ++k) {
-                const VT cu = pfu[k], cv = pfv[k];
-                pfu[k] = ld_ro<T, V>(up + (long long)min(r + k + U, pmax) * g.pitch);
-                pfv[k] = ld_ro<T, V>(vp + (long long)min(r + k + U, pmax) * g.pitch);
+                const int slot = ring_pos + k;
+                ring.template wait<D - 1>();
+                const VT cu = ring.read(slot, 0), cv = ring.read(slot, 1);
+                const long long nxt = (long long)min(r + k + D, pmax) * g.pitch;
+                ring.fetch(slot, 0, up + nxt);
+                ring.fetch(slot, 1, vp + nxt);
+                ring.commit();
                 VT us, vs;
                 tentative_row<T, V, MODE>(A, wu[0], wu[1], cu, wv[0], wv[1], cv, us, vs);
                 const int ra = r + k - 1, rb = r + k - 2;
@@ -830,9 +838,11 @@ FB_DEV void predictor_task(const PredictorArgs<T>& A, int strip, int chunk, int 
                 wus[0] = wus[1]; wus[1] = us;
                 wvs = vs;
             }
+            ring_pos = (ring_pos + U) % D;
         }
-        nu_ = pfu[0];
-        nv_ = pfv[0];
+        ring.template wait<0>();
+        nu_ = (r < load_hi) ? ring.read(ring_pos, 0) : vzero<T, V>();
+        nv_ = (r < load_hi) ? ring.read(ring_pos, 1) : vzero<T, V>();
     }
 }
 

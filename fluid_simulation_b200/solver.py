@@ -230,6 +230,29 @@ class ParallelNavierStokes:
     def getPNext(self, output=None):
         return self._get("p_next", output)
 
+    # -- raw dumps, as the reference's drivers write them -------------------------------------
+    def write_dat(self, prefix="Cuda", directory="."):
+        """Write ``{prefix}UValues.float.dat`` / ``VValues`` / ``PValues``: raw little-endian values in
+        getter order (``i = x*Y + y``), the files ``fluid_cpp/cuda_main.cu:69-80`` (prefix ``Cuda``) and
+        ``fluid_cpp/main.cpp:68-78`` (prefix ``Cpp``) produce and ``figures/plot_c_time_data.ipynb``
+        reads. Host state is written, so call ``migrateDeviceToHost()`` first, like the getters.
+        The file name keeps the reference's ``.float.dat`` suffix for fp32 and uses ``.double.dat``
+        for fp64. Returns the three paths."""
+        import os
+        suffix = "float" if self.dtype == np.float32 else "double"
+        paths = []
+        for letter, name in (("U", "u"), ("V", "v"), ("P", "p")):
+            path = os.path.join(directory, f"{prefix}{letter}Values.{suffix}.dat")
+            self._hostf(name).astype(self.dtype.newbyteorder("<"), copy=False).tofile(path)
+            paths.append(path)
+        return paths
+
+    @staticmethod
+    def read_dat(path, num_x_bins, num_y_bins, dtype=np.float32):
+        """Load one such file as an ``(X, Y)`` array (``.T`` gives the ``[y, x]`` orientation of the
+        reference's NumPy solver and of its notebook, cell 6)."""
+        return np.fromfile(path, dtype=np.dtype(dtype).newbyteorder("<")).reshape(num_x_bins, num_y_bins)
+
 
 class TiledNavierStokes(ParallelNavierStokes):
     """Drop-in for ``TiledNavierStokes<T>`` (``fluid_cpp/cuda/TiledNavierStokes.cuh:10-23``).

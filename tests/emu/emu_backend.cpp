@@ -152,9 +152,9 @@ template <typename T> int launch_predictor(const fb::PredictorArgs<T>& a, int nc
     constexpr int V = fb::VecWidth<T>::V;
     set_ranges({a.u, a.v, a.us, a.vs, a.rhs}, (size_t)a.g.rows * a.g.pitch * sizeof(T));
     const int mode = sizeof(T) == 4 ? a.m.mode : 0;
-    if (mode == 2) run_grid(a.g.nstrips, nchunks, [&](int s, int c, int l) { fb::predictor_task<T, V, (sizeof(T) == 4 ? 2 : 0)>(a, s, c, l); });
-    else if (mode == 1) run_grid(a.g.nstrips, nchunks, [&](int s, int c, int l) { fb::predictor_task<T, V, (sizeof(T) == 4 ? 1 : 0)>(a, s, c, l); });
-    else run_grid(a.g.nstrips, nchunks, [&](int s, int c, int l) { fb::predictor_task<T, V, 0>(a, s, c, l); });
+    if (mode == 2) run_grid(a.g.nstrips, nchunks, [&](int s, int c, int l) { fb::predictor_task<T, V, (sizeof(T) == 4 ? 2 : 0)>(a, s, c, l, l, 32); });
+    else if (mode == 1) run_grid(a.g.nstrips, nchunks, [&](int s, int c, int l) { fb::predictor_task<T, V, (sizeof(T) == 4 ? 1 : 0)>(a, s, c, l, l, 32); });
+    else run_grid(a.g.nstrips, nchunks, [&](int s, int c, int l) { fb::predictor_task<T, V, 0>(a, s, c, l, l, 32); });
     return 0;
 }
 template <typename T> int launch_corrector(const fb::CorrectorArgs<T>& a, bool mask, int nchunks, void*) {

@@ -220,3 +220,19 @@ def test_unit_spacing(Solver, kmax):
     o.solve()
     H.compare_with(s, o, tag=f"unit/k{kmax}")
     s.close()
+
+
+def test_raw_dat_dumps_follow_the_reference_layout(Solver, golden, tmp_path):
+    """`Cuda{U,V,P}Values.float.dat` as written by fluid_cpp/cuda_main.cu:69-80: raw little-endian
+    fp32 in getter order, re-indexed by the reference's notebook as data[j*N + i] -> [i, j]."""
+    rec = dict(golden["cavity41_S3_K7"])
+    s = H.golden_case_setup(rec, Solver)
+    s.migrateSolve()
+    paths = s.write_dat("Cuda", str(tmp_path))
+    want = H.load_fields(golden["cavity41_S3_K7"])
+    for path, n in zip(paths, ("u", "v", "p")):
+        raw = np.fromfile(path, dtype="<f4")
+        assert raw.size == 41 * 41
+        H.assert_bit_equal(raw.reshape(41, 41), want[n], n)
+        H.assert_bit_equal(type(s).read_dat(path, 41, 41), want[n], n)
+    s.close()
