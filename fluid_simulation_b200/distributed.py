@@ -80,8 +80,9 @@ class SlabSolver:
         if self.on_gpu:
             self.main = torch.cuda.current_stream(self.device)
             self.comm = torch.cuda.Stream(self.device)
+            self.edge = torch.cuda.Stream(self.device, priority=-1)   # edge strips jump the queue
         else:
-            self.main = self.comm = None
+            self.main = self.comm = self.edge = None
         self._set_edges(1.0)
 
     # ------------------------------------------------------------------------------------------
@@ -153,11 +154,12 @@ class SlabSolver:
             self._ptr("rhs"), dt, nu, rho, star_lo, star_hi, rhs_lo, rhs_hi, self._stream()))
         self.launches += 1
 
-    def _sweeps(self, k, lo, hi):
+    def _sweeps(self, k, lo, hi, stream=None):
         """k sweeps: reads f['p'], writes global rows [lo, hi) of f['p_next']."""
+        st = self._stream() if stream is None else C.c_void_p(stream.cuda_stream)
         _lib.check(self.lib, self.lib.fluidb200_poisson_sweeps(
             C.byref(self.slab), self._ptr("p"), self._ptr("p_next"), self._ptr("rhs"), C.byref(self.edges["p"]),
-            None, k, lo, hi, self._stream()))
+            None, k, lo, hi, st))
         self.launches += 1
 
     def _swap_p(self):
@@ -183,25 +185,29 @@ class SlabSolver:
                 self.exchange(["p_next"], d)
                 self._swap_p()
                 continue
-            # 1. the d-row strips the neighbours are waiting for (none on a wall side)
+            # Three independent pieces of one sweep launch: all read f['p'], write disjoint rows of f['p_next'].
+            # 1. the d-row strips the neighbours are waiting for (none on a wall side), on a HIGH-PRIORITY
+            #    stream so their few CTAs are scheduled ahead of the interior's
             lo_strip = (x0, x0 + d) if self.rank > 0 else None
             hi_strip = (x1 - d, x1) if self.rank < self.world - 1 else None
+            start = torch.cuda.Event()
+            start.record(self.main)
+            self.edge.wait_event(start)
             for strip in (lo_strip, hi_strip):
                 if strip:
-                    self._sweeps(k, *strip)
+                    self._sweeps(k, *strip, stream=self.edge)
             ready = torch.cuda.Event()
-            ready.record(self.main)
-            # 2. ship them on the communication stream ...
+            ready.record(self.edge)
+            # 2. the interior of the owned range, concurrently, on the main stream
+            self._sweeps(k, lo_strip[1] if lo_strip else x0, hi_strip[0] if hi_strip else x1)
+            # 3. ship the strips on the communication stream while the interior runs
             self.comm.wait_event(ready)
             with torch.cuda.stream(self.comm):
                 works = self._post_exchange(["p_next"], d)
-            # 3. ... while the interior of the owned range is swept on the main stream
-            self._sweeps(k, lo_strip[1] if lo_strip else x0, hi_strip[0] if hi_strip else x1)
-            with torch.cuda.stream(self.comm):
                 self._wait(works)
                 done = torch.cuda.Event()
                 done.record(self.comm)
-            self.main.wait_event(done)
+            self.main.wait_event(done)   # (comm waited for `ready`, so the strips are complete too)
             self._swap_p()
 
     def corrector(self):
