@@ -115,3 +115,23 @@ def test_cuda_graph_replay_matches_plain_launches(Solver, golden):
         H.compare_with(a, {n: b._hostf(n) for n in H.ALL_FIELDS}, tag=f"graph/K{K}")
         assert a.launch_count() == b.launch_count()
         a.close(); b.close()
+
+
+def _random_cases(n, seed, lo, hi):
+    rng = np.random.default_rng(seed)
+    return [(int(rng.integers(lo, hi)), int(rng.integers(lo, hi)), int(rng.integers(1, 24)), int(rng.integers(1, 9)))
+            for _ in range(n)]
+
+
+@pytest.mark.parametrize("X,Y,K,kmax", _random_cases(12, 7, 130, 1500))
+def test_random_shapes_gpu(Solver, X, Y, K, kmax):
+    """Non-multiple-of-tile shapes between 130 and 1500 per side, random sweep counts and depths."""
+    o = Oracle(X, Y).set_cavity()
+    o.time_step, o.num_iterations, o.num_poisson_iterations = 1e-6, 2, K
+    s = Solver(X, Y).set_cavity()
+    s.time_step, s.num_iterations, s.num_poisson_iterations = 1e-6, 2, K
+    s.set_sweeps_per_launch(kmax)
+    s.migrateSolve()
+    o.solve()
+    H.compare_with(s, o, tag=f"random/{X}x{Y}/K{K}/k{kmax}")
+    s.close()

@@ -236,3 +236,26 @@ def test_raw_dat_dumps_follow_the_reference_layout(Solver, golden, tmp_path):
         H.assert_bit_equal(raw.reshape(41, 41), want[n], n)
         H.assert_bit_equal(type(s).read_dat(path, 41, 41), want[n], n)
     s.close()
+
+
+def _random_cases(n, seed, max_dim):
+    rng = np.random.default_rng(seed)
+    out = []
+    for _ in range(n):
+        X = int(rng.integers(3, max_dim)); Y = int(rng.integers(3, max_dim))
+        out.append((X, Y, int(rng.integers(1, 14)), int(rng.integers(1, 9)), ["float32", "float64"][int(rng.integers(0, 2))]))
+    return out
+
+
+@pytest.mark.parametrize("X,Y,K,kmax,dtype", _random_cases(10, 2024, 260))
+def test_random_shapes(Solver, X, Y, K, kmax, dtype):
+    """Odd, tiny and non-multiple-of-tile shapes (3 <= X, Y < 260), random depth and blocking."""
+    o = Oracle(X, Y, dtype=np.dtype(dtype)).set_cavity()
+    o.time_step, o.num_iterations, o.num_poisson_iterations = 1e-5, 2, K
+    s = Solver(X, Y, dtype=np.dtype(dtype)).set_cavity()
+    s.time_step, s.num_iterations, s.num_poisson_iterations = 1e-5, 2, K
+    s.set_sweeps_per_launch(kmax)
+    s.migrateSolve()
+    o.solve()
+    H.compare_with(s, o, tag=f"random/{X}x{Y}/K{K}/k{kmax}/{dtype}")
+    s.close()
