@@ -177,6 +177,40 @@ int predictor_t(const fluidb200_slab* g, const void* u, const void* v, void* us,
     return 0;
 }
 
+// Decide which tasks of a Jacobi launch may go to the lean FAST kernel (jacobi_fast_task): every
+// step of such a task must be a fast step, i.e.
+//   strips [sf_lo, sf_hi): no y-edge column inside the strip's 32*V loaded columns;
+//   chunks [cf_lo, cf_hi): pipeline starts at c0-K >= max(row0, K+2) and ends at c1-1+K <= X-2,
+//                          and the chunk spans fewer than 2^31 elements (32-bit running offsets).
+// Everything else (walls, edge strips) stays with the general kernel. part = 1 asks the backend for
+// the split launch, part = 0 for the single general kernel.
+template <typename T>
+void split_jacobi(fb::JacobiArgs<T>* a, const fluidb200_slab* g, int K, int nchunks, bool use_mask) {
+    a->part = 0;
+    a->nchunks = nchunks;
+    a->sf_lo = a->sf_hi = a->cf_lo = a->cf_hi = 0;
+    if (use_mask || env_int("FLUIDB200_NO_SPLIT", 0)) return;
+    const int W = 32 * vec_width<T>(), S = W - 2 * halo_cols(K);
+    const int nstrips = a->g.nstrips, rpc = a->g.rows_per_chunk;
+    int sf_lo = 1, sf_hi = 1;
+    while (sf_hi < nstrips && sf_hi * S + W <= g->Y - 1) ++sf_hi;  // strip sf_hi is the first that holds column Y-1
+    int cf_lo = nchunks, cf_hi = 0;
+    for (int c = 0; c < nchunks; ++c) {
+        const int c0 = a->out_lo + c * rpc, c1 = std::min(c0 + rpc, a->out_hi);
+        const bool ok = c0 - K >= std::max(g->row0, K + 2) && c1 - 1 + K <= g->X - 2 &&
+                        (long long)(c1 - c0 + 2 * K + 1) * g->pitch < (1LL << 31);
+        if (ok) {
+            cf_lo = std::min(cf_lo, c);
+            cf_hi = std::max(cf_hi, c + 1);
+        } else if (cf_hi > 0) {
+            break;  // fast chunks are one contiguous run
+        }
+    }
+    if (sf_hi - sf_lo < 1 || cf_hi - cf_lo < 1) return;
+    a->part = 1;
+    a->sf_lo = sf_lo; a->sf_hi = sf_hi; a->cf_lo = cf_lo; a->cf_hi = cf_hi;
+}
+
 template <typename T>
 int poisson_t(const fluidb200_slab* g, const void* p_in, void* p_out, const void* rhs,
               const fluidb200_edges* e, const fluidb200_mask* mask, int sweeps, int out_lo, int out_hi,
@@ -191,8 +225,10 @@ int poisson_t(const fluidb200_slab* g, const void* p_in, void* p_out, const void
     a.e = to_dev_edges<T>(e);
     const int nstrips = num_strips<T>(g->Y, halo_cols(sweeps));
     int rpc, nchunks;
-    plan_chunks(out_hi - out_lo, sweeps, nstrips, sweeps <= 2 ? 5 : sweeps <= 4 ? 4 : sweeps <= 6 ? 3 : 2, kJacobiTasks, &rpc, &nchunks);
+    // resident CTAs per SM of the kernel that does the bulk of the work (the lean FAST kernel)
+    plan_chunks(out_hi - out_lo, sweeps, nstrips, sweeps <= 2 ? 5 : sweeps <= 5 ? 4 : 3, kJacobiTasks, &rpc, &nchunks);
     a.g = make_geom(g, nstrips, rpc);
+    split_jacobi<T>(&a, g, sweeps, nchunks, use_mask);
     BE_CHECK(fbk::launch_jacobi<T>(a, sweeps, use_mask, nchunks, stream), "poisson launch");
     return 0;
 }

@@ -30,9 +30,21 @@ constexpr int kThreads = fb::kWarpsPerCta * 32;
 #endif
 template <typename T, int V, int K, bool MASK>
 __global__ void __launch_bounds__(kThreads, FLUIDB200_JACOBI_MIN_BLOCKS(K)) jacobi_kernel(const __grid_constant__ fb::JacobiArgs<T> A) {
-    const int strip = blockIdx.x * fb::kWarpsPerCta + (threadIdx.x >> 5);
-    if (strip >= A.g.nstrips) return;  // whole warps only; the tasks use no block barrier
-    fb::jacobi_task<T, V, K, MASK>(A, strip, blockIdx.y, threadIdx.x & 31, threadIdx.x, kThreads);
+    int strip, chunk;  // whole warps only; the tasks use no block barrier
+    if (!fb::jacobi_decode_task(A, (int)blockIdx.x, (int)blockIdx.y, (int)(threadIdx.x >> 5), fb::kWarpsPerCta, &strip, &chunk)) return;
+    fb::jacobi_task<T, V, K, MASK>(A, strip, chunk, threadIdx.x & 31, threadIdx.x, kThreads);
+}
+
+// The lean twin (see jacobi_fast_task): without the general path it needs fewer registers, so it
+// is compiled for one more resident CTA per SM than jacobi_kernel.
+#ifndef FLUIDB200_JACOBI_FAST_MIN_BLOCKS
+#define FLUIDB200_JACOBI_FAST_MIN_BLOCKS(K) ((K) <= 2 ? 5 : (K) <= 5 ? 4 : 3)
+#endif
+template <typename T, int V, int K>
+__global__ void __launch_bounds__(kThreads, FLUIDB200_JACOBI_FAST_MIN_BLOCKS(K)) jacobi_fast_kernel(const __grid_constant__ fb::JacobiArgs<T> A) {
+    int strip, chunk;
+    if (!fb::jacobi_decode_task(A, (int)blockIdx.x, (int)blockIdx.y, (int)(threadIdx.x >> 5), fb::kWarpsPerCta, &strip, &chunk)) return;
+    fb::jacobi_fast_task<T, V, K>(A, strip, chunk, threadIdx.x & 31, threadIdx.x, kThreads);
 }
 
 template <typename T, int V, int MODE>
@@ -69,14 +81,61 @@ inline dim3 grid_for(int nstrips, int nchunks) {
     return dim3((unsigned)((nstrips + fb::kWarpsPerCta - 1) / fb::kWarpsPerCta), (unsigned)nchunks, 1);
 }
 
+// Side stream for the GENERAL part of a split Jacobi launch: forked from and joined back into the
+// caller's stream with events, high priority so that its few, long tasks start first and run
+// underneath the FAST kernel instead of after it. One per host thread and device.
+struct SideStream {
+    int device = -1;
+    cudaStream_t stream = nullptr;
+    cudaEvent_t fork = nullptr, join = nullptr;
+};
+SideStream* side_stream() {
+    static thread_local SideStream table[64];
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return nullptr;
+    SideStream& s = table[dev];
+    if (!s.stream) {
+        int lo = 0, hi = 0;
+        cudaDeviceGetStreamPriorityRange(&lo, &hi);  // hi = numerically smallest = highest priority
+        if (cudaStreamCreateWithPriority(&s.stream, cudaStreamNonBlocking, hi) != cudaSuccess ||
+            cudaEventCreateWithFlags(&s.fork, cudaEventDisableTiming) != cudaSuccess ||
+            cudaEventCreateWithFlags(&s.join, cudaEventDisableTiming) != cudaSuccess) {
+            s.stream = nullptr;
+            return nullptr;
+        }
+        s.device = dev;
+    }
+    return &s;
+}
+
 template <typename T, int K> int launch_jacobi_k(const fb::JacobiArgs<T>& a, bool mask, int nchunks, cudaStream_t st) {
     constexpr int V = fb::VecWidth<T>::V;
-    const dim3 grid = grid_for(a.g.nstrips, nchunks);
     // dynamic shared memory: the per-lane cp.async prefetch ring (D slots x 2 arrays x 16 B per thread)
     const size_t smem = (size_t)fb::JacobiRing<K>::D * 2 * 16 * kThreads;
-    if (K == 1 && mask) jacobi_kernel<T, V, 1, true><<<grid, kThreads, smem, st>>>(a);
-    else jacobi_kernel<T, V, K, false><<<grid, kThreads, smem, st>>>(a);
-    return rc_of(cudaGetLastError());
+    SideStream* side = (a.part != 0 && !mask) ? side_stream() : nullptr;
+    if (!side) {  // one kernel does every task
+        fb::JacobiArgs<T> all = a;
+        all.part = 0;
+        const dim3 grid = grid_for(a.g.nstrips, nchunks);
+        if (K == 1 && mask) jacobi_kernel<T, V, 1, true><<<grid, kThreads, smem, st>>>(all);
+        else jacobi_kernel<T, V, K, false><<<grid, kThreads, smem, st>>>(all);
+        return rc_of(cudaGetLastError());
+    }
+    // split launch: GENERAL tasks on the side stream, FAST tasks on the caller's stream, then join
+    fb::JacobiArgs<T> gen = a, fast = a;
+    gen.part = 2;
+    fast.part = 1;
+    if (rc_of(cudaEventRecord(side->fork, st)) || rc_of(cudaStreamWaitEvent(side->stream, side->fork, 0))) return -1;
+    const int ngen = fb::jacobi_part2_tasks(gen);
+    if (ngen > 0) {
+        const dim3 ggrid((unsigned)((ngen + fb::kWarpsPerCta - 1) / fb::kWarpsPerCta), 1, 1);
+        jacobi_kernel<T, V, K, false><<<ggrid, kThreads, smem, side->stream>>>(gen);
+        if (rc_of(cudaGetLastError())) return -1;
+    }
+    if (rc_of(cudaEventRecord(side->join, side->stream))) return -1;
+    jacobi_fast_kernel<T, V, K><<<grid_for(a.sf_hi - a.sf_lo, a.cf_hi - a.cf_lo), kThreads, smem, st>>>(fast);
+    if (rc_of(cudaGetLastError())) return -1;
+    return rc_of(cudaStreamWaitEvent(st, side->join, 0));
 }
 
 }  // namespace

@@ -76,7 +76,54 @@ template <typename T> struct JacobiArgs {
     T hx, hy;
     int out_lo, out_hi;   // global rows to write
     Edges<T> e;
+    // Split launch (see JacobiSplit): a launch is cut into a lean FAST kernel over the tasks whose
+    // whole pipeline runs on plain interior rows/columns and a GENERAL kernel over the rest.
+    int part;             // 0 = one kernel does every task, 1 = fast tasks only, 2 = all other tasks
+    int sf_lo, sf_hi;     // strips [sf_lo, sf_hi) hold no y-edge column
+    int cf_lo, cf_hi;     // chunks [cf_lo, cf_hi) neither touch an x wall nor lack halo rows
+    int nchunks;
 };
+
+// Task decoding shared by the CUDA wrappers and the emulator. Returns false for padding threads.
+// part 1: grid (ceil((sf_hi-sf_lo)/W), cf_hi-cf_lo), warps = adjacent fast strips of one fast chunk.
+// part 2: one-dimensional list: first the edge strips x all chunks, then the fast strips x the
+//         remaining (wall) chunks.
+template <typename T>
+inline
+#ifdef __CUDACC__
+    __host__ __device__
+#endif
+    bool jacobi_decode_task(const JacobiArgs<T>& a, int bx, int by, int warp, int warps_per_cta, int* strip, int* chunk) {
+    if (a.part == 0) {
+        *strip = bx * warps_per_cta + warp;
+        *chunk = by;
+        return *strip < a.g.nstrips;
+    }
+    if (a.part == 1) {
+        *strip = a.sf_lo + bx * warps_per_cta + warp;
+        *chunk = a.cf_lo + by;
+        return *strip < a.sf_hi;
+    }
+    const int id = bx * warps_per_cta + warp;
+    const int E = a.sf_lo + (a.g.nstrips - a.sf_hi), C = a.nchunks;
+    if (id < E * C) {
+        const int e = id % E;
+        *strip = e < a.sf_lo ? e : a.sf_hi + (e - a.sf_lo);
+        *chunk = id / E;
+        return true;
+    }
+    const int id2 = id - E * C, Si = a.sf_hi - a.sf_lo, Cn = C - (a.cf_hi - a.cf_lo);
+    if (Si <= 0) return false;
+    const int ci = id2 / Si;
+    if (ci >= Cn) return false;
+    *strip = a.sf_lo + id2 % Si;
+    *chunk = ci < a.cf_lo ? ci : ci - a.cf_lo + a.cf_hi;
+    return true;
+}
+template <typename T> inline int jacobi_part2_tasks(const JacobiArgs<T>& a) {
+    const int E = a.sf_lo + (a.g.nstrips - a.sf_hi);
+    return E * a.nchunks + (a.sf_hi - a.sf_lo) * (a.nchunks - (a.cf_hi - a.cf_lo));
+}
 
 // Fused tentative velocity + right-hand side (see predictor_task)
 template <typename T> struct PredictorArgs {

@@ -587,6 +587,98 @@ FB_DEV void jacobi_task(const JacobiArgs<T>& A, int strip, int chunk, int lane, 
     }
 }
 
+// The FAST-ONLY twin of jacobi_task: same pipeline, same arithmetic, but compiled without any of
+// the general path (walls, y-edges, masks, range checks), which is what sets the register count
+// of jacobi_task (K=5: 149 -> 126 registers, K=8: 210 -> 168), i.e. one more resident CTA per SM.
+// The host (split_jacobi in api.cpp) only sends it tasks for which EVERY step is a fast step:
+// strip without a y-edge column, r_begin = c0-K >= max(row0, K+2), r_end = c1-1+K <= X-2.
+// The step count is rounded UP to a multiple of U; the extra steps read clamped rows and are
+// never stored.
+template <typename T, int V, int K>
+FB_DEV void jacobi_fast_task(const JacobiArgs<T>& A, int strip, int chunk, int lane, int tid, int nthreads) {
+    constexpr int H = (K + 3) & ~3;
+    constexpr int U = JacobiRing<K>::U, D = JacobiRing<K>::D;
+    static_assert(D % U == 0, "ring depth must be a multiple of the unroll factor");
+    using A_ = Ar<T>;
+    using VT = Vec<T, V>;
+    const Geom& g = A.g;
+    Strip<V, H> st;
+    st.init(g, strip, lane);
+    const int c0 = A.out_lo + chunk * g.rows_per_chunk;
+    const int c1 = min(c0 + g.rows_per_chunk, A.out_hi);
+    if (c0 >= c1) return;
+    const int r_begin = c0 - K;
+    const int load_hi = min(c1 + K, g.row0 + g.rows);
+    const int r_end = c1 - 1 + K;
+    const int pmax = load_hi - 1, bmax = min(load_hi - 1, g.X - 2);
+
+    const long long base = (long long)st.lcol + (long long)(r_begin - g.row0) * g.pitch;
+    const T* pbase = A.p_in + base;
+    const T* bbase = A.rhs + base;
+    T* obase = A.p_out + (long long)st.col0 + (long long)(r_begin - g.row0) * g.pitch;
+    const unsigned pitch32 = (unsigned)g.pitch;
+    const unsigned pmax_off = (unsigned)(pmax - r_begin) * pitch32;
+    const unsigned bmax_off = (unsigned)(bmax - r_begin) * pitch32;
+
+    VT w[K][2];
+    VT bw[K];
+#pragma unroll
+    for (int t = 0; t < K; ++t) {
+        w[t][0] = vzero<T, V>();
+        w[t][1] = vzero<T, V>();
+        bw[t] = vzero<T, V>();
+    }
+    const bool scale_b = !(A.hx == T(1) && A.hy == T(1));
+
+    LaneRing<T, V, D> ring;
+    ring.init(tid, nthreads);
+#pragma unroll
+    for (int j = 0; j < D; ++j) {
+        ring.fetch(j, 0, pbase + min((unsigned)j * pitch32, pmax_off));
+        // rhs of row r_begin+j-1; for j = 0 that row feeds only pipeline-fill values: any row will do
+        ring.fetch(j, 1, bbase + min((unsigned)(j > 0 ? j - 1 : 0) * pitch32, bmax_off));
+        ring.commit();
+    }
+    unsigned poff = min((unsigned)D * pitch32, pmax_off);
+    unsigned boff = min((unsigned)(D - 1) * pitch32, bmax_off);
+    int soff = -K * (int)pitch32;  // row stored by the current step, relative to r_begin
+    int sbase = 0;
+#pragma unroll 1
+    for (int r = r_begin; r <= r_end; r += U) {
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            const int slot = (D == U) ? u : sbase + u;
+            ring.template wait<D - 1>();
+            VT cur = ring.read(slot, 0);
+            VT bnew = ring.read(slot, 1);
+            ring.fetch(slot, 0, pbase + poff);
+            ring.fetch(slot, 1, bbase + boff);
+            ring.commit();
+            poff = min(poff + pitch32, pmax_off);
+            boff = min(boff + pitch32, bmax_off);
+            if (scale_b) {
+#pragma unroll
+                for (int e = 0; e < V; ++e) bnew.a[e] = A_::mul(A_::mul(bnew.a[e], A.hx), A.hy);
+            }
+#pragma unroll
+            for (int t = K - 1; t > 0; --t) bw[t] = bw[t - 1];
+            bw[0] = bnew;
+#pragma unroll
+            for (int t = 1; t <= K; ++t) {
+                const VT out = jacobi_row<T, V>(w[t - 1][0], w[t - 1][1], cur, bw[t - 1]);
+                w[t - 1][0] = w[t - 1][1];
+                w[t - 1][1] = cur;
+                cur = out;
+            }
+            const int row = r + u - K;  // row level K produced in this step
+            if (st.st_ok && row >= c0 && row < c1) st_vec<T, V>(obase + soff, cur);
+            soff += (int)pitch32;
+        }
+        if (D != U) sbase = (sbase + U) % D;
+    }
+    ring.template wait<0>();  // nothing may still be landing in shared memory when the CTA retires
+}
+
 // =========================================================================================
 // Fused tentative velocity + divergence right-hand side ("predictor").
 // Replaces unified_timestep_kernel + compute_righthand_kernel

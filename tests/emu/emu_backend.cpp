@@ -125,14 +125,41 @@ static void set_ranges(std::initializer_list<const void*> ptrs, size_t bytes) {
     for (const void* p : ptrs)
         if (p) emu_ranges[emu_nranges++] = {(const char*)p, (const char*)p + bytes};
 }
+// Emulates the CUDA wrappers literally: (blockIdx.x, blockIdx.y, warp) -> task through the same
+// jacobi_decode_task, so the split launch (FAST twin + GENERAL kernel) is what gets tested.
 template <typename T, int K>
 static void jac_k(const fb::JacobiArgs<T>& a, bool mask, int nchunks) {
     set_ranges({a.p_in, a.p_out, a.rhs}, (size_t)a.g.rows * a.g.pitch * sizeof(T));
     constexpr int V = fb::VecWidth<T>::V;
-    if (K == 1 && mask)
-        run_grid(a.g.nstrips, nchunks, [&](int s, int c, int l) { fb::jacobi_task<T, V, 1, true>(a, s, c, l, l, 32); });
-    else
-        run_grid(a.g.nstrips, nchunks, [&](int s, int c, int l) { fb::jacobi_task<T, V, K, false>(a, s, c, l, l, 32); });
+    constexpr int W = fb::kWarpsPerCta;
+    auto general = [&](const fb::JacobiArgs<T>& g, int nwarps_x, int ny) {
+        run_grid(nwarps_x, ny, [&](int wx, int by, int l) {
+            int strip, chunk;
+            if (!fb::jacobi_decode_task(g, wx / W, by, wx % W, W, &strip, &chunk)) return;
+            if (K == 1 && mask) fb::jacobi_task<T, V, 1, true>(g, strip, chunk, l, l, 32);
+            else fb::jacobi_task<T, V, K, false>(g, strip, chunk, l, l, 32);
+        });
+    };
+    auto round_up = [](int n) { return (n + W - 1) / W * W; };
+    if (a.part == 0 || mask) {
+        fb::JacobiArgs<T> all = a;
+        all.part = 0;
+        general(all, round_up(a.g.nstrips), nchunks);
+        return;
+    }
+    fb::JacobiArgs<T> gen = a, fast = a;
+    gen.part = 2;
+    fast.part = 1;
+    if (getenv("FLUIDB200_EMU_VERBOSE"))
+        std::fprintf(stderr, "EMU split K=%d: strips [%d,%d) of %d, chunks [%d,%d) of %d -> %d fast, %d general tasks\n", K,
+                     a.sf_lo, a.sf_hi, a.g.nstrips, a.cf_lo, a.cf_hi, nchunks, (a.sf_hi - a.sf_lo) * (a.cf_hi - a.cf_lo),
+                     fb::jacobi_part2_tasks(gen));
+    general(gen, round_up(fb::jacobi_part2_tasks(gen)), 1);
+    run_grid(round_up(a.sf_hi - a.sf_lo), a.cf_hi - a.cf_lo, [&](int wx, int by, int l) {
+        int strip, chunk;
+        if (!fb::jacobi_decode_task(fast, wx / W, by, wx % W, W, &strip, &chunk)) return;
+        fb::jacobi_fast_task<T, V, K>(fast, strip, chunk, l, l, 32);
+    });
 }
 template <typename T> int launch_jacobi(const fb::JacobiArgs<T>& a, int sweeps, bool mask, int nchunks, void*) {
     switch (sweeps) {
