@@ -35,7 +35,7 @@ import numpy as np  # noqa: E402
 
 GRID = int(os.environ.get("FLUIDB200_BENCH_GRID", 16384))
 SWEEPS = int(os.environ.get("FLUIDB200_BENCH_SWEEPS", 100))
-KMAX = int(os.environ.get("FLUIDB200_KMAX", 5))
+KMAX = int(os.environ.get("FLUIDB200_KMAX", 6))
 METRIC = "Gcell-updates/s per timestep (cavity 16384x16384 fp32, 100 Poisson sweeps/step)"
 UNIT = "Gcell-updates/s"
 # stable, well-conditioned parameters for a 16384^2 grid: hx = hy = 1

@@ -50,9 +50,9 @@ template <typename T> int num_strips(int Y, int H) {
 }
 
 // Warp tasks aimed for per launch (measured on B200 at 16384^2): the Jacobi pipeline pays K halo rows
-// per chunk end and is best around 12 waves; the two one-pass kernels have a 1-2 row halo and keep
+// per chunk end and is best around 9 waves; the two one-pass kernels have a 1-2 row halo and keep
 // improving up to ~40 waves.
-constexpr int kJacobiTasks = 148 * 16 * 12, kLightTasks = 148 * 16 * 40;
+constexpr int kJacobiTasks = 148 * 16 * 9, kLightTasks = 148 * 16 * 40;
 
 // Split `n` output rows into chunks. More chunks = more warps in flight and a smaller tail, but
 // every chunk recomputes `halo` rows at each end. The chunk count is chosen so that the grid is
@@ -207,6 +207,9 @@ void split_jacobi(fb::JacobiArgs<T>* a, const fluidb200_slab* g, int K, int nchu
         }
     }
     if (sf_hi - sf_lo < 1 || cf_hi - cf_lo < 1) return;
+    // a launch that cannot fill the GPU a few times over is latency bound: the second kernel and the
+    // fork/join events would cost more than the extra occupancy brings (measured at 1000^2)
+    if ((long long)(sf_hi - sf_lo) * (cf_hi - cf_lo) < (long long)env_int("FLUIDB200_SPLIT_MIN_TASKS", 8192)) return;
     a->part = 1;
     a->sf_lo = sf_lo; a->sf_hi = sf_hi; a->cf_lo = cf_lo; a->cf_hi = cf_hi;
 }
@@ -226,7 +229,7 @@ int poisson_t(const fluidb200_slab* g, const void* p_in, void* p_out, const void
     const int nstrips = num_strips<T>(g->Y, halo_cols(sweeps));
     int rpc, nchunks;
     // resident CTAs per SM of the kernel that does the bulk of the work (the lean FAST kernel)
-    plan_chunks(out_hi - out_lo, sweeps, nstrips, sweeps <= 2 ? 5 : sweeps <= 5 ? 4 : 3, kJacobiTasks, &rpc, &nchunks);
+    plan_chunks(out_hi - out_lo, sweeps, nstrips, sweeps <= 2 ? 5 : sweeps <= 6 ? 4 : 3, kJacobiTasks, &rpc, &nchunks);
     a.g = make_geom(g, nstrips, rpc);
     split_jacobi<T>(&a, g, sweeps, nchunks, use_mask);
     BE_CHECK(fbk::launch_jacobi<T>(a, sweeps, use_mask, nchunks, stream), "poisson launch");
@@ -543,7 +546,7 @@ extern "C" int fluidb200_create(fluidb200_solver** out, int dtype, int X, int Y,
     s->dtype = dtype; s->X = X; s->Y = Y;
     s->esize = dtype == FLUIDB200_F32 ? 4 : 8;
     s->pitch = ((int64_t)Y + 31) / 32 * 32;
-    s->kmax = env_int("FLUIDB200_KMAX", 5);
+    s->kmax = env_int("FLUIDB200_KMAX", 6);
     fluidb200_set_domain(s, domain_x, domain_y);
     if (fbk::be_stream_create(&s->stream) != 0) {
         delete s;

@@ -38,7 +38,7 @@ __global__ void __launch_bounds__(kThreads, FLUIDB200_JACOBI_MIN_BLOCKS(K)) jaco
 // The lean twin (see jacobi_fast_task): without the general path it needs fewer registers, so it
 // is compiled for one more resident CTA per SM than jacobi_kernel.
 #ifndef FLUIDB200_JACOBI_FAST_MIN_BLOCKS
-#define FLUIDB200_JACOBI_FAST_MIN_BLOCKS(K) ((K) <= 2 ? 5 : (K) <= 5 ? 4 : 3)
+#define FLUIDB200_JACOBI_FAST_MIN_BLOCKS(K) ((K) <= 2 ? 5 : (K) <= 6 ? 4 : 3)
 #endif
 template <typename T, int V, int K>
 __global__ void __launch_bounds__(kThreads, FLUIDB200_JACOBI_FAST_MIN_BLOCKS(K)) jacobi_fast_kernel(const __grid_constant__ fb::JacobiArgs<T> A) {

@@ -263,7 +263,7 @@ class TiledNavierStokes(ParallelNavierStokes):
 
     def __init__(self, *a, **k):
         super().__init__(*a, **k)
-        self.set_sweeps_per_launch(5)
+        self.set_sweeps_per_launch(6)
 
 
 def solve_navier_stokes(num_elements=41, domain_size=1.0, num_iterations=1000, time_step=0.001,

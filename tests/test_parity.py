@@ -259,3 +259,19 @@ def test_random_shapes(Solver, X, Y, K, kmax, dtype):
     o.solve()
     H.compare_with(s, o, tag=f"random/{X}x{Y}/K{K}/k{kmax}/{dtype}")
     s.close()
+
+
+@pytest.mark.parametrize("knob", ["FLUIDB200_NO_SPLIT", "FLUIDB200_SPLIT_MIN_TASKS"])
+def test_single_kernel_and_split_launch_agree(Solver, env, knob):
+    """The Jacobi launch as ONE general kernel (NO_SPLIT=1, or a grid below the split threshold) and
+    as the split pair must produce the same bits as the oracle."""
+    env[knob] = "1" if knob == "FLUIDB200_NO_SPLIT" else "1000000"
+    X, Y = 90, 420
+    o = Oracle(X, Y).set_cavity()
+    o.time_step, o.num_iterations, o.num_poisson_iterations = 1e-5, 2, 13
+    s = Solver(X, Y).set_cavity()
+    s.time_step, s.num_iterations, s.num_poisson_iterations = 1e-5, 2, 13
+    s.migrateSolve()
+    o.solve()
+    H.compare_with(s, o, tag=knob)
+    s.close()
