@@ -208,8 +208,9 @@ void split_jacobi(fb::JacobiArgs<T>* a, const fluidb200_slab* g, int K, int nchu
     }
     if (sf_hi - sf_lo < 1 || cf_hi - cf_lo < 1) return;
     // a launch that cannot fill the GPU a few times over is latency bound: the second kernel and the
-    // fork/join events would cost more than the extra occupancy brings (measured at 1000^2)
-    if ((long long)(sf_hi - sf_lo) * (cf_hi - cf_lo) < (long long)env_int("FLUIDB200_SPLIT_MIN_TASKS", 8192)) return;
+    // fork/join events would cost more than the extra occupancy brings (measured: no gain at 1000^2,
+    // 25 % at 2048^2)
+    if ((long long)(sf_hi - sf_lo) * (cf_hi - cf_lo) < (long long)env_int("FLUIDB200_SPLIT_MIN_TASKS", 512)) return;
     a->part = 1;
     a->sf_lo = sf_lo; a->sf_hi = sf_hi; a->cf_lo = cf_lo; a->cf_hi = cf_hi;
 }
@@ -546,7 +547,13 @@ extern "C" int fluidb200_create(fluidb200_solver** out, int dtype, int X, int Y,
     s->dtype = dtype; s->X = X; s->Y = Y;
     s->esize = dtype == FLUIDB200_F32 ? 4 : 8;
     s->pitch = ((int64_t)Y + 31) / 32 * 32;
-    s->kmax = env_int("FLUIDB200_KMAX", 6);
+    // Temporal-blocking depth. Measured on B200 (fp32): 6 for grids that fill the GPU many times over
+    // (16384^2: 2.86 Tcell-sweeps/s), 4 around 8192^2, 3 below (short pipelines fill faster and the
+    // halo recomputation weighs more on small chunks). FLUIDB200_KMAX / set_sweeps_per_launch override.
+    {
+        const long long cells = (long long)X * Y;
+        s->kmax = env_int("FLUIDB200_KMAX", cells >= 150000000LL ? 6 : cells >= 40000000LL ? 4 : 3);
+    }
     fluidb200_set_domain(s, domain_x, domain_y);
     if (fbk::be_stream_create(&s->stream) != 0) {
         delete s;
