@@ -497,9 +497,12 @@ int step_poisson(fluidb200_solver* s, int sweeps) {
     fill_slab(s, &g);
     const bool masked = s->mask[2].set != nullptr;
     const int kmax = masked ? 1 : std::max(1, std::min(s->kmax, FLUIDB200_MAX_SWEEPS_PER_LAUNCH));
+    // n = ceil(sweeps / kmax) launches of nearly equal depth (100 sweeps at depth 7: 10 x 7 + 5 x 6)
+    // rather than full launches and a shallow remainder: a launch costs about the same at any depth.
+    const int nlaunch = (sweeps + kmax - 1) / kmax;
     int left = sweeps;
-    while (left > 0) {
-        const int k = std::min(kmax, left);
+    for (int i = 0; i < nlaunch; ++i) {
+        const int k = (left + (nlaunch - i) - 1) / (nlaunch - i);
         int rc = fluidb200_poisson_sweeps(&g, s->f[FLUIDB200_FIELD_P], s->f[FLUIDB200_FIELD_P_NEXT],
                                           s->f[FLUIDB200_FIELD_RHS], &s->edges[2], masked ? &s->mask[2] : nullptr, k, 0,
                                           s->X, s->stream);

@@ -32,7 +32,7 @@ template <typename T, int V, int K, bool MASK>
 __global__ void __launch_bounds__(kThreads, FLUIDB200_JACOBI_MIN_BLOCKS(K)) jacobi_kernel(const __grid_constant__ fb::JacobiArgs<T> A) {
     int strip, chunk;  // whole warps only; the tasks use no block barrier
     if (!fb::jacobi_decode_task(A, (int)blockIdx.x, (int)blockIdx.y, (int)(threadIdx.x >> 5), fb::kWarpsPerCta, &strip, &chunk)) return;
-    fb::jacobi_task<T, V, K, MASK>(A, strip, chunk, threadIdx.x & 31, threadIdx.x, kThreads);
+    fb::jacobi_general_task<T, V, K, MASK>(A, strip, chunk, threadIdx.x & 31, threadIdx.x, kThreads);
 }
 
 // The lean twin (see jacobi_fast_task): without the general path it needs fewer registers, so it

@@ -325,9 +325,22 @@ template <typename T, int V, int D> struct LaneRing {
 #endif
 };
 // ring depth used by the Jacobi fast path for blocking depth K (U = steps per unrolled iteration)
+// Unroll factor U of the fast loop. U = K (rounded up to even) lets the row windows and the
+// right-hand-side shift register rotate by register renaming alone, but at K >= 7 the unrolled body
+// (8 steps x 8 levels, 27 KB of code) no longer sits in the instruction caches: 4 steps per iteration
+// plus a few moves is 10 % faster there (measured, profiles/README_r1.md). Build-time knobs
+// (0 = the default rule), kept for such measurements:
+#ifndef FLUIDB200_U_DEEP
+#define FLUIDB200_U_DEEP 4   // K = 7, 8
+#endif
+#ifndef FLUIDB200_U_MID
+#define FLUIDB200_U_MID 0    // K = 5, 6
+#endif
 template <int K> struct JacobiRing {
-    static constexpr int U = (K + 1) & ~1;
-    static constexpr int D = U < 4 ? 4 : U;
+    static constexpr int U0 = (K + 1) & ~1;
+    static constexpr int U = (K >= 7 && FLUIDB200_U_DEEP) ? FLUIDB200_U_DEEP : ((K == 5 || K == 6) && FLUIDB200_U_MID) ? FLUIDB200_U_MID : U0;
+    static constexpr int D0 = U0 < 4 ? 4 : U0;
+    static constexpr int D = (D0 % U == 0) ? D0 : ((D0 + U - 1) / U) * U;
 };
 
 // =========================================================================================
@@ -379,6 +392,18 @@ FB_DEV Vec<T, V> wall_row_out(const Edges<T>& e, int edge, int x, const Vec<T, V
     return r;
 }
 
+#if !defined(FLUIDB200_NO_PACKED_F32X2) && !defined(FLUIDB200_HOST_EMU)
+FB_DEV float2 fsub2(float2 a, float2 b) {  // two correctly rounded differences in one instruction
+    unsigned long long xa, xb, xr;
+    float2 r;
+    asm("mov.b64 %0, {%1,%2};" : "=l"(xa) : "f"(a.x), "f"(a.y));
+    asm("mov.b64 %0, {%1,%2};" : "=l"(xb) : "f"(b.x), "f"(b.y));
+    asm("sub.rn.f32x2 %0, %1, %2;" : "=l"(xr) : "l"(xa), "l"(xb));
+    asm("mov.b64 {%0,%1}, %2;" : "=f"(r.x), "=f"(r.y) : "l"(xr));
+    return r;
+}
+#endif
+
 // One Jacobi update of a row strip: out = ((b - (((xm + xp) + yp) + ym)) * -0.25
 // (SerialNavierStokes.cpp:144-146, operand order kept).
 template <typename T, int V>
@@ -386,6 +411,25 @@ FB_DEV Vec<T, V> jacobi_row(const Vec<T, V>& xm, const Vec<T, V>& c, const Vec<T
     using A_ = Ar<T>;
     Vec<T, V> ym, yp, out;
     y_neighbours<T, V>(c, ym, yp);
+#if !defined(FLUIDB200_NO_PACKED_F32X2) && !defined(FLUIDB200_HOST_EMU)
+    if constexpr (sizeof(T) == 4 && V == 4) {
+        // sm_100 packed fp32: one FADD2 rounds two independent sums exactly like two FADDs. Only the
+        // first sum and the subtraction pair up without register moves; the multiplication stays
+        // scalar because ptxas (12.9) contracts mul.rn.f32x2 + add.rn.f32x2 into FFMA2.
+        float2 s0 = __fadd2_rn(make_float2(xm.a[0], xm.a[1]), make_float2(xp.a[0], xp.a[1]));
+        float2 s1 = __fadd2_rn(make_float2(xm.a[2], xm.a[3]), make_float2(xp.a[2], xp.a[3]));
+        s0.x = __fadd_rn(__fadd_rn(s0.x, yp.a[0]), ym.a[0]);
+        s0.y = __fadd_rn(__fadd_rn(s0.y, yp.a[1]), ym.a[1]);
+        s1.x = __fadd_rn(__fadd_rn(s1.x, yp.a[2]), ym.a[2]);
+        s1.y = __fadd_rn(__fadd_rn(s1.y, yp.a[3]), ym.a[3]);
+        const float2 d0 = fsub2(make_float2(b.a[0], b.a[1]), s0), d1 = fsub2(make_float2(b.a[2], b.a[3]), s1);
+        out.a[0] = __fmul_rn(d0.x, -0.25f);
+        out.a[1] = __fmul_rn(d0.y, -0.25f);
+        out.a[2] = __fmul_rn(d1.x, -0.25f);
+        out.a[3] = __fmul_rn(d1.y, -0.25f);
+        return out;
+    }
+#endif
 #pragma unroll
     for (int e = 0; e < V; ++e) {
         const T s = A_::add(A_::add(A_::add(xm.a[e], xp.a[e]), yp.a[e]), ym.a[e]);
@@ -594,8 +638,8 @@ FB_DEV void jacobi_task(const JacobiArgs<T>& A, int strip, int chunk, int lane, 
 // strip without a y-edge column, r_begin = c0-K >= max(row0, K+2), r_end = c1-1+K <= X-2.
 // The step count is rounded UP to a multiple of U; the extra steps read clamped rows and are
 // never stored.
-template <typename T, int V, int K>
-FB_DEV void jacobi_fast_task(const JacobiArgs<T>& A, int strip, int chunk, int lane, int tid, int nthreads) {
+template <typename T, int V, int K, bool SCALE_B, bool YEDGE>
+FB_DEV void jacobi_fast_body(const JacobiArgs<T>& A, int strip, int chunk, int lane, int tid, int nthreads) {
     constexpr int H = (K + 3) & ~3;
     constexpr int U = JacobiRing<K>::U, D = JacobiRing<K>::D;
     static_assert(D % U == 0, "ring depth must be a multiple of the unroll factor");
@@ -615,7 +659,9 @@ FB_DEV void jacobi_fast_task(const JacobiArgs<T>& A, int strip, int chunk, int l
     const long long base = (long long)st.lcol + (long long)(r_begin - g.row0) * g.pitch;
     const T* pbase = A.p_in + base;
     const T* bbase = A.rhs + base;
-    T* obase = A.p_out + (long long)st.col0 + (long long)(r_begin - g.row0) * g.pitch;
+    // row stored by step r is r-K; the pointer runs along with the steps and is only dereferenced
+    // for rows of the chunk
+    T* optr = A.p_out + (long long)st.col0 + (long long)(r_begin - K - g.row0) * g.pitch;
     const unsigned pitch32 = (unsigned)g.pitch;
     const unsigned pmax_off = (unsigned)(pmax - r_begin) * pitch32;
     const unsigned bmax_off = (unsigned)(bmax - r_begin) * pitch32;
@@ -628,7 +674,6 @@ FB_DEV void jacobi_fast_task(const JacobiArgs<T>& A, int strip, int chunk, int l
         w[t][1] = vzero<T, V>();
         bw[t] = vzero<T, V>();
     }
-    const bool scale_b = !(A.hx == T(1) && A.hy == T(1));
 
     LaneRing<T, V, D> ring;
     ring.init(tid, nthreads);
@@ -641,7 +686,6 @@ FB_DEV void jacobi_fast_task(const JacobiArgs<T>& A, int strip, int chunk, int l
     }
     unsigned poff = min((unsigned)D * pitch32, pmax_off);
     unsigned boff = min((unsigned)(D - 1) * pitch32, bmax_off);
-    int soff = -K * (int)pitch32;  // row stored by the current step, relative to r_begin
     int sbase = 0;
 #pragma unroll 1
     for (int r = r_begin; r <= r_end; r += U) {
@@ -656,7 +700,7 @@ FB_DEV void jacobi_fast_task(const JacobiArgs<T>& A, int strip, int chunk, int l
             ring.commit();
             poff = min(poff + pitch32, pmax_off);
             boff = min(boff + pitch32, bmax_off);
-            if (scale_b) {
+            if (SCALE_B) {
 #pragma unroll
                 for (int e = 0; e < V; ++e) bnew.a[e] = A_::mul(A_::mul(bnew.a[e], A.hx), A.hy);
             }
@@ -665,18 +709,43 @@ FB_DEV void jacobi_fast_task(const JacobiArgs<T>& A, int strip, int chunk, int l
             bw[0] = bnew;
 #pragma unroll
             for (int t = 1; t <= K; ++t) {
-                const VT out = jacobi_row<T, V>(w[t - 1][0], w[t - 1][1], cur, bw[t - 1]);
+                VT out = jacobi_row<T, V>(w[t - 1][0], w[t - 1][1], cur, bw[t - 1]);
+                // strips holding column 0 or Y-1: the y-edge cells of every level (:163-175). The row
+                // index only addresses per-cell boundary arrays; rows of the pipeline fill and of the
+                // rounded-up tail are clamped (their values are never stored).
+                if (YEDGE) apply_y_edges<T, V, H>(A.e, st, min(max(r + u - t, 1), g.X - 2), out, out, out);
                 w[t - 1][0] = w[t - 1][1];
                 w[t - 1][1] = cur;
                 cur = out;
             }
             const int row = r + u - K;  // row level K produced in this step
-            if (st.st_ok && row >= c0 && row < c1) st_vec<T, V>(obase + soff, cur);
-            soff += (int)pitch32;
+            if (st.st_ok && row >= c0 && row < c1) st_vec<T, V>(optr, cur);
+            optr += pitch32;
         }
         if (D != U) sbase = (sbase + U) % D;
     }
     ring.template wait<0>();  // nothing may still be landing in shared memory when the CTA retires
+}
+
+// The scaling of the right-hand side by hx*hy (two exact multiplications by 1 on a unit-spaced grid)
+// is decided once per task, not once per row.
+template <typename T, int V, int K>
+FB_DEV void jacobi_fast_task(const JacobiArgs<T>& A, int strip, int chunk, int lane, int tid, int nthreads) {
+    if (A.hx == T(1) && A.hy == T(1)) jacobi_fast_body<T, V, K, false, false>(A, strip, chunk, lane, tid, nthreads);
+    else jacobi_fast_body<T, V, K, true, false>(A, strip, chunk, lane, tid, nthreads);
+}
+
+// One task of the GENERAL kernel of a split launch. Strips that hold a y-edge column but whose
+// chunk is a fast chunk (no x wall within reach of the pipeline) run the lean pipeline with the
+// y-edge cells added; only chunks at an x wall, masked sweeps and unsplit launches need jacobi_task.
+template <typename T, int V, int K, bool MASK>
+FB_DEV void jacobi_general_task(const JacobiArgs<T>& A, int strip, int chunk, int lane, int tid, int nthreads) {
+    if (!MASK && A.part == 2 && chunk >= A.cf_lo && chunk < A.cf_hi) {
+        if (A.hx == T(1) && A.hy == T(1)) jacobi_fast_body<T, V, K, false, true>(A, strip, chunk, lane, tid, nthreads);
+        else jacobi_fast_body<T, V, K, true, true>(A, strip, chunk, lane, tid, nthreads);
+        return;
+    }
+    jacobi_task<T, V, K, MASK>(A, strip, chunk, lane, tid, nthreads);
 }
 
 // =========================================================================================

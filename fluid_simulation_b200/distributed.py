@@ -173,8 +173,9 @@ class SlabSolver:
         left = int(sweeps)
         d = self.kmax
         x0, x1 = self.x0, self.x1
-        while left > 0:
-            k = min(self.kmax, left)
+        nlaunch = -(-left // self.kmax)   # launches of nearly equal depth, like step_poisson in csrc/api.cpp
+        for i in range(nlaunch):
+            k = -(-left // (nlaunch - i))
             left -= k
             if self.world == 1:
                 self._sweeps(k, 0, self.X)
