@@ -177,28 +177,31 @@ int predictor_t(const fluidb200_slab* g, const void* u, const void* v, void* us,
     return 0;
 }
 
-// Decide which tasks of a Jacobi launch may go to the lean FAST kernel (jacobi_fast_task): every
-// step of such a task must be a fast step, i.e.
-//   strips [sf_lo, sf_hi): no y-edge column inside the strip's 32*V loaded columns;
+// Decide which tasks of a Jacobi launch may go to the lean kernels (jacobi_fast_task / jacobi_edge_task):
+// every step of such a task must be a plain interior step in x, i.e.
 //   chunks [cf_lo, cf_hi): pipeline starts at c0-K >= max(row0, K+2) and ends at c1-1+K <= X-2,
-//                          and the chunk spans fewer than 2^31 elements (32-bit running offsets).
-// Everything else (walls, edge strips) stays with the general kernel. part = 1 asks the backend for
-// the split launch, part = 0 for the single general kernel.
+//                          and the chunk spans fewer than 2^31 elements (32-bit running offsets);
+//   strips [sf_lo, sf_hi): no y-edge column inside the strip's 32*V loaded columns (FAST kernel);
+//                          the other strips of those chunks go to the EDGE kernel.
+// The remaining (wall) chunks stay with the general kernel. part = 1 asks the backend for the split
+// launch, part = 0 for the single general kernel.
 template <typename T>
 void split_jacobi(fb::JacobiArgs<T>* a, const fluidb200_slab* g, int K, int nchunks, bool use_mask) {
     a->part = 0;
     a->nchunks = nchunks;
     a->sf_lo = a->sf_hi = a->cf_lo = a->cf_hi = 0;
+    a->edge_lean = 0;
     if (use_mask || env_int("FLUIDB200_NO_SPLIT", 0)) return;
     const int W = 32 * vec_width<T>(), S = W - 2 * halo_cols(K);
-    const int nstrips = a->g.nstrips, rpc = a->g.rows_per_chunk;
+    const int nstrips = a->g.nstrips;
     int sf_lo = 1, sf_hi = 1;
     while (sf_hi < nstrips && sf_hi * S + W <= g->Y - 1) ++sf_hi;  // strip sf_hi is the first that holds column Y-1
     int cf_lo = nchunks, cf_hi = 0;
     for (int c = 0; c < nchunks; ++c) {
-        const int c0 = a->out_lo + c * rpc, c1 = std::min(c0 + rpc, a->out_hi);
-        const bool ok = c0 - K >= std::max(g->row0, K + 2) && c1 - 1 + K <= g->X - 2 &&
-                        (long long)(c1 - c0 + 2 * K + 1) * g->pitch < (1LL << 31);
+        int c0, c1;
+        fb::jacobi_chunk_rows(*a, c, &c0, &c1);
+        const bool ok = c0 < c1 && c0 - K >= std::max(g->row0, K + 2) && c1 - 1 + K <= g->X - 2 &&
+                        c1 + K <= g->row0 + g->rows && (long long)(c1 - c0 + 2 * K + 1) * g->pitch < (1LL << 31);
         if (ok) {
             cf_lo = std::min(cf_lo, c);
             cf_hi = std::max(cf_hi, c + 1);
@@ -207,12 +210,14 @@ void split_jacobi(fb::JacobiArgs<T>* a, const fluidb200_slab* g, int K, int nchu
         }
     }
     if (sf_hi - sf_lo < 1 || cf_hi - cf_lo < 1) return;
-    // a launch that cannot fill the GPU a few times over is latency bound: the second kernel and the
+    // a launch that cannot fill the GPU a few times over is latency bound: the extra kernels and the
     // fork/join events would cost more than the extra occupancy brings (measured: no gain at 1000^2,
     // 25 % at 2048^2)
     if ((long long)(sf_hi - sf_lo) * (cf_hi - cf_lo) < (long long)env_int("FLUIDB200_SPLIT_MIN_TASKS", 512)) return;
     a->part = 1;
     a->sf_lo = sf_lo; a->sf_hi = sf_hi; a->cf_lo = cf_lo; a->cf_hi = cf_hi;
+    // the lean EDGE kernel knows constant and copy boundary cells; per-cell arrays stay with the general kernel
+    a->edge_lean = a->e.mode[fb::BOTTOM] != fb::EDGE_ARRAY && a->e.mode[fb::TOP] != fb::EDGE_ARRAY;
 }
 
 template <typename T>
@@ -230,9 +235,26 @@ int poisson_t(const fluidb200_slab* g, const void* p_in, void* p_out, const void
     const int nstrips = num_strips<T>(g->Y, halo_cols(sweeps));
     int rpc, nchunks;
     // resident CTAs per SM of the kernel that does the bulk of the work (the lean FAST kernel)
-    plan_chunks(out_hi - out_lo, sweeps, nstrips, sweeps <= 2 ? 5 : sweeps <= 6 ? 4 : 3, kJacobiTasks, &rpc, &nchunks);
-    a.g = make_geom(g, nstrips, rpc);
-    split_jacobi<T>(&a, g, sweeps, nchunks, use_mask);
+    const int ctas_per_sm = sweeps <= 2 ? 5 : sweeps <= 6 ? 4 : 3;
+    // First try: the chunks at an x wall as short as the pipeline allows (the next chunk must start
+    // at row >= 2K+2, the previous one end at row <= X-K-2), because only the register-heavy general
+    // kernel can run them; the rows between are chunked uniformly and go to the lean kernels.
+    const int n = out_hi - out_lo;
+    a.head = out_lo == 0 ? 2 * sweeps + 2 : 0;
+    a.tail = out_hi == g->X ? sweeps + 1 : 0;
+    a.part = 0;
+    if (!use_mask && (a.head || a.tail) && n - a.head - a.tail >= 4 * sweeps + 8) {
+        plan_chunks(n - a.head - a.tail, sweeps, nstrips, ctas_per_sm, kJacobiTasks, &rpc, &nchunks);
+        nchunks += (a.head > 0) + (a.tail > 0);
+        a.g = make_geom(g, nstrips, rpc);
+        split_jacobi<T>(&a, g, sweeps, nchunks, use_mask);
+    }
+    if (a.part == 0) {  // no split (small grid, masked sweep, no wall in range): plain uniform chunks
+        a.head = a.tail = 0;
+        plan_chunks(n, sweeps, nstrips, ctas_per_sm, kJacobiTasks, &rpc, &nchunks);
+        a.g = make_geom(g, nstrips, rpc);
+        split_jacobi<T>(&a, g, sweeps, nchunks, use_mask);
+    }
     BE_CHECK(fbk::launch_jacobi<T>(a, sweeps, use_mask, nchunks, stream), "poisson launch");
     return 0;
 }

@@ -32,7 +32,7 @@ template <typename T, int V, int K, bool MASK>
 __global__ void __launch_bounds__(kThreads, FLUIDB200_JACOBI_MIN_BLOCKS(K)) jacobi_kernel(const __grid_constant__ fb::JacobiArgs<T> A) {
     int strip, chunk;  // whole warps only; the tasks use no block barrier
     if (!fb::jacobi_decode_task(A, (int)blockIdx.x, (int)blockIdx.y, (int)(threadIdx.x >> 5), fb::kWarpsPerCta, &strip, &chunk)) return;
-    fb::jacobi_general_task<T, V, K, MASK>(A, strip, chunk, threadIdx.x & 31, threadIdx.x, kThreads);
+    fb::jacobi_task<T, V, K, MASK>(A, strip, chunk, threadIdx.x & 31, threadIdx.x, kThreads);
 }
 
 // The lean twin (see jacobi_fast_task): without the general path it needs fewer registers, so it
@@ -45,6 +45,17 @@ __global__ void __launch_bounds__(kThreads, FLUIDB200_JACOBI_FAST_MIN_BLOCKS(K))
     int strip, chunk;
     if (!fb::jacobi_decode_task(A, (int)blockIdx.x, (int)blockIdx.y, (int)(threadIdx.x >> 5), fb::kWarpsPerCta, &strip, &chunk)) return;
     fb::jacobi_fast_task<T, V, K>(A, strip, chunk, threadIdx.x & 31, threadIdx.x, kThreads);
+}
+
+// The lean pipeline plus the y-edge cells, for the strips that hold column 0 or Y-1.
+#ifndef FLUIDB200_JACOBI_EDGE_MIN_BLOCKS
+#define FLUIDB200_JACOBI_EDGE_MIN_BLOCKS(K) ((K) <= 2 ? 5 : (K) <= 4 ? 4 : (K) <= 6 ? 3 : 2)
+#endif
+template <typename T, int V, int K>
+__global__ void __launch_bounds__(kThreads, FLUIDB200_JACOBI_EDGE_MIN_BLOCKS(K)) jacobi_edge_kernel(const __grid_constant__ fb::JacobiArgs<T> A) {
+    int strip, chunk;
+    if (!fb::jacobi_decode_task(A, (int)blockIdx.x, (int)blockIdx.y, (int)(threadIdx.x >> 5), fb::kWarpsPerCta, &strip, &chunk)) return;
+    fb::jacobi_edge_task<T, V, K>(A, strip, chunk, threadIdx.x & 31, threadIdx.x, kThreads);
 }
 
 template <typename T, int V, int MODE>
@@ -121,12 +132,24 @@ template <typename T, int K> int launch_jacobi_k(const fb::JacobiArgs<T>& a, boo
         else jacobi_kernel<T, V, K, false><<<grid, kThreads, smem, st>>>(all);
         return rc_of(cudaGetLastError());
     }
-    // split launch: GENERAL tasks on the side stream, FAST tasks on the caller's stream, then join
-    fb::JacobiArgs<T> gen = a, fast = a;
+    // split launch: GENERAL (wall chunks) and EDGE (y-edge strips) tasks on the side stream, FAST tasks
+    // on the caller's stream, then join
+    fb::JacobiArgs<T> gen = a, edge = a, fast = a;
     gen.part = 2;
+    edge.part = 3;
     fast.part = 1;
     if (rc_of(cudaEventRecord(side->fork, st)) || rc_of(cudaStreamWaitEvent(side->stream, side->fork, 0))) return -1;
-    const int ngen = fb::jacobi_part2_tasks(gen);
+#ifdef FLUIDB200_EXPERIMENT_SKIP_SIDE   // timing experiments only (wrong results): 1 = no edge, 2 = no general, 3 = neither
+    const int ngen = (FLUIDB200_EXPERIMENT_SKIP_SIDE & 2) ? 0 : fb::jacobi_part2_tasks(gen);
+    const int nedge = (FLUIDB200_EXPERIMENT_SKIP_SIDE & 1) ? 0 : fb::jacobi_part3_tasks(edge);
+#else
+    const int ngen = fb::jacobi_part2_tasks(gen), nedge = fb::jacobi_part3_tasks(edge);
+#endif
+    if (nedge > 0) {
+        const dim3 egrid((unsigned)((nedge + fb::kWarpsPerCta - 1) / fb::kWarpsPerCta), 1, 1);
+        jacobi_edge_kernel<T, V, K><<<egrid, kThreads, smem, side->stream>>>(edge);
+        if (rc_of(cudaGetLastError())) return -1;
+    }
     if (ngen > 0) {
         const dim3 ggrid((unsigned)((ngen + fb::kWarpsPerCta - 1) / fb::kWarpsPerCta), 1, 1);
         jacobi_kernel<T, V, K, false><<<ggrid, kThreads, smem, side->stream>>>(gen);

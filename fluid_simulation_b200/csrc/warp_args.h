@@ -76,24 +76,48 @@ template <typename T> struct JacobiArgs {
     T hx, hy;
     int out_lo, out_hi;   // global rows to write
     Edges<T> e;
-    // Split launch (see JacobiSplit): a launch is cut into a lean FAST kernel over the tasks whose
-    // whole pipeline runs on plain interior rows/columns and a GENERAL kernel over the rest.
-    int part;             // 0 = one kernel does every task, 1 = fast tasks only, 2 = all other tasks
+    // Split launch (split_jacobi in api.cpp): a launch is cut into a lean FAST kernel over the tasks
+    // whose whole pipeline runs on plain interior rows and columns, a lean EDGE kernel over the
+    // strips that hold a y-edge column (same rows), and the GENERAL kernel over the chunks at an x wall.
+    int part;             // 0 = one kernel does every task, 1 = fast, 2 = general (wall chunks), 3 = edge strips
     int sf_lo, sf_hi;     // strips [sf_lo, sf_hi) hold no y-edge column
     int cf_lo, cf_hi;     // chunks [cf_lo, cf_hi) neither touch an x wall nor lack halo rows
     int nchunks;
+    // Chunking of the output rows [out_lo, out_hi): an optional short first chunk of `head` rows and
+    // last chunk of `tail` rows (the wall chunks of a split launch, kept as short as the pipeline
+    // allows because only the general kernel can run them), uniform chunks of g.rows_per_chunk between.
+    int head, tail;
+    // 1: the strips holding a y-edge column have their own lean kernel (part 3); 0 (a y edge with
+    // per-cell boundary arrays): they are general tasks, appended to the part 2 list
+    int edge_lean;
 };
+
+#ifdef __CUDACC__
+#define FB_HD __host__ __device__
+#else
+#define FB_HD
+#endif
+
+// rows [c0, c1) written by chunk `chunk` (c0 >= c1: nothing)
+template <typename T> inline FB_HD void jacobi_chunk_rows(const JacobiArgs<T>& a, int chunk, int* c0, int* c1) {
+    const int lo = a.out_lo + a.head, hi = a.out_hi - a.tail;  // the uniformly chunked middle
+    if (a.head > 0 && chunk == 0) {
+        *c0 = a.out_lo; *c1 = lo;
+    } else if (a.tail > 0 && chunk == a.nchunks - 1) {
+        *c0 = hi; *c1 = a.out_hi;
+    } else {
+        const int i = chunk - (a.head > 0 ? 1 : 0);
+        *c0 = lo + i * a.g.rows_per_chunk;
+        *c1 = *c0 + a.g.rows_per_chunk < hi ? *c0 + a.g.rows_per_chunk : hi;
+    }
+}
 
 // Task decoding shared by the CUDA wrappers and the emulator. Returns false for padding threads.
 // part 1: grid (ceil((sf_hi-sf_lo)/W), cf_hi-cf_lo), warps = adjacent fast strips of one fast chunk.
-// part 2: one-dimensional list: first the edge strips x all chunks, then the fast strips x the
-//         remaining (wall) chunks.
+// part 3: one-dimensional list: edge strips x fast chunks.
+// part 2: one-dimensional list: every strip x the remaining (wall) chunks.
 template <typename T>
-inline
-#ifdef __CUDACC__
-    __host__ __device__
-#endif
-    bool jacobi_decode_task(const JacobiArgs<T>& a, int bx, int by, int warp, int warps_per_cta, int* strip, int* chunk) {
+inline FB_HD bool jacobi_decode_task(const JacobiArgs<T>& a, int bx, int by, int warp, int warps_per_cta, int* strip, int* chunk) {
     if (a.part == 0) {
         *strip = bx * warps_per_cta + warp;
         *chunk = by;
@@ -105,24 +129,34 @@ inline
         return *strip < a.sf_hi;
     }
     const int id = bx * warps_per_cta + warp;
-    const int E = a.sf_lo + (a.g.nstrips - a.sf_hi), C = a.nchunks;
-    if (id < E * C) {
+    if (a.part == 3) {
+        const int E = a.sf_lo + (a.g.nstrips - a.sf_hi);
+        if (id >= E * (a.cf_hi - a.cf_lo)) return false;
         const int e = id % E;
         *strip = e < a.sf_lo ? e : a.sf_hi + (e - a.sf_lo);
-        *chunk = id / E;
+        *chunk = a.cf_lo + id / E;
         return true;
     }
-    const int id2 = id - E * C, Si = a.sf_hi - a.sf_lo, Cn = C - (a.cf_hi - a.cf_lo);
-    if (Si <= 0) return false;
-    const int ci = id2 / Si;
-    if (ci >= Cn) return false;
-    *strip = a.sf_lo + id2 % Si;
-    *chunk = ci < a.cf_lo ? ci : ci - a.cf_lo + a.cf_hi;
+    const int E = a.sf_lo + (a.g.nstrips - a.sf_hi), nwall = a.nchunks - (a.cf_hi - a.cf_lo);
+    const int ci = id / a.g.nstrips;
+    if (ci < nwall) {
+        *strip = id % a.g.nstrips;
+        *chunk = ci < a.cf_lo ? ci : ci - a.cf_lo + a.cf_hi;
+        return true;
+    }
+    const int id2 = id - nwall * a.g.nstrips;  // edge strips x fast chunks, when no lean kernel takes them
+    if (a.edge_lean || id2 >= E * (a.cf_hi - a.cf_lo)) return false;
+    const int e = id2 % E;
+    *strip = e < a.sf_lo ? e : a.sf_hi + (e - a.sf_lo);
+    *chunk = a.cf_lo + id2 / E;
     return true;
+}
+template <typename T> inline int jacobi_part3_tasks(const JacobiArgs<T>& a) {
+    return a.edge_lean ? (a.sf_lo + (a.g.nstrips - a.sf_hi)) * (a.cf_hi - a.cf_lo) : 0;
 }
 template <typename T> inline int jacobi_part2_tasks(const JacobiArgs<T>& a) {
     const int E = a.sf_lo + (a.g.nstrips - a.sf_hi);
-    return E * a.nchunks + (a.sf_hi - a.sf_lo) * (a.nchunks - (a.cf_hi - a.cf_lo));
+    return a.g.nstrips * (a.nchunks - (a.cf_hi - a.cf_lo)) + (a.edge_lean ? 0 : E * (a.cf_hi - a.cf_lo));
 }
 
 // Fused tentative velocity + right-hand side (see predictor_task)

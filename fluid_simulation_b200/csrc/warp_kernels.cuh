@@ -272,6 +272,33 @@ FB_DEV void apply_y_edges(const Edges<T>& e, const Strip<V, H>& st, int row, Vec
     }
 }
 
+// The same two cells for y edges whose boundary value does not depend on the row (UNSET = copy the
+// neighbour, CONST): everything that is uniform over the rows is decided once per task, and a row
+// costs a shuffle and a few selects, without branches. Used by the lean Jacobi pipeline.
+template <typename T, int V> struct YEdgeUniform {
+    bool lane0_bottom, bot_use, top_use;
+    T bot_v, top_v;
+    unsigned top_bits;
+    template <int H> FB_DEV void init(const Edges<T>& e, const Strip<V, H>& st) {
+        lane0_bottom = st.has_bottom && st.lane == 0;
+        bot_use = e.mode[BOTTOM] == EDGE_CONST;
+        top_use = e.mode[TOP] == EDGE_CONST;
+        bot_v = e.cval[BOTTOM];
+        top_v = e.cval[TOP];
+        top_bits = st.top_bits;  // 0 in every lane of a strip without column Y-1
+    }
+    FB_DEV void apply(Vec<T, V>& out) const {
+        const T below = shfl_up1(out.a[V - 1]);
+        const T nb = bot_use ? bot_v : out.a[1];
+        Vec<T, V> nt;
+#pragma unroll
+        for (int k = 0; k < V; ++k) nt.a[k] = top_use ? top_v : (k > 0 ? out.a[k > 0 ? k - 1 : 0] : below);
+#pragma unroll
+        for (int k = V - 1; k >= 0; --k) out.a[k] = ((top_bits >> k) & 1u) ? nt.a[k] : out.a[k];
+        out.a[0] = lane0_bottom ? nb : out.a[0];
+    }
+};
+
 // store only interior columns [1, Y-2] of a row (edge cells of u_next/v_next/rhs are never
 // written by the reference, SerialNavierStokes.cpp:299-300,326-327)
 template <typename T, int V>
@@ -453,8 +480,8 @@ FB_DEV void jacobi_task(const JacobiArgs<T>& A, int strip, int chunk, int lane, 
     Strip<V, H> st;
     st.init(g, strip, lane);
 
-    const int c0 = A.out_lo + chunk * g.rows_per_chunk;
-    const int c1 = min(c0 + g.rows_per_chunk, A.out_hi);
+    int c0, c1;
+    jacobi_chunk_rows(A, chunk, &c0, &c1);
     if (c0 >= c1) return;
     const int slab_hi = g.row0 + g.rows;
     const int r_begin = max(c0 - K, g.row0);
@@ -648,8 +675,8 @@ FB_DEV void jacobi_fast_body(const JacobiArgs<T>& A, int strip, int chunk, int l
     const Geom& g = A.g;
     Strip<V, H> st;
     st.init(g, strip, lane);
-    const int c0 = A.out_lo + chunk * g.rows_per_chunk;
-    const int c1 = min(c0 + g.rows_per_chunk, A.out_hi);
+    int c0, c1;
+    jacobi_chunk_rows(A, chunk, &c0, &c1);
     if (c0 >= c1) return;
     const int r_begin = c0 - K;
     const int load_hi = min(c1 + K, g.row0 + g.rows);
@@ -674,6 +701,9 @@ FB_DEV void jacobi_fast_body(const JacobiArgs<T>& A, int strip, int chunk, int l
         w[t][1] = vzero<T, V>();
         bw[t] = vzero<T, V>();
     }
+
+    YEdgeUniform<T, V> ye;
+    if (YEDGE) ye.init(A.e, st);
 
     LaneRing<T, V, D> ring;
     ring.init(tid, nthreads);
@@ -710,10 +740,8 @@ FB_DEV void jacobi_fast_body(const JacobiArgs<T>& A, int strip, int chunk, int l
 #pragma unroll
             for (int t = 1; t <= K; ++t) {
                 VT out = jacobi_row<T, V>(w[t - 1][0], w[t - 1][1], cur, bw[t - 1]);
-                // strips holding column 0 or Y-1: the y-edge cells of every level (:163-175). The row
-                // index only addresses per-cell boundary arrays; rows of the pipeline fill and of the
-                // rounded-up tail are clamped (their values are never stored).
-                if (YEDGE) apply_y_edges<T, V, H>(A.e, st, min(max(r + u - t, 1), g.X - 2), out, out, out);
+                // strips holding column 0 or Y-1: the y-edge cells of every level (:163-175)
+                if (YEDGE) ye.apply(out);
                 w[t - 1][0] = w[t - 1][1];
                 w[t - 1][1] = cur;
                 cur = out;
@@ -735,17 +763,12 @@ FB_DEV void jacobi_fast_task(const JacobiArgs<T>& A, int strip, int chunk, int l
     else jacobi_fast_body<T, V, K, true, false>(A, strip, chunk, lane, tid, nthreads);
 }
 
-// One task of the GENERAL kernel of a split launch. Strips that hold a y-edge column but whose
-// chunk is a fast chunk (no x wall within reach of the pipeline) run the lean pipeline with the
-// y-edge cells added; only chunks at an x wall, masked sweeps and unsplit launches need jacobi_task.
-template <typename T, int V, int K, bool MASK>
-FB_DEV void jacobi_general_task(const JacobiArgs<T>& A, int strip, int chunk, int lane, int tid, int nthreads) {
-    if (!MASK && A.part == 2 && chunk >= A.cf_lo && chunk < A.cf_hi) {
-        if (A.hx == T(1) && A.hy == T(1)) jacobi_fast_body<T, V, K, false, true>(A, strip, chunk, lane, tid, nthreads);
-        else jacobi_fast_body<T, V, K, true, true>(A, strip, chunk, lane, tid, nthreads);
-        return;
-    }
-    jacobi_task<T, V, K, MASK>(A, strip, chunk, lane, tid, nthreads);
+// One task of the EDGE kernel of a split launch: a strip that holds a y-edge column, in a chunk
+// with no x wall within reach of the pipeline. The lean pipeline with the y-edge cells added.
+template <typename T, int V, int K>
+FB_DEV void jacobi_edge_task(const JacobiArgs<T>& A, int strip, int chunk, int lane, int tid, int nthreads) {
+    if (A.hx == T(1) && A.hy == T(1)) jacobi_fast_body<T, V, K, false, true>(A, strip, chunk, lane, tid, nthreads);
+    else jacobi_fast_body<T, V, K, true, true>(A, strip, chunk, lane, tid, nthreads);
 }
 
 // =========================================================================================

@@ -136,8 +136,8 @@ static void jac_k(const fb::JacobiArgs<T>& a, bool mask, int nchunks) {
         run_grid(nwarps_x, ny, [&](int wx, int by, int l) {
             int strip, chunk;
             if (!fb::jacobi_decode_task(g, wx / W, by, wx % W, W, &strip, &chunk)) return;
-            if (K == 1 && mask) fb::jacobi_general_task<T, V, 1, true>(g, strip, chunk, l, l, 32);
-            else fb::jacobi_general_task<T, V, K, false>(g, strip, chunk, l, l, 32);
+            if (K == 1 && mask) fb::jacobi_task<T, V, 1, true>(g, strip, chunk, l, l, 32);
+            else fb::jacobi_task<T, V, K, false>(g, strip, chunk, l, l, 32);
         });
     };
     auto round_up = [](int n) { return (n + W - 1) / W * W; };
@@ -147,14 +147,20 @@ static void jac_k(const fb::JacobiArgs<T>& a, bool mask, int nchunks) {
         general(all, round_up(a.g.nstrips), nchunks);
         return;
     }
-    fb::JacobiArgs<T> gen = a, fast = a;
+    fb::JacobiArgs<T> gen = a, edge = a, fast = a;
     gen.part = 2;
+    edge.part = 3;
     fast.part = 1;
     if (getenv("FLUIDB200_EMU_VERBOSE"))
-        std::fprintf(stderr, "EMU split K=%d: strips [%d,%d) of %d, chunks [%d,%d) of %d -> %d fast, %d general tasks\n", K,
+        std::fprintf(stderr, "EMU split K=%d: strips [%d,%d) of %d, chunks [%d,%d) of %d -> %d fast, %d edge, %d general tasks (head %d, tail %d)\n", K,
                      a.sf_lo, a.sf_hi, a.g.nstrips, a.cf_lo, a.cf_hi, nchunks, (a.sf_hi - a.sf_lo) * (a.cf_hi - a.cf_lo),
-                     fb::jacobi_part2_tasks(gen));
+                     fb::jacobi_part3_tasks(edge), fb::jacobi_part2_tasks(gen), a.head, a.tail);
     general(gen, round_up(fb::jacobi_part2_tasks(gen)), 1);
+    run_grid(round_up(fb::jacobi_part3_tasks(edge)), 1, [&](int wx, int by, int l) {
+        int strip, chunk;
+        if (!fb::jacobi_decode_task(edge, wx / W, by, wx % W, W, &strip, &chunk)) return;
+        fb::jacobi_edge_task<T, V, K>(edge, strip, chunk, l, l, 32);
+    });
     run_grid(round_up(a.sf_hi - a.sf_lo), a.cf_hi - a.cf_lo, [&](int wx, int by, int l) {
         int strip, chunk;
         if (!fb::jacobi_decode_task(fast, wx / W, by, wx % W, W, &strip, &chunk)) return;

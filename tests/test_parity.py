@@ -275,3 +275,22 @@ def test_single_kernel_and_split_launch_agree(Solver, env, knob):
     o.solve()
     H.compare_with(s, o, tag=knob)
     s.close()
+
+
+@pytest.mark.parametrize("kmax", [1, 2, 3, 4, 5, 6, 7, 8])
+@pytest.mark.parametrize("unit", [False, True])
+def test_split_launch_every_depth(Solver, kmax, unit):
+    """All three kernels of the split Jacobi launch at every blocking depth: the lean FAST kernel on
+    the middle strip, the lean EDGE kernel on the strips holding column 0 / Y-1 (cavity edges are
+    CONST or UNSET), the general kernel on the short chunks at the x walls."""
+    X, Y = 72, 300
+    dom = (float(X - 1), float(Y - 1)) if unit else (1.0, 1.0)
+    o = Oracle(X, Y, *dom).set_cavity()
+    o.time_step, o.num_iterations, o.num_poisson_iterations = (0.001 if unit else 1e-5), 2, 2 * kmax
+    s = Solver(X, Y, *dom).set_cavity()
+    s.time_step, s.num_iterations, s.num_poisson_iterations = o.time_step, 2, 2 * kmax
+    s.set_sweeps_per_launch(kmax)
+    s.migrateSolve()
+    o.solve()
+    H.compare_with(s, o, tag=f"split-depth/k{kmax}/unit{unit}")
+    s.close()
