@@ -50,9 +50,10 @@ template <typename T> int num_strips(int Y, int H) {
 }
 
 // Warp tasks aimed for per launch (measured on B200 at 16384^2): the Jacobi pipeline pays K halo rows
-// per chunk end and is best around 9 waves; the two one-pass kernels have a 1-2 row halo and keep
-// improving up to ~40 waves.
-constexpr int kJacobiTasks = 148 * 16 * 9, kLightTasks = 148 * 16 * 40;
+// per chunk end and is best around 9 x 2368 tasks up to depth 6 and 5 x 2368 at depth 7-8 (longer
+// chunks: fewer recomputed rows); the two one-pass kernels have a 1-2 row halo and keep improving
+// up to ~40 x 2368.
+constexpr int kJacobiTasks = 148 * 16 * 9, kJacobiTasksDeep = 148 * 16 * 5, kLightTasks = 148 * 16 * 40;
 
 // Split `n` output rows into chunks. More chunks = more warps in flight and a smaller tail, but
 // every chunk recomputes `halo` rows at each end. The chunk count is chosen so that the grid is
@@ -236,6 +237,7 @@ int poisson_t(const fluidb200_slab* g, const void* p_in, void* p_out, const void
     int rpc, nchunks;
     // resident CTAs per SM of the kernel that does the bulk of the work (the lean FAST kernel)
     const int ctas_per_sm = sweeps <= 2 ? 5 : sweeps <= 6 ? 4 : 3;
+    const int tasks = sweeps >= 7 ? kJacobiTasksDeep : kJacobiTasks;
     // First try: the chunks at an x wall as short as the pipeline allows (the next chunk must start
     // at row >= 2K+2, the previous one end at row <= X-K-2), because only the register-heavy general
     // kernel can run them; the rows between are chunked uniformly and go to the lean kernels.
@@ -244,14 +246,14 @@ int poisson_t(const fluidb200_slab* g, const void* p_in, void* p_out, const void
     a.tail = out_hi == g->X ? sweeps + 1 : 0;
     a.part = 0;
     if (!use_mask && (a.head || a.tail) && n - a.head - a.tail >= 4 * sweeps + 8) {
-        plan_chunks(n - a.head - a.tail, sweeps, nstrips, ctas_per_sm, kJacobiTasks, &rpc, &nchunks);
+        plan_chunks(n - a.head - a.tail, sweeps, nstrips, ctas_per_sm, tasks, &rpc, &nchunks);
         nchunks += (a.head > 0) + (a.tail > 0);
         a.g = make_geom(g, nstrips, rpc);
         split_jacobi<T>(&a, g, sweeps, nchunks, use_mask);
     }
     if (a.part == 0) {  // no split (small grid, masked sweep, no wall in range): plain uniform chunks
         a.head = a.tail = 0;
-        plan_chunks(n, sweeps, nstrips, ctas_per_sm, kJacobiTasks, &rpc, &nchunks);
+        plan_chunks(n, sweeps, nstrips, ctas_per_sm, tasks, &rpc, &nchunks);
         a.g = make_geom(g, nstrips, rpc);
         split_jacobi<T>(&a, g, sweeps, nchunks, use_mask);
     }
@@ -572,12 +574,13 @@ extern "C" int fluidb200_create(fluidb200_solver** out, int dtype, int X, int Y,
     s->dtype = dtype; s->X = X; s->Y = Y;
     s->esize = dtype == FLUIDB200_F32 ? 4 : 8;
     s->pitch = ((int64_t)Y + 31) / 32 * 32;
-    // Temporal-blocking depth. Measured on B200 (fp32): 6 for grids that fill the GPU many times over
-    // (16384^2: 2.86 Tcell-sweeps/s), 4 around 8192^2, 3 below (short pipelines fill faster and the
-    // halo recomputation weighs more on small chunks). FLUIDB200_KMAX / set_sweeps_per_launch override.
+    // Temporal-blocking depth, from depth sweeps on B200 (fp32, Gcell-sweeps/s at the chosen depth):
+    // 8 from 8192^2 up (2880; 16384^2: 3640), 7 around 6144^2 (2290), 5 around 3072^2-4096^2 (940-1460),
+    // 3 below (2048^2: 590, 1000^2: 170): short pipelines fill faster and the recomputed halo weighs
+    // more on small chunks. FLUIDB200_KMAX / set_sweeps_per_launch override.
     {
         const long long cells = (long long)X * Y;
-        s->kmax = env_int("FLUIDB200_KMAX", cells >= 150000000LL ? 6 : cells >= 40000000LL ? 4 : 3);
+        s->kmax = env_int("FLUIDB200_KMAX", cells >= 60000000LL ? 8 : cells >= 30000000LL ? 7 : cells >= 8000000LL ? 5 : 3);
     }
     fluidb200_set_domain(s, domain_x, domain_y);
     if (fbk::be_stream_create(&s->stream) != 0) {

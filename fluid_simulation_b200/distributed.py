@@ -44,7 +44,7 @@ class SlabSolver:
     """One rank's slab of a lid-driven cavity (boundary set-up of fluid_cpp/main.cpp:43-55)."""
 
     def __init__(self, X, Y, domain_x, domain_y, dtype=np.float32, *, rank=0, world=1, group=None,
-                 device="cuda", kmax=6, libpath=None, overlap=True):
+                 device="cuda", kmax=8, libpath=None, overlap=True):
         import torch
         self.torch = torch
         self.dist = torch.distributed if world > 1 else None
