@@ -211,10 +211,18 @@ def run_single(args):
     achieved = alg_bytes / (jac_launch_ms * 1e-3) / 1e9
     peak, peak_src = peaks()
     kernel = f"jacobi_fast_kernel<float,4,{KMAX}>"   # + the edge and wall kernels of the same split launch
-    traffic = None   # ncu dram bytes per launch for exactly this kernel and grid, when a capture is on file
+    # ncu dram bytes per launch for exactly these kernels and this grid, when captures are on file: the mean over
+    # the launches of one step (same rule as step_poisson: launch i takes ceil(left / launches left) sweeps)
+    traffic = None
     try:
         with open(os.path.join(ROOT, "profiles", "ncu_traffic_r1.json")) as f:
-            traffic = json.load(f).get(f"{kernel}@{X}x{Y}")
+            table = json.load(f)
+        left, per_launch = SWEEPS, []
+        for i in range(n_launch):
+            k = -(-left // (n_launch - i))
+            left -= k
+            per_launch.append(table[f"jacobi_fast_kernel<float,4,{k}>@{X}x{Y}"])
+        traffic = sum(per_launch) / len(per_launch)
     except Exception:
         pass
     roofline = {"bound": "hbm", "kernel": kernel, "achieved": achieved, "peak": peak,
