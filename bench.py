@@ -263,6 +263,50 @@ def run_single(args):
            "d2h_bytes_per_step": 3 * cells * 4, "steps": e2e_steps, "ms_per_step": e2e_s / e2e_steps * 1e3,
            "api": "fluidb200_upload(u,v,p pinned host) + fluidb200_solve(1 step) + fluidb200_download(u,v,p)"}
     assert bool(torch.isfinite(host[0]).all()), "non-finite field after the e2e steps"
+
+    # The same calls from TWO host threads, each with its own solver handle, stream and pinned buffers (two
+    # independent simulations in flight): the upload of one overlaps the download of the other on the full-duplex
+    # link and both hide the compute. Reported beside the single-instance figure, which stays e2e.value.
+    if not os.environ.get("FLUIDB200_SKIP_E2E_PAIR"):
+        import threading
+        s2 = ParallelNavierStokes(X, Y, float(X - 1), float(Y - 1), dtype=np.float32)
+        s2.time_step, s2.kinematic_viscosity, s2.density = DT, NU, RHO
+        s2.num_poisson_iterations, s2.num_iterations = SWEEPS, 1
+        s2.set_sweeps_per_launch(KMAX)
+        s2.upload_cavity(LID)
+        s2._push_params()
+        host2 = [torch.zeros((X, Y), dtype=torch.float32).pin_memory() for _ in range(3)]
+        host2[0][:, Y - 1] = LID
+        fields2 = (C.c_void_p * _lib.NUM_FIELDS)()
+        for i in range(3):
+            fields2[i] = host2[i].data_ptr()
+        own = torch.cuda.Stream()   # the first handle was timed on torch's default stream; give it a stream of its own
+        _lib.check(lib, lib.fluidb200_set_stream(h, own.cuda_stream))
+
+        def worker(handle, flds, hst, n):
+            for _ in range(n):
+                _lib.check(lib, lib.fluidb200_upload(handle, flds, None, None))
+                _lib.check(lib, lib.fluidb200_solve(handle))
+                for i in range(3):
+                    _lib.check(lib, lib.fluidb200_download(handle, i, hst[i].data_ptr()))
+
+        worker(s2._h, fields2, host2, 1)  # warm-up of the second handle
+        torch.cuda.synchronize()
+        per = max(2, e2e_steps)
+        th = [threading.Thread(target=worker, args=(h, fields, host, per)),
+              threading.Thread(target=worker, args=(s2._h, fields2, host2, per))]
+        t0 = time.perf_counter()
+        for t in th:
+            t.start()
+        for t in th:
+            t.join()
+        torch.cuda.synchronize()
+        pair_s = time.perf_counter() - t0
+        e2e["two_instances"] = {"value": cells * 2 * per / pair_s / 1e9, "unit": UNIT, "steps": 2 * per,
+                                "ms_per_step": pair_s / (2 * per) * 1e3,
+                                "api": "the same three calls from two host threads, one solver handle each"}
+        assert bool(torch.isfinite(host2[0]).all())
+        s2.close()
     s.close()
 
     # ---- BASELINE.json configs[1], for the record: 1000 x 1000, 1000 timesteps, 50 sweeps each (the shape the

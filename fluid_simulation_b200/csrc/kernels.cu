@@ -66,7 +66,7 @@ __global__ void __launch_bounds__(kThreads) predictor_kernel(const __grid_consta
 }
 
 template <typename T, int V, bool MASK, int MODE>
-__global__ void __launch_bounds__(kThreads) corrector_kernel(const __grid_constant__ fb::CorrectorArgs<T> A) {
+__global__ void __launch_bounds__(kThreads, 4) corrector_kernel(const __grid_constant__ fb::CorrectorArgs<T> A) {
     const int strip = blockIdx.x * fb::kWarpsPerCta + (threadIdx.x >> 5);
     if (strip >= A.g.nstrips) return;
     fb::corrector_task<T, V, MASK, MODE>(A, strip, blockIdx.y, threadIdx.x & 31);

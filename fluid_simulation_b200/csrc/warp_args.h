@@ -40,6 +40,10 @@ template <typename T> struct Metric {
     double inv_hx2, inv_hy2, inv_hxhy;
     float inv_hx2f, inv_hy2f, inv_hxhyf;
     int mode;
+    // mode 2: the Laplacian numerator t is safe to scale when t == 0 or pow2_lo <= |t| < inf, with
+    // pow2_lo = 2^-120 * max(1, hx*hy) so that t / (hx*hy) is a normal float as well; stored as the
+    // bit pattern minus one (see Flags in warp_kernels.cuh)
+    unsigned pow2_lo_m1;
 };
 inline bool metric_is_pow2(double h) {
     if (!(h > 0)) return false;
@@ -56,6 +60,12 @@ template <typename T> inline Metric<T> make_metric(T hx, T hy, int forced_mode =
     m.inv_hxhy = 1.0 / ((double)hx * (double)hy);
     m.inv_hx2f = (float)m.inv_hx2; m.inv_hy2f = (float)m.inv_hy2; m.inv_hxhyf = (float)m.inv_hxhy;
     m.mode = 0;
+    {
+        const double hxhy = (double)hx * (double)hy;
+        union { float f; unsigned u; } lo;
+        lo.f = (float)(7.52316384526264e-37 /* 2^-120 */ * (hxhy > 1.0 ? hxhy : 1.0));
+        m.pow2_lo_m1 = lo.u - 1u;
+    }
     if (sizeof(T) == 4) {
         const double lo = 9.094947017729282e-13 /* 2^-40 */, hi = 1099511627776.0 /* 2^40 */;
         const bool sane = (double)hx >= lo && (double)hx <= hi && (double)hy >= lo && (double)hy <= hi;

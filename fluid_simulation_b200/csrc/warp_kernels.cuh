@@ -56,6 +56,17 @@ template <typename T> struct Ar;
 //              division is an exact scaling, i.e. one correctly rounded multiplication.
 enum { DIV_EXACT = 0, DIV_FAST = 1, DIV_POW2 = 2 };
 
+// What the division-free modes collect over the cells of one row strip. The row is recomputed with
+// DIV_EXACT when raised() says so; nothing branches per cell.
+struct Flags {
+    bool bad = false;        // DIV_FAST: some cell was flagged
+    // DIV_POW2: over the Laplacian numerators t of the row, the minimum of (bits(|t|) - 1), where a zero
+    // wraps to the top and so never counts as small, and the maximum of bits(|t|): two integer
+    // min/max per value instead of a range test per cell
+    unsigned lo = 0xffffffffu, hi = 0u;
+    FB_DEV bool raised(unsigned pow2_lo_m1) const { return bad || lo < pow2_lo_m1 || hi >= 0x7f800000u; }
+};
+
 template <> struct Ar<float> {
     static FB_DEV float add(float a, float b) { return __fadd_rn(a, b); }
     static FB_DEV float sub(float a, float b) { return __fsub_rn(a, b); }
@@ -72,14 +83,14 @@ template <> struct Ar<float> {
     // mostly-zero fields of an impulsively started cavity hit all the time.
     // DIV_POW2: d * (1/h2) is the same real number as d / h2 and is rounded once, like the division.
     template <int MODE>
-    static FB_DEV float cdiff(float a, float b, float h, float h2, double inv_h2, float inv_h2f, bool& bad) {
+    static FB_DEV float cdiff(float a, float b, float h, float h2, double inv_h2, float inv_h2f, Flags& fl) {
         (void)h;
         const float d = __fsub_rn(a, b);
         if (MODE == DIV_EXACT) return __fdiv_rn(d, h2);
         if (MODE == DIV_POW2) return __fmul_rn(d, inv_h2f);
         // (float -> double is exact for every input, subnormals included; inf/nan propagate like the division)
         const float r = __double2float_rn(__dmul_rn((double)d, inv_h2));
-        bad |= (d != 0.0f) && (fabsf(r) < 7.52316385e-37f /* 2^-120 */);
+        fl.bad |= (d != 0.0f) && (fabsf(r) < 7.52316385e-37f /* 2^-120 */);
         return r;
     }
     // (s - 4.*c) / hx / hy with s already rounded to float: the one place the fp32 path is
@@ -95,7 +106,7 @@ template <> struct Ar<float> {
     // RN32(D * 2^k) = RN32(D) * 2^k = fmaf(-4, c, s) * 2^k (double rounding of a float sum is
     // innocuous); values at the edge of the subnormal range are flagged.
     template <int MODE>
-    static FB_DEV float lap_tail(float s, float c, float hx, float hy, double inv_hxhy, float inv_hxhyf, bool& bad) {
+    static FB_DEV float lap_tail(float s, float c, float hx, float hy, double inv_hxhy, float inv_hxhyf, Flags& fl) {
         if (MODE == DIV_EXACT) {
             double t = __fma_rn(-4.0, (double)c, (double)s);
             t = __ddiv_rn(t, (double)hx);
@@ -105,9 +116,10 @@ template <> struct Ar<float> {
         if (MODE == DIV_POW2) {
             const float t = __fmaf_rn(-4.0f, c, s);
             const float r = __fmul_rn(t, inv_hxhyf);
-            // 2^-120 <= |t|, |r| <= 2^120, or t == 0  (one unsigned compare each on the exponent field)
-            const unsigned ta = __float_as_uint(t) & 0x7fffffffu, ra = __float_as_uint(r) & 0x7fffffffu;
-            bad |= (ta != 0u) && ((ta - 0x03800000u) >= 0x78000000u || (ra - 0x03800000u) >= 0x78000000u);
+            // t == 0 or pow2_lo <= |t| < inf (then r is normal too), checked per row by Flags::raised
+            const unsigned ta = __float_as_uint(t) & 0x7fffffffu;
+            fl.lo = min(fl.lo, ta - 1u);
+            fl.hi = max(fl.hi, ta);
             return r;
         }
         const double d = __fma_rn(-4.0, (double)c, (double)s);
@@ -115,7 +127,7 @@ template <> struct Ar<float> {
         const float r = __double2float_rn(q);
         // distance of the 29 sub-float bits of q from the midpoint pattern, as one unsigned compare
         const unsigned low = (unsigned)__double2loint(q) & 0x1fffffffu;
-        bad |= (low - 0x0ffffff0u) <= 32u || (fabsf(r) < 7.52316385e-37f && d != 0.0);
+        fl.bad |= (low - 0x0ffffff0u) <= 32u || (fabsf(r) < 7.52316385e-37f && d != 0.0);
         return r;
     }
     // t *= -0.25 : the double multiply is exact, so this is one float rounding (subnormals).
@@ -126,11 +138,11 @@ template <> struct Ar<double> {
     static FB_DEV double add(double a, double b) { return __dadd_rn(a, b); }
     static FB_DEV double sub(double a, double b) { return __dsub_rn(a, b); }
     static FB_DEV double mul(double a, double b) { return __dmul_rn(a, b); }
-    template <int MODE> static FB_DEV double cdiff(double a, double b, double h, double h2, double, double, bool&) {
+    template <int MODE> static FB_DEV double cdiff(double a, double b, double h, double h2, double, double, Flags&) {
         (void)h2;
         return __ddiv_rn(__dmul_rn(__dsub_rn(a, b), 0.5), h);  // "/ 2." is an exact halving
     }
-    template <int MODE> static FB_DEV double lap_tail(double s, double c, double hx, double hy, double, double, bool&) {
+    template <int MODE> static FB_DEV double lap_tail(double s, double c, double hx, double hy, double, double, Flags&) {
         double d = __fma_rn(-4.0, c, s);  // 4.*c exact -> single rounding
         d = __ddiv_rn(d, hx);
         return __ddiv_rn(d, hy);
@@ -788,16 +800,16 @@ template <typename T> struct UV {
 // would pin them to local memory in the hot loop.
 template <typename T, int MODE>
 FB_DEV UV<T> tentative_cell(const PredictorArgs<T>& A, T uc, T vc, T uxm, T uxp, T uym, T uyp, T vxm, T vxp, T vym,
-                            T vyp, bool& bad) {
+                            T vyp, Flags& fl) {
     using A_ = Ar<T>;
-    const T du_dx = A_::template cdiff<MODE>(uxp, uxm, A.m.hx, A.m.hx2, A.m.inv_hx2, A.m.inv_hx2f, bad);
-    const T dv_dx = A_::template cdiff<MODE>(vxp, vxm, A.m.hx, A.m.hx2, A.m.inv_hx2, A.m.inv_hx2f, bad);
-    const T du_dy = A_::template cdiff<MODE>(uyp, uym, A.m.hy, A.m.hy2, A.m.inv_hy2, A.m.inv_hy2f, bad);
-    const T dv_dy = A_::template cdiff<MODE>(vyp, vym, A.m.hy, A.m.hy2, A.m.inv_hy2, A.m.inv_hy2f, bad);
+    const T du_dx = A_::template cdiff<MODE>(uxp, uxm, A.m.hx, A.m.hx2, A.m.inv_hx2, A.m.inv_hx2f, fl);
+    const T dv_dx = A_::template cdiff<MODE>(vxp, vxm, A.m.hx, A.m.hx2, A.m.inv_hx2, A.m.inv_hx2f, fl);
+    const T du_dy = A_::template cdiff<MODE>(uyp, uym, A.m.hy, A.m.hy2, A.m.inv_hy2, A.m.inv_hy2f, fl);
+    const T dv_dy = A_::template cdiff<MODE>(vyp, vym, A.m.hy, A.m.hy2, A.m.inv_hy2, A.m.inv_hy2f, fl);
     const T su = A_::add(A_::add(A_::add(uxm, uxp), uyp), uym);
     const T sv = A_::add(A_::add(A_::add(vxm, vxp), vyp), vym);
-    const T u_lap = A_::template lap_tail<MODE>(su, uc, A.m.hx, A.m.hy, A.m.inv_hxhy, A.m.inv_hxhyf, bad);
-    const T v_lap = A_::template lap_tail<MODE>(sv, vc, A.m.hx, A.m.hy, A.m.inv_hxhy, A.m.inv_hxhyf, bad);
+    const T u_lap = A_::template lap_tail<MODE>(su, uc, A.m.hx, A.m.hy, A.m.inv_hxhy, A.m.inv_hxhyf, fl);
+    const T v_lap = A_::template lap_tail<MODE>(sv, vc, A.m.hx, A.m.hy, A.m.inv_hxhy, A.m.inv_hxhyf, fl);
     const T du_dt = A_::sub(A_::sub(A_::mul(A.nu, u_lap), A_::mul(uc, du_dx)), A_::mul(vc, du_dy));
     const T dv_dt = A_::sub(A_::sub(A_::mul(A.nu, v_lap), A_::mul(uc, dv_dx)), A_::mul(vc, dv_dy));
     UV<T> r;
@@ -808,37 +820,35 @@ FB_DEV UV<T> tentative_cell(const PredictorArgs<T>& A, T uc, T vc, T uxm, T uxp,
 template <typename T>
 FB_DEV_NOINLINE UV<T> tentative_cell_exact(const PredictorArgs<T>& A, T uc, T vc, T uxm, T uxp, T uym, T uyp, T vxm,
                                            T vxp, T vym, T vyp) {
-    bool bad = false;
-    return tentative_cell<T, DIV_EXACT>(A, uc, vc, uxm, uxp, uym, uyp, vxm, vxp, vym, vyp, bad);
+    Flags fl;
+    return tentative_cell<T, DIV_EXACT>(A, uc, vc, uxm, uxp, uym, uyp, vxm, vxp, vym, vyp, fl);
 }
 
 // u_next, v_next of one interior row strip from rows x-1 (um,vm), x (u0,v0), x+1 (up,vp) of u, v.
-// All cells are first evaluated in MODE without branching; a cell the division-free arithmetic
-// flagged is then recomputed with IEEE divisions (per lane; the shuffles stay outside).
+// All cells are first evaluated in MODE without branching; if the division-free arithmetic raised a
+// flag on any of this lane's cells they are recomputed with IEEE divisions (per lane; the shuffles
+// stay outside).
 template <typename T, int V, int MODE>
 FB_DEV void tentative_row(const PredictorArgs<T>& A, const Vec<T, V>& um, const Vec<T, V>& u0, const Vec<T, V>& up_,
                           const Vec<T, V>& vm, const Vec<T, V>& v0, const Vec<T, V>& vp_, Vec<T, V>& us, Vec<T, V>& vs) {
     Vec<T, V> uym, uyp, vym, vyp;
     y_neighbours<T, V>(u0, uym, uyp);
     y_neighbours<T, V>(v0, vym, vyp);
-    bool bad[V];
+    Flags fl;
 #pragma unroll
     for (int e = 0; e < V; ++e) {
-        bad[e] = false;
         const UV<T> r = tentative_cell<T, MODE>(A, u0.a[e], v0.a[e], um.a[e], up_.a[e], uym.a[e], uyp.a[e], vm.a[e],
-                                                vp_.a[e], vym.a[e], vyp.a[e], bad[e]);
+                                                vp_.a[e], vym.a[e], vyp.a[e], fl);
         us.a[e] = r.u;
         vs.a[e] = r.v;
     }
-    if (MODE != DIV_EXACT) {
+    if (MODE != DIV_EXACT && fl.raised(A.m.pow2_lo_m1)) {
 #pragma unroll
         for (int e = 0; e < V; ++e) {
-            if (bad[e]) {
-                const UV<T> r = tentative_cell_exact<T>(A, u0.a[e], v0.a[e], um.a[e], up_.a[e], uym.a[e], uyp.a[e],
-                                                        vm.a[e], vp_.a[e], vym.a[e], vyp.a[e]);
-                us.a[e] = r.u;
-                vs.a[e] = r.v;
-            }
+            const UV<T> r = tentative_cell_exact<T>(A, u0.a[e], v0.a[e], um.a[e], up_.a[e], uym.a[e], uyp.a[e],
+                                                    vm.a[e], vp_.a[e], vym.a[e], vyp.a[e]);
+            us.a[e] = r.u;
+            vs.a[e] = r.v;
         }
     }
 }
@@ -846,31 +856,27 @@ FB_DEV void tentative_row(const PredictorArgs<T>& A, const Vec<T, V>& um, const 
 // right-hand side of one interior cell from u_next at x-1, x+1 and v_next at y-1, y+1
 // (SerialNavierStokes.cpp:325-335)
 template <typename T, int MODE>
-FB_DEV T rhs_cell(const PredictorArgs<T>& A, T us_m, T us_p, T vs_ym, T vs_yp, bool& bad) {
+FB_DEV T rhs_cell(const PredictorArgs<T>& A, T us_m, T us_p, T vs_ym, T vs_yp, Flags& fl) {
     using A_ = Ar<T>;
-    const T du_next_dx = A_::template cdiff<MODE>(us_p, us_m, A.m.hx, A.m.hx2, A.m.inv_hx2, A.m.inv_hx2f, bad);
-    const T dv_next_dy = A_::template cdiff<MODE>(vs_yp, vs_ym, A.m.hy, A.m.hy2, A.m.inv_hy2, A.m.inv_hy2f, bad);
+    const T du_next_dx = A_::template cdiff<MODE>(us_p, us_m, A.m.hx, A.m.hx2, A.m.inv_hx2, A.m.inv_hx2f, fl);
+    const T dv_next_dy = A_::template cdiff<MODE>(vs_yp, vs_ym, A.m.hy, A.m.hy2, A.m.inv_hy2, A.m.inv_hy2f, fl);
     return A_::mul(A.rho_over_dt, A_::add(du_next_dx, dv_next_dy));
 }
 template <typename T>
 FB_DEV_NOINLINE T rhs_cell_exact(const PredictorArgs<T>& A, T us_m, T us_p, T vs_ym, T vs_yp) {
-    bool bad = false;
-    return rhs_cell<T, DIV_EXACT>(A, us_m, us_p, vs_ym, vs_yp, bad);
+    Flags fl;
+    return rhs_cell<T, DIV_EXACT>(A, us_m, us_p, vs_ym, vs_yp, fl);
 }
 template <typename T, int V, int MODE>
 FB_DEV Vec<T, V> rhs_row(const PredictorArgs<T>& A, const Vec<T, V>& us_m, const Vec<T, V>& us_p, const Vec<T, V>& vs0) {
     Vec<T, V> vym, vyp, q;
     y_neighbours<T, V>(vs0, vym, vyp);
-    bool bad[V];
+    Flags fl;
 #pragma unroll
-    for (int e = 0; e < V; ++e) {
-        bad[e] = false;
-        q.a[e] = rhs_cell<T, MODE>(A, us_m.a[e], us_p.a[e], vym.a[e], vyp.a[e], bad[e]);
-    }
-    if (MODE != DIV_EXACT) {
+    for (int e = 0; e < V; ++e) q.a[e] = rhs_cell<T, MODE>(A, us_m.a[e], us_p.a[e], vym.a[e], vyp.a[e], fl);
+    if (MODE != DIV_EXACT && fl.raised(A.m.pow2_lo_m1)) {
 #pragma unroll
-        for (int e = 0; e < V; ++e)
-            if (bad[e]) q.a[e] = rhs_cell_exact<T>(A, us_m.a[e], us_p.a[e], vym.a[e], vyp.a[e]);
+        for (int e = 0; e < V; ++e) q.a[e] = rhs_cell_exact<T>(A, us_m.a[e], us_p.a[e], vym.a[e], vyp.a[e]);
     }
     return q;
 }
@@ -920,6 +926,7 @@ FB_DEV void predictor_task(const PredictorArgs<T>& A, int strip, int chunk, int 
     const int fast_lo = max(r_begin, 4);
     int nfast = min(r_end, X - 1) - fast_lo + 1;
     if (y_edges || nfast < 0) nfast = 0;
+    if ((long long)(load_hi - r_begin + 1) * g.pitch >= (1LL << 31)) nfast = 0;  // 32-bit offsets in the fast loop
     nfast -= nfast % U;
     const int fast_hi = fast_lo + nfast - 1;
 
@@ -982,20 +989,28 @@ FB_DEV void predictor_task(const PredictorArgs<T>& A, int strip, int chunk, int 
         if (phase == 1 || nfast == 0) break;
         // ---------------- FAST path ----------------
         const int pmax = load_hi - 1;
-        // rows of u and v are prefetched D steps ahead through the per-lane cp.async ring
+        // rows of u and v are prefetched D steps ahead through the per-lane cp.async ring; inside the
+        // loop the row to fetch is a 32-bit element offset from row r (clamped at the last loaded row)
+        // and the three store pointers run along with the steps
         constexpr int D = 4;
         static_assert(D % U == 0, "ring depth must be a multiple of the unroll factor");
         LaneRing<T, V, D> ring;
         ring.init(tid, nthreads);
+        const T* ubase = up + (long long)r * g.pitch;
+        const T* vbase = vp + (long long)r * g.pitch;
+        const unsigned pitch32 = (unsigned)g.pitch;
+        const unsigned pmax_off = (unsigned)(pmax - r) * pitch32;
 #pragma unroll
         for (int j = 0; j < D; ++j) {
-            ring.fetch(j, 0, up + (long long)min(r + j, pmax) * g.pitch);
-            ring.fetch(j, 1, vp + (long long)min(r + j, pmax) * g.pitch);
+            const unsigned off = min((unsigned)j * pitch32, pmax_off);
+            ring.fetch(j, 0, ubase + off);
+            ring.fetch(j, 1, vbase + off);
             ring.commit();
         }
-        T* uso = A.us + sbase;
-        T* vso = A.vs + sbase;
-        T* rho = A.rhs + sbase;
+        unsigned poff = min((unsigned)D * pitch32, pmax_off);
+        T* uso = A.us + sbase + (long long)(r - 1) * g.pitch;   // row ra = r-1 of u_next, v_next
+        T* vso = A.vs + sbase + (long long)(r - 1) * g.pitch;
+        T* rho = A.rhs + sbase + (long long)(r - 2) * g.pitch;  // row rb = r-2 of the right-hand side
         int ring_pos = 0;
 #pragma unroll 1
         for (; r <= fast_hi; r += U) {
@@ -1004,19 +1019,22 @@ FB_DEV void predictor_task(const PredictorArgs<T>& A, int strip, int chunk, int 
                 const int slot = ring_pos + k;
                 ring.template wait<D - 1>();
                 const VT cu = ring.read(slot, 0), cv = ring.read(slot, 1);
-                const long long nxt = (long long)min(r + k + D, pmax) * g.pitch;
-                ring.fetch(slot, 0, up + nxt);
-                ring.fetch(slot, 1, vp + nxt);
+                ring.fetch(slot, 0, ubase + poff);
+                ring.fetch(slot, 1, vbase + poff);
                 ring.commit();
+                poff = min(poff + pitch32, pmax_off);
                 VT us, vs;
                 tentative_row<T, V, MODE>(A, wu[0], wu[1], cu, wv[0], wv[1], cv, us, vs);
                 const int ra = r + k - 1, rb = r + k - 2;
                 if (st.st_ok && ra >= s0 && ra < s1) {
-                    st_vec<T, V>(uso + (long long)ra * g.pitch, us);
-                    st_vec<T, V>(vso + (long long)ra * g.pitch, vs);
+                    st_vec<T, V>(uso, us);
+                    st_vec<T, V>(vso, vs);
                 }
                 const VT q = rhs_row<T, V, MODE>(A, wus[0], us, wvs);
-                if (st.st_ok && rb >= b0 && rb < b1) st_vec<T, V>(rho + (long long)rb * g.pitch, q);
+                if (st.st_ok && rb >= b0 && rb < b1) st_vec<T, V>(rho, q);
+                uso += pitch32;
+                vso += pitch32;
+                rho += pitch32;
                 wu[0] = wu[1]; wu[1] = cu;
                 wv[0] = wv[1]; wv[1] = cv;
                 wus[0] = wus[1]; wus[1] = us;
@@ -1064,10 +1082,10 @@ FB_DEV Vec<T, V> velocity_wall_row(const Edges<T>& e, int edge, int x, const Vec
 // corrected u, v of one interior cell from p at x-1, x+1, y-1, y+1 and u_next, v_next
 // (SerialNavierStokes.cpp:338-350)
 template <typename T, int MODE>
-FB_DEV UV<T> correct_cell(const CorrectorArgs<T>& A, T pxm, T pxp, T pym, T pyp, T us, T vs, bool& bad) {
+FB_DEV UV<T> correct_cell(const CorrectorArgs<T>& A, T pxm, T pxp, T pym, T pyp, T us, T vs, Flags& fl) {
     using A_ = Ar<T>;
-    const T dp_dx = A_::template cdiff<MODE>(pxp, pxm, A.m.hx, A.m.hx2, A.m.inv_hx2, A.m.inv_hx2f, bad);
-    const T dp_dy = A_::template cdiff<MODE>(pyp, pym, A.m.hy, A.m.hy2, A.m.inv_hy2, A.m.inv_hy2f, bad);
+    const T dp_dx = A_::template cdiff<MODE>(pxp, pxm, A.m.hx, A.m.hx2, A.m.inv_hx2, A.m.inv_hx2f, fl);
+    const T dp_dy = A_::template cdiff<MODE>(pyp, pym, A.m.hy, A.m.hy2, A.m.inv_hy2, A.m.inv_hy2f, fl);
     UV<T> r;
     r.u = A_::sub(us, A_::mul(A.dt_over_rho, dp_dx));
     r.v = A_::sub(vs, A_::mul(A.dt_over_rho, dp_dy));
@@ -1075,30 +1093,27 @@ FB_DEV UV<T> correct_cell(const CorrectorArgs<T>& A, T pxm, T pxp, T pym, T pyp,
 }
 template <typename T>
 FB_DEV_NOINLINE UV<T> correct_cell_exact(const CorrectorArgs<T>& A, T pxm, T pxp, T pym, T pyp, T us, T vs) {
-    bool bad = false;
-    return correct_cell<T, DIV_EXACT>(A, pxm, pxp, pym, pyp, us, vs, bad);
+    Flags fl;
+    return correct_cell<T, DIV_EXACT>(A, pxm, pxp, pym, pyp, us, vs, fl);
 }
 template <typename T, int V, int MODE>
 FB_DEV void correct_row(const CorrectorArgs<T>& A, const Vec<T, V>& pm, const Vec<T, V>& p0, const Vec<T, V>& pp_,
                         const Vec<T, V>& us, const Vec<T, V>& vs, Vec<T, V>& un, Vec<T, V>& vn) {
     Vec<T, V> pym, pyp;
     y_neighbours<T, V>(p0, pym, pyp);
-    bool bad[V];
+    Flags fl;
 #pragma unroll
     for (int e = 0; e < V; ++e) {
-        bad[e] = false;
-        const UV<T> r = correct_cell<T, MODE>(A, pm.a[e], pp_.a[e], pym.a[e], pyp.a[e], us.a[e], vs.a[e], bad[e]);
+        const UV<T> r = correct_cell<T, MODE>(A, pm.a[e], pp_.a[e], pym.a[e], pyp.a[e], us.a[e], vs.a[e], fl);
         un.a[e] = r.u;
         vn.a[e] = r.v;
     }
-    if (MODE != DIV_EXACT) {
+    if (MODE != DIV_EXACT && fl.raised(A.m.pow2_lo_m1)) {
 #pragma unroll
         for (int e = 0; e < V; ++e) {
-            if (bad[e]) {
-                const UV<T> r = correct_cell_exact<T>(A, pm.a[e], pp_.a[e], pym.a[e], pyp.a[e], us.a[e], vs.a[e]);
-                un.a[e] = r.u;
-                vn.a[e] = r.v;
-            }
+            const UV<T> r = correct_cell_exact<T>(A, pm.a[e], pp_.a[e], pym.a[e], pyp.a[e], us.a[e], vs.a[e]);
+            un.a[e] = r.u;
+            vn.a[e] = r.v;
         }
     }
 }

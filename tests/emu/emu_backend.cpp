@@ -232,17 +232,17 @@ extern "C" int fluidb200_poisson_solve_noalloc(const fluidb200_slab*, void*, con
 template <int MODE> static void cdiff_hook(const float* a, const float* b, float h, long long n, float* out) {
     const fb::Metric<float> m = fb::make_metric<float>(h, h);
     for (long long i = 0; i < n; ++i) {
-        bool bad = false;
-        out[i] = fb::Ar<float>::cdiff<MODE>(a[i], b[i], m.hx, m.hx2, m.inv_hx2, m.inv_hx2f, bad);
-        if (bad) out[i] = fb::Ar<float>::cdiff<fb::DIV_EXACT>(a[i], b[i], m.hx, m.hx2, m.inv_hx2, m.inv_hx2f, bad);
+        fb::Flags fl;
+        out[i] = fb::Ar<float>::cdiff<MODE>(a[i], b[i], m.hx, m.hx2, m.inv_hx2, m.inv_hx2f, fl);
+        if (fl.raised(m.pow2_lo_m1)) out[i] = fb::Ar<float>::cdiff<fb::DIV_EXACT>(a[i], b[i], m.hx, m.hx2, m.inv_hx2, m.inv_hx2f, fl);
     }
 }
 template <int MODE> static void lap_hook(const float* s, const float* c, float hx, float hy, long long n, float* out) {
     const fb::Metric<float> m = fb::make_metric<float>(hx, hy);
     for (long long i = 0; i < n; ++i) {
-        bool bad = false;
-        out[i] = fb::Ar<float>::lap_tail<MODE>(s[i], c[i], m.hx, m.hy, m.inv_hxhy, m.inv_hxhyf, bad);
-        if (bad) out[i] = fb::Ar<float>::lap_tail<fb::DIV_EXACT>(s[i], c[i], m.hx, m.hy, m.inv_hxhy, m.inv_hxhyf, bad);
+        fb::Flags fl;
+        out[i] = fb::Ar<float>::lap_tail<MODE>(s[i], c[i], m.hx, m.hy, m.inv_hxhy, m.inv_hxhyf, fl);
+        if (fl.raised(m.pow2_lo_m1)) out[i] = fb::Ar<float>::lap_tail<fb::DIV_EXACT>(s[i], c[i], m.hx, m.hy, m.inv_hxhy, m.inv_hxhyf, fl);
     }
 }
 extern "C" int emu_metric_mode_f32(float hx, float hy) { return fb::make_metric<float>(hx, hy).mode; }
