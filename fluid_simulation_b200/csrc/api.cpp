@@ -580,7 +580,11 @@ extern "C" int fluidb200_create(fluidb200_solver** out, int dtype, int X, int Y,
     // more on small chunks. FLUIDB200_KMAX / set_sweeps_per_launch override.
     {
         const long long cells = (long long)X * Y;
-        s->kmax = env_int("FLUIDB200_KMAX", cells >= 60000000LL ? 8 : cells >= 30000000LL ? 7 : cells >= 8000000LL ? 5 : 3);
+        int k = cells >= 60000000LL ? 8 : cells >= 30000000LL ? 7 : cells >= 8000000LL ? 5 : 3;
+        // fp64: half the FP rate and twice the bytes; depth 6 is DRAM bound already (16384^2: 1570
+        // Gcell-sweeps/s at depth 6, 1520 at 8; 8192^2: 1300 at 6, 1340 at 7)
+        if (dtype == FLUIDB200_F64) k = std::min(k, 6);
+        s->kmax = env_int("FLUIDB200_KMAX", k);
     }
     fluidb200_set_domain(s, domain_x, domain_y);
     if (fbk::be_stream_create(&s->stream) != 0) {

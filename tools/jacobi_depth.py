@@ -1,5 +1,5 @@
 #!/usr/bin/env python
-"""Microseconds per Jacobi launch for each blocking depth k (16384^2 fp32 cavity unless N is set).
+"""Microseconds per Jacobi launch for each blocking depth k (16384^2 fp32 cavity unless N / DTYPE=f64 are set).
 
     python tools/jacobi_depth.py [k ...]        # default 4 5 6 7 8
 
@@ -16,9 +16,10 @@ import torch
 from fluid_simulation_b200 import ParallelNavierStokes, _lib
 
 N = int(os.environ.get("N", 16384))
+DT = np.float64 if os.environ.get("DTYPE", "f32") == "f64" else np.float32
 ks = [int(a) for a in sys.argv[1:]] or [4, 5, 6, 7, 8]
 lib = _lib.load()
-s = ParallelNavierStokes(N, N, float(N - 1), float(N - 1), dtype=np.float32)
+s = ParallelNavierStokes(N, N, float(N - 1), float(N - 1), dtype=DT)
 s.num_poisson_iterations, s.num_iterations = 100, 1
 st = torch.cuda.current_stream()
 _lib.check(lib, lib.fluidb200_set_stream(s._h, st.cuda_stream))
