@@ -128,7 +128,7 @@ template <typename T, int K> int launch_jacobi_k(const fb::JacobiArgs<T>& a, boo
         fb::JacobiArgs<T> all = a;
         all.part = 0;
         const dim3 grid = grid_for(a.g.nstrips, nchunks);
-        if (K == 1 && mask) jacobi_kernel<T, V, 1, true><<<grid, kThreads, smem, st>>>(all);
+        if (mask) jacobi_kernel<T, V, K, true><<<grid, kThreads, smem, st>>>(all);
         else jacobi_kernel<T, V, K, false><<<grid, kThreads, smem, st>>>(all);
         return rc_of(cudaGetLastError());
     }

@@ -139,8 +139,8 @@ int fluidb200_predictor(const fluidb200_slab* g, const void* u, const void* v, v
  * Writes global rows [out_lo, out_hi) of p_out (all Y columns, edge rows included when the
  * range touches them). Needs p_in on rows [out_lo-sweeps, out_hi+sweeps) and rhs on rows
  * [out_lo-sweeps+1, out_hi+sweeps-1), both clipped to the box; the range must be present
- * locally. `mask` (may be NULL) enables interior pressure flags; with a mask only sweeps==1
- * is accepted. */
+ * locally. `mask` (may be NULL) enables interior pressure flags (SerialNavierStokes.cpp:154-160),
+ * applied at every one of the `sweeps` levels; masked launches always use the general kernel. */
 int fluidb200_poisson_sweeps(const fluidb200_slab* g, const void* p_in, void* p_out,
                              const void* rhs, const fluidb200_edges* p_edges,
                              const fluidb200_mask* mask, int sweeps, int out_lo, int out_hi,

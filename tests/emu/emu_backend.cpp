@@ -136,7 +136,7 @@ static void jac_k(const fb::JacobiArgs<T>& a, bool mask, int nchunks) {
         run_grid(nwarps_x, ny, [&](int wx, int by, int l) {
             int strip, chunk;
             if (!fb::jacobi_decode_task(g, wx / W, by, wx % W, W, &strip, &chunk)) return;
-            if (K == 1 && mask) fb::jacobi_task<T, V, 1, true>(g, strip, chunk, l, l, 32);
+            if (mask) fb::jacobi_task<T, V, K, true>(g, strip, chunk, l, l, 32);
             else fb::jacobi_task<T, V, K, false>(g, strip, chunk, l, l, 32);
         });
     };

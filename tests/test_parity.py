@@ -294,3 +294,26 @@ def test_split_launch_every_depth(Solver, kmax, unit):
     o.solve()
     H.compare_with(s, o, tag=f"split-depth/k{kmax}/unit{unit}")
     s.close()
+
+
+@pytest.mark.parametrize("depth", [1, 2, 3, 4, 6, 8])
+def test_interior_flags_inside_temporal_blocking(Solver, env, depth):
+    """General boundary conditions (interior obstacle flags for u, v and p, partly unset edges) with
+    the pressure flags applied at every level of a `depth`-sweep launch (SerialNavierStokes.cpp:
+    154-160 runs once per sweep). The solver caps masked launches at depth 2 unless told otherwise."""
+    from tests.golden.make_golden import general_bcs
+    env["FLUIDB200_MASK_KMAX"] = str(depth)
+    X, Y, S, K = 61, 300, 3, 2 * depth
+    o = general_bcs(X, Y, np.dtype("float32"))
+    o.time_step, o.num_iterations, o.num_poisson_iterations = 1e-4, S, K
+    s = Solver(X, Y, 1.0, 1.0, np.dtype("float32"))
+    for f, setter in (("u", s.setUBoundaryCondition), ("v", s.setVBoundaryCondition), ("p", s.setPBoundaryCondition)):
+        flag, val = getattr(o, f + "_set"), getattr(o, f + "_bc")
+        for x, y in np.argwhere(flag):
+            setter(int(x), int(y), float(val[x, y]))
+    s.time_step, s.num_iterations, s.num_poisson_iterations = 1e-4, S, K
+    s.set_sweeps_per_launch(8)
+    s.migrateSolve()
+    o.solve()
+    H.compare_with(s, o, tag=f"masked/depth{depth}")
+    s.close()
