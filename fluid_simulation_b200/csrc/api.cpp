@@ -51,9 +51,11 @@ template <typename T> int num_strips(int Y, int H) {
 
 // Warp tasks aimed for per launch (measured on B200 at 16384^2): the Jacobi pipeline pays K halo rows
 // per chunk end and is best around 9 x 2368 tasks up to depth 6 and 5 x 2368 at depth 7-8 (longer
-// chunks: fewer recomputed rows); the two one-pass kernels have a 1-2 row halo and keep improving
-// up to ~40 x 2368.
-constexpr int kJacobiTasks = 148 * 16 * 9, kJacobiTasksDeep = 148 * 16 * 5, kLightTasks = 148 * 16 * 40;
+// chunks: fewer recomputed rows); the two one-pass kernels have a 1-2 row halo: the corrector is best
+// around 40 x 2368 (0.89 ms), the predictor keeps improving down to 16-row chunks (10 x 2368: 1.76 ms,
+// 40 x: 1.14 ms, 64 x: 1.08 ms; its ring depth makes no difference).
+constexpr int kJacobiTasks = 148 * 16 * 9, kJacobiTasksDeep = 148 * 16 * 5, kLightTasks = 148 * 16 * 40,
+              kPredictorTasks = 148 * 16 * 64;
 
 // Split `n` output rows into chunks. More chunks = more warps in flight and a smaller tail, but
 // every chunk recomputes `halo` rows at each end. The chunk count is chosen so that the grid is
@@ -172,7 +174,7 @@ int predictor_t(const fluidb200_slab* g, const void* u, const void* v, void* us,
     a.hi = std::max(star_hi, rhs_hi);
     const int nstrips = num_strips<T>(g->Y, 4);
     int rpc, nchunks;
-    plan_chunks(a.hi - a.lo, 2, nstrips, 4, kLightTasks, &rpc, &nchunks);
+    plan_chunks(a.hi - a.lo, 2, nstrips, 4, env_int("FLUIDB200_LIGHT_TASKS", kPredictorTasks), &rpc, &nchunks);
     a.g = make_geom(g, nstrips, rpc);
     BE_CHECK(fbk::launch_predictor<T>(a, nchunks, stream), "predictor launch");
     return 0;
@@ -278,7 +280,7 @@ int corrector_t(const fluidb200_slab* g, const void* p, const void* us, const vo
     a.ev = to_dev_edges<T>(ev);
     const int nstrips = num_strips<T>(g->Y, 4);
     int rpc, nchunks;
-    plan_chunks(out_hi - out_lo, 1, nstrips, 4, kLightTasks, &rpc, &nchunks);
+    plan_chunks(out_hi - out_lo, 1, nstrips, 4, env_int("FLUIDB200_LIGHT_TASKS", kLightTasks), &rpc, &nchunks);
     a.g = make_geom(g, nstrips, rpc);
     BE_CHECK(fbk::launch_corrector<T>(a, um || vm, nchunks, stream), "corrector launch");
     return 0;

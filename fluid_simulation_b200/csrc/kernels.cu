@@ -139,12 +139,7 @@ template <typename T, int K> int launch_jacobi_k(const fb::JacobiArgs<T>& a, boo
     edge.part = 3;
     fast.part = 1;
     if (rc_of(cudaEventRecord(side->fork, st)) || rc_of(cudaStreamWaitEvent(side->stream, side->fork, 0))) return -1;
-#ifdef FLUIDB200_EXPERIMENT_SKIP_SIDE   // timing experiments only (wrong results): 1 = no edge, 2 = no general, 3 = neither
-    const int ngen = (FLUIDB200_EXPERIMENT_SKIP_SIDE & 2) ? 0 : fb::jacobi_part2_tasks(gen);
-    const int nedge = (FLUIDB200_EXPERIMENT_SKIP_SIDE & 1) ? 0 : fb::jacobi_part3_tasks(edge);
-#else
     const int ngen = fb::jacobi_part2_tasks(gen), nedge = fb::jacobi_part3_tasks(edge);
-#endif
     if (nedge > 0) {
         const dim3 egrid((unsigned)((nedge + fb::kWarpsPerCta - 1) / fb::kWarpsPerCta), 1, 1);
         jacobi_edge_kernel<T, V, K><<<egrid, kThreads, smem, side->stream>>>(edge);
@@ -244,7 +239,7 @@ template <typename T> int launch_predictor(const fb::PredictorArgs<T>& a, int nc
     const dim3 grid = grid_for(a.g.nstrips, nchunks);
     cudaStream_t st = (cudaStream_t)stream;
     // the arithmetic mode is a compile-time property of the kernel (see Metric::mode); fp64 has only mode 0
-    const size_t smem = (size_t)4 * 2 * 16 * kThreads;  // per-lane cp.async ring: 4 slots x {u, v} x 16 B
+    const size_t smem = (size_t)FLUIDB200_PRED_D * 2 * 16 * kThreads;  // per-lane cp.async ring: D slots x {u, v} x 16 B
     if (sizeof(T) == 4 && a.m.mode == 2) predictor_kernel<T, V, (sizeof(T) == 4 ? 2 : 0)><<<grid, kThreads, smem, st>>>(a);
     else if (sizeof(T) == 4 && a.m.mode == 1) predictor_kernel<T, V, (sizeof(T) == 4 ? 1 : 0)><<<grid, kThreads, smem, st>>>(a);
     else predictor_kernel<T, V, 0><<<grid, kThreads, smem, st>>>(a);

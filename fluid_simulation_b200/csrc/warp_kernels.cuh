@@ -882,6 +882,9 @@ FB_DEV Vec<T, V> rhs_row(const PredictorArgs<T>& A, const Vec<T, V>& us_m, const
 }
 
 
+#ifndef FLUIDB200_PRED_D
+#define FLUIDB200_PRED_D 4   // rows of u and v in flight per lane in the predictor's fast loop
+#endif
 // Pipeline: step r loads row r of u, v; level A produces u_next, v_next of row r-1, level B the
 // right-hand side of row r-2 (it needs u_next of rows r-3 and r-1). Interior strips away from the
 // box walls take the FAST path (2 steps per iteration, no range checks).
@@ -992,7 +995,7 @@ FB_DEV void predictor_task(const PredictorArgs<T>& A, int strip, int chunk, int 
         // rows of u and v are prefetched D steps ahead through the per-lane cp.async ring; inside the
         // loop the row to fetch is a 32-bit element offset from row r (clamped at the last loaded row)
         // and the three store pointers run along with the steps
-        constexpr int D = 4;
+        constexpr int D = FLUIDB200_PRED_D;
         static_assert(D % U == 0, "ring depth must be a multiple of the unroll factor");
         LaneRing<T, V, D> ring;
         ring.init(tid, nthreads);
