@@ -35,7 +35,7 @@ class Edges(C.Structure):
 
 class Mask(C.Structure):
     """struct fluidb200_mask"""
-    _fields_ = [("set", C.c_void_p), ("val", C.c_void_p)]
+    _fields_ = [("set", C.c_void_p), ("val", C.c_void_p), ("tiles", C.c_void_p)]
 
 
 class FluidB200Error(RuntimeError):

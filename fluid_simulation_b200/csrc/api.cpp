@@ -194,7 +194,8 @@ void split_jacobi(fb::JacobiArgs<T>* a, const fluidb200_slab* g, int K, int nchu
     a->nchunks = nchunks;
     a->sf_lo = a->sf_hi = a->cf_lo = a->cf_hi = 0;
     a->edge_lean = 0;
-    if (use_mask || env_int("FLUIDB200_NO_SPLIT", 0)) return;
+    a->gen_all = 0;
+    if ((use_mask && !a->mtiles) || env_int("FLUIDB200_NO_SPLIT", 0)) return;
     const int W = 32 * vec_width<T>(), S = W - 2 * halo_cols(K);
     const int nstrips = a->g.nstrips;
     int sf_lo = 1, sf_hi = 1;
@@ -221,6 +222,7 @@ void split_jacobi(fb::JacobiArgs<T>* a, const fluidb200_slab* g, int K, int nchu
     a->sf_lo = sf_lo; a->sf_hi = sf_hi; a->cf_lo = cf_lo; a->cf_hi = cf_hi;
     // the lean EDGE kernel knows constant and copy boundary cells; per-cell arrays stay with the general kernel
     a->edge_lean = a->e.mode[fb::BOTTOM] != fb::EDGE_ARRAY && a->e.mode[fb::TOP] != fb::EDGE_ARRAY;
+    a->gen_all = use_mask ? 1 : 0;  // masked: the general kernel is offered every task (see jacobi_general_task)
 }
 
 template <typename T>
@@ -232,6 +234,8 @@ int poisson_t(const fluidb200_slab* g, const void* p_in, void* p_out, const void
     const bool use_mask = mask && mask->set;
     a.mset = use_mask ? mask->set : nullptr;
     a.mval = use_mask ? (const T*)mask->val : nullptr;
+    a.mtiles = use_mask ? mask->tiles : nullptr;
+    a.mtiles_nc = (g->Y + fb::kMaskTileCols - 1) / fb::kMaskTileCols;
     a.hx = (T)g->hx; a.hy = (T)g->hy;
     a.out_lo = out_lo; a.out_hi = out_hi;
     a.e = to_dev_edges<T>(e);
@@ -247,7 +251,7 @@ int poisson_t(const fluidb200_slab* g, const void* p_in, void* p_out, const void
     a.head = out_lo == 0 ? 2 * sweeps + 2 : 0;
     a.tail = out_hi == g->X ? sweeps + 1 : 0;
     a.part = 0;
-    if (!use_mask && (a.head || a.tail) && n - a.head - a.tail >= 4 * sweeps + 8) {
+    if ((!use_mask || a.mtiles) && (a.head || a.tail) && n - a.head - a.tail >= 4 * sweeps + 8) {
         plan_chunks(n - a.head - a.tail, sweeps, nstrips, ctas_per_sm, tasks, &rpc, &nchunks);
         nchunks += (a.head > 0) + (a.tail > 0);
         a.g = make_geom(g, nstrips, rpc);
@@ -402,6 +406,7 @@ struct fluidb200_solver {
     void* edge_val[3][4] = {};
     uint8_t* edge_set[3][4] = {};
     fluidb200_mask mask[3] = {};     // interior flags (device), NULL when none
+    bool mask_sparse = false;        // pressure flags touch few tiles: masked launches keep the full blocking depth
     void* stream = nullptr;
     bool own_stream = false;
     int kmax = 4;
@@ -436,7 +441,8 @@ void free_bc(fluidb200_solver* s, int f) {
     }
     if (s->mask[f].set) fbk::be_free((void*)s->mask[f].set);
     if (s->mask[f].val) fbk::be_free((void*)s->mask[f].val);
-    s->mask[f].set = nullptr; s->mask[f].val = nullptr;
+    if (s->mask[f].tiles) fbk::be_free((void*)s->mask[f].tiles);
+    s->mask[f].set = nullptr; s->mask[f].val = nullptr; s->mask[f].tiles = nullptr;
 }
 
 // Turn dense host flag/value arrays of one field into the edge description (+ interior mask).
@@ -502,6 +508,26 @@ int upload_bc_t(fluidb200_solver* s, int f, const T* val, const uint8_t* set) {
         BE_CHECK(fbk::be_memcpy2d_async(ds, s->pitch, set, Y, Y, X, fbk::H2D, s->stream), "mask upload");
         BE_CHECK(fbk::be_memcpy2d_async(dv, s->pitch * sizeof(T), val, Y * sizeof(T), Y * sizeof(T), X, fbk::H2D,
                                         s->stream), "mask upload");
+        if (f == 2) {
+            // tile summary of the interior pressure flags: lets a masked Jacobi launch keep its lean kernels
+            // wherever there is no flag (see fluidb200_mask::tiles)
+            const int TR = FLUIDB200_MASK_TILE_ROWS, TC = FLUIDB200_MASK_TILE_COLS;
+            const int ntr = (X + TR - 1) / TR, ntc = (Y + TC - 1) / TC;
+            std::vector<uint8_t> tiles((size_t)ntr * ntc, 0);
+            size_t flagged = 0;
+            for (int x = 1; x < X - 1; ++x) {
+                const uint8_t* row = set + (size_t)x * Y;
+                uint8_t* trow = tiles.data() + (size_t)(x / TR) * ntc;
+                for (int y = 1; y < Y - 1; ++y)
+                    if (row[y]) trow[y / TC] = 1;
+            }
+            for (uint8_t t : tiles) flagged += t;
+            s->mask_sparse = flagged * 20 <= tiles.size();  // flags in at most 5 % of the tiles
+            void* dt = nullptr;
+            BE_CHECK(fbk::be_malloc(&dt, tiles.size()), "mask tiles alloc");
+            s->mask[f].tiles = (const uint8_t*)dt;
+            BE_CHECK(fbk::be_memcpy_async(dt, tiles.data(), tiles.size(), fbk::H2D, s->stream), "mask tiles upload");
+        }
         BE_CHECK(fbk::be_stream_sync(s->stream), "mask upload");
     }
     return 0;
@@ -517,17 +543,27 @@ int step_predictor(fluidb200_solver* s) {
     return rc;
 }
 
-// Deepest blocking used when interior pressure flags are present: every task then runs the general
-// path, which is instruction bound, so depth only saves DRAM passes it does not need (measured at
-// 8192^2, us per sweep: depth 1 255, depth 2 192, depth 4 203, depth 8 366).
-constexpr int kMaskedKmaxDefault = 2;
+// Blocking depth when interior pressure flags are present. Tasks with a flagged cell in their footprint
+// run the general path, which is instruction and latency bound (no row prefetch), so a deep pipeline
+// only makes those few tasks the critical path of the launch. Measured at 8192^2, us per sweep:
+//   no tile summary (every task general): depth 1 255, depth 2 192, depth 4 203, depth 8 366 -> 2;
+//   tile summary, one 64 x 64 obstacle  : depth 1 155, depth 2 79, depth 4 50, depth 6 53, depth 8 61 -> 4
+//   (the same grid without flags: 23 at depth 8).
+constexpr int kMaskedKmaxDefault = 2, kSparseMaskedKmax = 4;
 int masked_kmax() { return std::max(1, env_int("FLUIDB200_MASK_KMAX", kMaskedKmaxDefault)); }
+// flags in few tiles (and FLUIDB200_MASK_KMAX not set: tests and measurements force a depth with it)
+bool sparse_mask(const fluidb200_solver* s) { return s->mask_sparse && s->mask[2].tiles && getenv("FLUIDB200_MASK_KMAX") == nullptr; }
+int poisson_kmax(const fluidb200_solver* s) {
+    int k = s->kmax;
+    if (s->mask[2].set) k = std::min(k, sparse_mask(s) ? kSparseMaskedKmax : masked_kmax());
+    return std::max(1, std::min(k, FLUIDB200_MAX_SWEEPS_PER_LAUNCH));
+}
 
 int step_poisson(fluidb200_solver* s, int sweeps) {
     fluidb200_slab g;
     fill_slab(s, &g);
     const bool masked = s->mask[2].set != nullptr;
-    const int kmax = std::max(1, std::min(masked ? std::min(s->kmax, masked_kmax()) : s->kmax, FLUIDB200_MAX_SWEEPS_PER_LAUNCH));
+    const int kmax = poisson_kmax(s);
     // n = ceil(sweeps / kmax) launches of nearly equal depth (100 sweeps at depth 7: 10 x 7 + 5 x 6)
     // rather than full launches and a shallow remainder: a launch costs about the same at any depth.
     const int nlaunch = (sweeps + kmax - 1) / kmax;
@@ -565,7 +601,7 @@ int one_step(fluidb200_solver* s) {
 }
 
 int launches_per_step(const fluidb200_solver* s) {
-    const int kmax = std::max(1, std::min(s->mask[2].set ? std::min(s->kmax, masked_kmax()) : s->kmax, FLUIDB200_MAX_SWEEPS_PER_LAUNCH));
+    const int kmax = poisson_kmax(s);
     return 2 + (s->K + kmax - 1) / kmax;
 }
 

@@ -32,7 +32,7 @@ template <typename T, int V, int K, bool MASK>
 __global__ void __launch_bounds__(kThreads, FLUIDB200_JACOBI_MIN_BLOCKS(K)) jacobi_kernel(const __grid_constant__ fb::JacobiArgs<T> A) {
     int strip, chunk;  // whole warps only; the tasks use no block barrier
     if (!fb::jacobi_decode_task(A, (int)blockIdx.x, (int)blockIdx.y, (int)(threadIdx.x >> 5), fb::kWarpsPerCta, &strip, &chunk)) return;
-    fb::jacobi_task<T, V, K, MASK>(A, strip, chunk, threadIdx.x & 31, threadIdx.x, kThreads);
+    fb::jacobi_general_task<T, V, K, MASK>(A, strip, chunk, threadIdx.x & 31, threadIdx.x, kThreads);
 }
 
 // The lean twin (see jacobi_fast_task): without the general path it needs fewer registers, so it
@@ -123,7 +123,7 @@ template <typename T, int K> int launch_jacobi_k(const fb::JacobiArgs<T>& a, boo
     constexpr int V = fb::VecWidth<T>::V;
     // dynamic shared memory: the per-lane cp.async prefetch ring (D slots x 2 arrays x 16 B per thread)
     const size_t smem = (size_t)fb::JacobiRing<K>::D * 2 * 16 * kThreads;
-    SideStream* side = (a.part != 0 && !mask) ? side_stream() : nullptr;
+    SideStream* side = a.part != 0 ? side_stream() : nullptr;
     if (!side) {  // one kernel does every task
         fb::JacobiArgs<T> all = a;
         all.part = 0;
@@ -147,7 +147,8 @@ template <typename T, int K> int launch_jacobi_k(const fb::JacobiArgs<T>& a, boo
     }
     if (ngen > 0) {
         const dim3 ggrid((unsigned)((ngen + fb::kWarpsPerCta - 1) / fb::kWarpsPerCta), 1, 1);
-        jacobi_kernel<T, V, K, false><<<ggrid, kThreads, smem, side->stream>>>(gen);
+        if (mask) jacobi_kernel<T, V, K, true><<<ggrid, kThreads, smem, side->stream>>>(gen);
+        else jacobi_kernel<T, V, K, false><<<ggrid, kThreads, smem, side->stream>>>(gen);
         if (rc_of(cudaGetLastError())) return -1;
     }
     if (rc_of(cudaEventRecord(side->join, side->stream))) return -1;

@@ -82,6 +82,11 @@ template <typename T> struct JacobiArgs {
     const T* rhs;
     const uint8_t* mset;  // interior pressure flags (MASK build only)
     const T* mval;
+    // Optional summary of mset: one byte per tile of kMaskTileRows x kMaskTileCols cells (rows counted
+    // from g.row0), non-zero when the tile holds a flagged interior cell; mtiles_nc tiles per tile row.
+    // With it a masked launch can be split: tasks whose footprint holds no flag run the lean kernels.
+    const uint8_t* mtiles;
+    int mtiles_nc;
     Geom g;
     T hx, hy;
     int out_lo, out_hi;   // global rows to write
@@ -100,7 +105,12 @@ template <typename T> struct JacobiArgs {
     // 1: the strips holding a y-edge column have their own lean kernel (part 3); 0 (a y edge with
     // per-cell boundary arrays): they are general tasks, appended to the part 2 list
     int edge_lean;
+    // 1 (masked split launch): the part 2 list is EVERY task; a task skips itself unless it is a wall
+    // chunk, a strip no lean kernel takes, or flagged by mtiles -- and the lean kernels skip flagged tasks
+    int gen_all;
 };
+
+constexpr int kMaskTileRows = 16, kMaskTileCols = 64;
 
 #ifdef __CUDACC__
 #define FB_HD __host__ __device__
@@ -147,6 +157,11 @@ inline FB_HD bool jacobi_decode_task(const JacobiArgs<T>& a, int bx, int by, int
         *chunk = a.cf_lo + id / E;
         return true;
     }
+    if (a.gen_all) {
+        *strip = id % a.g.nstrips;
+        *chunk = id / a.g.nstrips;
+        return *chunk < a.nchunks;
+    }
     const int E = a.sf_lo + (a.g.nstrips - a.sf_hi), nwall = a.nchunks - (a.cf_hi - a.cf_lo);
     const int ci = id / a.g.nstrips;
     if (ci < nwall) {
@@ -165,6 +180,7 @@ template <typename T> inline int jacobi_part3_tasks(const JacobiArgs<T>& a) {
     return a.edge_lean ? (a.sf_lo + (a.g.nstrips - a.sf_hi)) * (a.cf_hi - a.cf_lo) : 0;
 }
 template <typename T> inline int jacobi_part2_tasks(const JacobiArgs<T>& a) {
+    if (a.gen_all) return a.g.nstrips * a.nchunks;
     const int E = a.sf_lo + (a.g.nstrips - a.sf_hi);
     return a.g.nstrips * (a.nchunks - (a.cf_hi - a.cf_lo)) + (a.edge_lean ? 0 : E * (a.cf_hi - a.cf_lo));
 }

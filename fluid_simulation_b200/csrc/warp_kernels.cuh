@@ -767,10 +767,31 @@ FB_DEV void jacobi_fast_body(const JacobiArgs<T>& A, int strip, int chunk, int l
     ring.template wait<0>();  // nothing may still be landing in shared memory when the CTA retires
 }
 
+// Masked split launch: does the footprint of task (strip, chunk) -- every row and column its pipeline
+// loads -- hold a flagged interior cell? Tile granularity (JacobiArgs::mtiles); all lanes read the
+// same few bytes.
+template <typename T, int V, int K>
+FB_DEV bool jacobi_task_flagged(const JacobiArgs<T>& A, int strip, int chunk) {
+    constexpr int H = (K + 3) & ~3, W = 32 * V, S = W - 2 * H;
+    const Geom& g = A.g;
+    int c0, c1;
+    jacobi_chunk_rows(A, chunk, &c0, &c1);
+    if (c0 >= c1) return false;
+    const int r0 = max(c0 - K, g.row0), r1 = min(c1 + K, g.row0 + g.rows);
+    const int y0 = strip * S, y1 = min(strip * S + W, g.Y);
+    if (r0 >= r1 || y0 >= y1) return false;
+    const int tr1 = (r1 - 1 - g.row0) / kMaskTileRows, tc0 = y0 / kMaskTileCols, tc1 = (y1 - 1) / kMaskTileCols;
+    unsigned any = 0;
+    for (int tr = (r0 - g.row0) / kMaskTileRows; tr <= tr1; ++tr)
+        for (int tc = tc0; tc <= tc1; ++tc) any |= A.mtiles[(long long)tr * A.mtiles_nc + tc];
+    return any != 0;
+}
+
 // The scaling of the right-hand side by hx*hy (two exact multiplications by 1 on a unit-spaced grid)
 // is decided once per task, not once per row.
 template <typename T, int V, int K>
 FB_DEV void jacobi_fast_task(const JacobiArgs<T>& A, int strip, int chunk, int lane, int tid, int nthreads) {
+    if (A.mtiles && jacobi_task_flagged<T, V, K>(A, strip, chunk)) return;  // the general kernel runs it
     if (A.hx == T(1) && A.hy == T(1)) jacobi_fast_body<T, V, K, false, false>(A, strip, chunk, lane, tid, nthreads);
     else jacobi_fast_body<T, V, K, true, false>(A, strip, chunk, lane, tid, nthreads);
 }
@@ -779,8 +800,21 @@ FB_DEV void jacobi_fast_task(const JacobiArgs<T>& A, int strip, int chunk, int l
 // with no x wall within reach of the pipeline. The lean pipeline with the y-edge cells added.
 template <typename T, int V, int K>
 FB_DEV void jacobi_edge_task(const JacobiArgs<T>& A, int strip, int chunk, int lane, int tid, int nthreads) {
+    if (A.mtiles && jacobi_task_flagged<T, V, K>(A, strip, chunk)) return;  // the general kernel runs it
     if (A.hx == T(1) && A.hy == T(1)) jacobi_fast_body<T, V, K, false, true>(A, strip, chunk, lane, tid, nthreads);
     else jacobi_fast_body<T, V, K, true, true>(A, strip, chunk, lane, tid, nthreads);
+}
+
+// One task of the general kernel. In a masked split launch it is offered every task and keeps the
+// ones no lean kernel runs: wall chunks, strips without a lean kernel, tasks with a flagged cell.
+template <typename T, int V, int K, bool MASK>
+FB_DEV void jacobi_general_task(const JacobiArgs<T>& A, int strip, int chunk, int lane, int tid, int nthreads) {
+    if (MASK && A.part == 2 && A.gen_all) {
+        const bool lean_chunk = chunk >= A.cf_lo && chunk < A.cf_hi;
+        const bool lean_strip = (strip >= A.sf_lo && strip < A.sf_hi) || A.edge_lean;
+        if (lean_chunk && lean_strip && !jacobi_task_flagged<T, V, K>(A, strip, chunk)) return;
+    }
+    jacobi_task<T, V, K, MASK>(A, strip, chunk, lane, tid, nthreads);
 }
 
 // =========================================================================================

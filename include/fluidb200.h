@@ -101,7 +101,16 @@ typedef struct fluidb200_edges {
 typedef struct fluidb200_mask {
     const uint8_t* set;       /* device uint8[rows*pitch] or NULL                         */
     const void* val;          /* device T[rows*pitch]     or NULL                         */
+    /* Optional (pressure mask only, may be NULL): a summary of `set`, one byte per tile of
+     * FLUIDB200_MASK_TILE_ROWS x FLUIDB200_MASK_TILE_COLS cells (local rows, columns from 0),
+     * tile (tr, tc) at tiles[tr * ceil(Y / TILE_COLS) + tc], non-zero when the tile holds a
+     * flagged INTERIOR cell (a zero byte promises there is none). With it fluidb200_poisson_sweeps
+     * runs the flag-free parts of the grid through its lean kernels; without it every task of a
+     * masked launch takes the general kernel. The solver handle builds it on upload. */
+    const uint8_t* tiles;
 } fluidb200_mask;
+#define FLUIDB200_MASK_TILE_ROWS 16
+#define FLUIDB200_MASK_TILE_COLS 64
 
 /* Geometry of the rows held in one device array set (a whole grid, or one x-slab of it).
  * Local row 0 is global row `row0`; the arrays hold `rows` rows. */

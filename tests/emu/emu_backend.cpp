@@ -136,12 +136,12 @@ static void jac_k(const fb::JacobiArgs<T>& a, bool mask, int nchunks) {
         run_grid(nwarps_x, ny, [&](int wx, int by, int l) {
             int strip, chunk;
             if (!fb::jacobi_decode_task(g, wx / W, by, wx % W, W, &strip, &chunk)) return;
-            if (mask) fb::jacobi_task<T, V, K, true>(g, strip, chunk, l, l, 32);
-            else fb::jacobi_task<T, V, K, false>(g, strip, chunk, l, l, 32);
+            if (mask) fb::jacobi_general_task<T, V, K, true>(g, strip, chunk, l, l, 32);
+            else fb::jacobi_general_task<T, V, K, false>(g, strip, chunk, l, l, 32);
         });
     };
     auto round_up = [](int n) { return (n + W - 1) / W * W; };
-    if (a.part == 0 || mask) {
+    if (a.part == 0) {
         fb::JacobiArgs<T> all = a;
         all.part = 0;
         general(all, round_up(a.g.nstrips), nchunks);

@@ -317,3 +317,29 @@ def test_interior_flags_inside_temporal_blocking(Solver, env, depth):
     o.solve()
     H.compare_with(s, o, tag=f"masked/depth{depth}")
     s.close()
+
+
+@pytest.mark.parametrize("depth", [2, 5, 8])
+def test_cavity_with_obstacles_keeps_lean_kernels(Solver, env, depth):
+    """A lid-driven cavity (constant / copy edges) with two small obstacles: the masked Jacobi launch
+    is split, tasks whose footprint holds no flagged cell run the lean FAST / EDGE kernels, the others
+    (one in the middle strip, one in the strip holding column 0) the general kernel."""
+    env["FLUIDB200_MASK_KMAX"] = str(depth)
+    X, Y, S, K = 96, 300, 2, 2 * depth
+    def setup(s):
+        s.set_cavity(1.0)
+        for x in range(40, 44):
+            for y in range(150, 155):
+                s.setUBoundaryCondition(x, y, 0.0); s.setVBoundaryCondition(x, y, 0.0)
+                if (x + y) % 2 == 0:
+                    s.setPBoundaryCondition(x, y, 0.0625)
+        s.setPBoundaryCondition(70, 5, -0.5)
+        s.time_step, s.num_iterations, s.num_poisson_iterations = 1e-5, S, K
+        return s
+    o = setup(Oracle(X, Y))
+    s = setup(Solver(X, Y))
+    s.set_sweeps_per_launch(8)
+    s.migrateSolve()
+    o.solve()
+    H.compare_with(s, o, tag=f"obstacles/depth{depth}")
+    s.close()

@@ -34,7 +34,7 @@ _lib.check(lib, lib.fluidb200_step_predictor(s._h))
 s.set_sweeps_per_launch(8)
 out = {}
 for k in ks:
-    os.environ["FLUIDB200_MASK_KMAX"] = str(k)
+    os.environ["FLUIDB200_MASK_KMAX"] = str(k)   # (also switches the sparse-mask depth rule off)
     _lib.check(lib, lib.fluidb200_step_poisson(s._h, 2 * k))
     torch.cuda.synchronize()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
