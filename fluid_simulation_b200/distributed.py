@@ -27,6 +27,7 @@ iteration count is fixed. On CPU the "device" library is tests/emu's host build 
 from __future__ import annotations
 
 import ctypes as C
+import os
 
 import numpy as np
 
@@ -80,9 +81,12 @@ class SlabSolver:
         if self.on_gpu:
             self.main = torch.cuda.current_stream(self.device)
             self.comm = torch.cuda.Stream(self.device)
-            self.edge = torch.cuda.Stream(self.device, priority=-1)   # edge strips jump the queue
+            self.edge = torch.cuda.Stream(self.device, priority=-1)   # edge strips jump the queue,
+            self.edge2 = torch.cuda.Stream(self.device, priority=-1)  # one stream per side so the two run side by side
+            if os.environ.get("FLUIDB200_ONE_EDGE_STREAM"):          # (measurement knob)
+                self.edge2 = self.edge
         else:
-            self.main = self.comm = self.edge = None
+            self.main = self.comm = self.edge = self.edge2 = None
         self._set_edges(1.0)
 
     # ------------------------------------------------------------------------------------------
@@ -193,16 +197,19 @@ class SlabSolver:
             hi_strip = (x1 - d, x1) if self.rank < self.world - 1 else None
             start = torch.cuda.Event()
             start.record(self.main)
-            self.edge.wait_event(start)
-            for strip in (lo_strip, hi_strip):
+            ready = []
+            for strip, stream in ((lo_strip, self.edge), (hi_strip, self.edge2)):
                 if strip:
-                    self._sweeps(k, *strip, stream=self.edge)
-            ready = torch.cuda.Event()
-            ready.record(self.edge)
+                    stream.wait_event(start)
+                    self._sweeps(k, *strip, stream=stream)
+                    ev = torch.cuda.Event()
+                    ev.record(stream)
+                    ready.append(ev)
             # 2. the interior of the owned range, concurrently, on the main stream
             self._sweeps(k, lo_strip[1] if lo_strip else x0, hi_strip[0] if hi_strip else x1)
             # 3. ship the strips on the communication stream while the interior runs
-            self.comm.wait_event(ready)
+            for ev in ready:
+                self.comm.wait_event(ev)
             with torch.cuda.stream(self.comm):
                 works = self._post_exchange(["p_next"], d)
                 self._wait(works)
@@ -274,10 +281,20 @@ def bench_distributed(args, grid, sweeps, kmax, prm, metric, unit):
     world = int(os.environ.get("WORLD_SIZE", 1))
     local = int(os.environ.get("LOCAL_RANK", rank))
     torch.cuda.set_device(local)
-    dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    # NCCL's own stream at high priority: the send/recv kernels of a halo exchange are a handful of CTAs that
+    # would otherwise queue behind the interior sweep's thousands
+    opts = None
+    if not os.environ.get("FLUIDB200_NCCL_LOWPRIO"):                 # (measurement knob)
+        try:
+            opts = dist.ProcessGroupNCCL.Options()
+            opts.is_high_priority_stream = True
+        except Exception:
+            opts = None
+    dist.init_process_group("nccl", device_id=torch.device("cuda", local), pg_options=opts)
     strong = os.environ.get("FLUIDB200_SCALING", "weak") == "strong"
     if strong:
         X = Y = int(os.environ.get("FLUIDB200_STRONG_GRID", 32768))
+        X = int(os.environ.get("FLUIDB200_STRONG_ROWS", X))   # (a shallower box, to study small slabs on few GPUs)
     else:
         X, Y = grid * world, grid
     s = SlabSolver(X, Y, float(X - 1), float(Y - 1), np.float32, rank=rank, world=world,
@@ -294,8 +311,10 @@ def bench_distributed(args, grid, sweeps, kmax, prm, metric, unit):
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     l0, hb0 = s.launches, s.halo_bytes
     e0.record(s.main)
+    t_issue = time.perf_counter()
     for _ in range(args.steps):
         s.step()
+    t_issue = time.perf_counter() - t_issue   # host time to ISSUE the steps (nothing waits for the GPU in there)
     e1.record(s.main)
     torch.cuda.synchronize()
     dist.barrier()
@@ -342,6 +361,7 @@ def bench_distributed(args, grid, sweeps, kmax, prm, metric, unit):
         "scaling": "strong" if strong else "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": {"workload": f"cavity {X}x{Y} fp32 ({s.x1 - s.x0} rows per GPU, x-slabs), {sweeps} Poisson sweeps/step",
                    "dt": prm["dt"], "nu": prm["nu"], "rho": prm["rho"], "hx": 1.0, "hy": 1.0, "sweeps_per_launch": kmax,
+                   "host_issue_ms_per_step": t_issue / args.steps * 1e3,
                    "parallelism": f"x-slabs x{world}, halo depth {kmax + 1}, NCCL send/recv overlapped with interior sweeps",
                    "halo_bytes_per_rank_per_step": halo_per_step,
                    "l2": f"fields are {(s.x1 - s.x0) * Y * 4 / 1e9:.2f} GB per GPU, >> 126 MB L2, no flush needed"},
