@@ -515,14 +515,6 @@ FB_DEV void jacobi_task(const JacobiArgs<T>& A, int strip, int chunk, int lane, 
         bw[t] = vzero<T, V>();
     }
 
-    auto load_p = [&](int r) -> VT {
-        if (r >= r_begin && r < load_hi) return ld_ro<T, V>(pin + (long long)r * g.pitch);
-        return vzero<T, V>();
-    };
-    auto load_b = [&](int r) -> VT {  // rhs of row r (interior rows only)
-        if (r >= r_begin && r < load_hi && r >= 1 && r <= X - 2) return ld_ro<T, V>(rin + (long long)r * g.pitch);
-        return vzero<T, V>();
-    };
     // (rhs * hx) * hy, SerialNavierStokes.cpp:144 -- once per row, reused by all K levels; with unit
     // spacing both multiplications are by 1 and exact, so they are skipped (warp-uniform branch)
     const bool scale_b = !(A.hx == T(1) && A.hy == T(1));
@@ -536,32 +528,52 @@ FB_DEV void jacobi_task(const JacobiArgs<T>& A, int strip, int chunk, int lane, 
         bw[0] = bnew;
     };
 
+    // Rows reach the pipeline through the per-lane cp.async ring, D steps ahead, on BOTH paths: one
+    // commit group per step r = {row r of p, row r-1 of rhs}, in slot (r - r_begin) % D. Row indices
+    // are clamped to rows that exist; a row the reference would not read (beyond the loaded range,
+    // rhs of a wall row) is replaced by zeros when it is taken out of the ring.
+    constexpr int U = (K + 1) & ~1;
+    constexpr int D = JacobiRing<K>::D;
+    static_assert(D % U == 0, "ring depth must be a multiple of the unroll factor");
+    const int pmax = load_hi - 1, bmax = min(load_hi - 1, X - 2);
+    LaneRing<T, V, D> ring;
+    ring.init(tid, nthreads);
+    auto fetch_step = [&](int slot, int rr) {
+        ring.fetch(slot, 0, pin + (long long)min(rr, pmax) * g.pitch);
+        ring.fetch(slot, 1, rin + (long long)max(min(rr - 1, bmax), r_begin) * g.pitch);
+        ring.commit();
+    };
+#pragma unroll
+    for (int j = 0; j < D; ++j) fetch_step(j, r_begin + j);
+
     // steps r in [fast_lo, fast_hi]: every level's row r-t lies in [2, X-3]. Strips that hold a
     // y-edge column and masked sweeps always take the general path. The fast loop is unrolled U
     // steps deep (U even and >= K) so that the row windows rotate by register renaming instead of
-    // moves, and it keeps U rows of p and rhs in flight per lane (U KB per warp) to cover HBM
-    // latency at the low occupancy this register-resident pipeline runs at.
-    constexpr int U = (K + 1) & ~1;
-    const int fast_lo = max(r_begin, K + 2);
+    // moves; it starts on a step whose rows sit in slot 0 so that its slot numbers are constants.
+    int fast_lo = max(r_begin, K + 2);
+    fast_lo += (D - (fast_lo - r_begin) % D) % D;
     int nfast = min(r_end, X - 2) - fast_lo + 1;
     if (MASK || y_edges || nfast < 0) nfast = 0;
     if ((long long)(load_hi - r_begin + 1) * g.pitch >= (1LL << 31)) nfast = 0;  // 32-bit offsets in the fast loop
     nfast -= nfast % U;
     const int fast_hi = fast_lo + nfast - 1;
 
-    VT nxt_p = load_p(r_begin);
-    VT nxt_b = load_b(r_begin - 1);
     int r = r_begin;
 #pragma unroll 1
     for (int phase = 0; phase < 2; ++phase) {
         // ---------------- GENERAL path: [r, fast_lo) first, then (fast_hi, r_end] ----------------
         const int gen_hi = (phase == 0 && nfast > 0) ? fast_lo - 1 : r_end;
+        int gslot = (r - r_begin) % D;
 #pragma unroll 1
         for (; r <= gen_hi; ++r) {
-            VT cur = nxt_p;
-            push_b(nxt_b);
-            nxt_p = load_p(r + 1);
-            nxt_b = load_b(r);
+            ring.template wait<D - 1>();          // the oldest group = this step's rows has landed
+            VT cur = ring.read(gslot, 0);
+            VT bnew = ring.read(gslot, 1);
+            fetch_step(gslot, r + D);
+            gslot = (gslot + 1 == D) ? 0 : gslot + 1;
+            if (r >= load_hi) cur = vzero<T, V>();
+            if (!(r - 1 >= r_begin && r - 1 < load_hi && r - 1 >= 1 && r - 1 <= X - 2)) bnew = vzero<T, V>();
+            push_b(bnew);
 #pragma unroll
             for (int t = 1; t <= K; ++t) {
                 const int rr = r - t;  // row this level produces now
@@ -607,14 +619,6 @@ FB_DEV void jacobi_task(const JacobiArgs<T>& A, int strip, int chunk, int lane, 
         }
         if (phase == 1 || nfast == 0) break;
         // ---------------- FAST path: [fast_lo, fast_hi], U steps per iteration ----------------
-        // Rows are prefetched D steps ahead through the per-lane cp.async ring; one commit group per
-        // step = {p row of that step, rhs row of the step before}. Row indices are clamped into the
-        // loaded range: the groups issued for steps beyond fast_hi are never consumed by this loop.
-        constexpr int D = JacobiRing<K>::D;
-        static_assert(D % U == 0, "ring depth must be a multiple of the unroll factor");
-        const int pmax = load_hi - 1, bmax = min(load_hi - 1, X - 2);
-        LaneRing<T, V, D> ring;
-        ring.init(tid, nthreads);
         // Addresses inside the loop are 32-bit element offsets from row r_begin of this chunk (the
         // host keeps a chunk below 2^31 elements), advanced by one pitch per step and clamped.
         const T* pbase = pin + (long long)r_begin * g.pitch;
@@ -623,13 +627,6 @@ FB_DEV void jacobi_task(const JacobiArgs<T>& A, int strip, int chunk, int lane, 
         const unsigned pitch32 = (unsigned)g.pitch;
         const unsigned pmax_off = (unsigned)(pmax - r_begin) * pitch32;
         const unsigned bmax_off = (unsigned)(bmax - r_begin) * pitch32;
-#pragma unroll
-        for (int j = 0; j < D; ++j) {
-            ring.fetch(j, 0, pin + (long long)min(r + j, pmax) * g.pitch);
-            ring.fetch(j, 1, rin + (long long)max(min(r + j - 1, bmax), r_begin) * g.pitch);
-            ring.commit();
-        }
-        (void)nxt_p; (void)nxt_b;  // the ring re-reads rows r and r-1; the register copies are dropped
         unsigned poff = (unsigned)(min(r + D, pmax) - r_begin) * pitch32;          // next p row to fetch
         unsigned boff = (unsigned)(min(r + D - 1, bmax) - r_begin) * pitch32;      // next rhs row to fetch
         int soff = (r - K - r_begin) * (int)pitch32;                               // row stored by this step
@@ -640,7 +637,7 @@ FB_DEV void jacobi_task(const JacobiArgs<T>& A, int strip, int chunk, int lane, 
 #pragma unroll
             for (int u = 0; u < U; ++u) {
                 const int slot = (D == U) ? u : sbase + u;
-                ring.template wait<D - 1>();          // the oldest group = this step's rows has landed
+                ring.template wait<D - 1>();
                 VT cur = ring.read(slot, 0);
                 push_b(ring.read(slot, 1));
                 ring.fetch(slot, 0, pbase + poff);
@@ -660,14 +657,9 @@ FB_DEV void jacobi_task(const JacobiArgs<T>& A, int strip, int chunk, int lane, 
             }
             if (D != U) sbase = (sbase + U) % D;
         }
-        // hand over to the general path: rows r (p) and r-1 (rhs) are the oldest group in the ring
-        ring.template wait<0>();
-        {
-            const int slot = (D == U) ? 0 : sbase;
-            nxt_p = (r < load_hi) ? ring.read(slot, 0) : vzero<T, V>();
-            nxt_b = (r - 1 >= 1 && r - 1 <= X - 2 && r - 1 < load_hi) ? ring.read(slot, 1) : vzero<T, V>();
-        }
+        // (fast_hi + 1 - r_begin is a multiple of U, so the general path resumes in the slot the loop left)
     }
+    ring.template wait<0>();  // nothing may still be landing in shared memory when the CTA retires
 }
 
 // The FAST-ONLY twin of jacobi_task: same pipeline, same arithmetic, but compiled without any of
