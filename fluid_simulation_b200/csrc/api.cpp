@@ -412,6 +412,7 @@ struct fluidb200_solver {
     int kmax = 4;
     bool use_graph = false;
     void* graph[2] = {nullptr, nullptr};  // one timestep, for each ping-pong parity
+    int64_t graph_kernels[2] = {0, 0};    // kernels recorded in each
     double graph_key[6] = {};
     void* graph_home_p = nullptr;     // where p lived when graph[0] was captured
     int64_t launches = 0;
@@ -536,10 +537,11 @@ int upload_bc_t(fluidb200_solver* s, int f, const T* val, const uint8_t* set) {
 int step_predictor(fluidb200_solver* s) {
     fluidb200_slab g;
     fill_slab(s, &g);
+    const long long k0 = fbk::be_kernel_count();
     int rc = fluidb200_predictor(&g, s->f[FLUIDB200_FIELD_U], s->f[FLUIDB200_FIELD_V], s->f[FLUIDB200_FIELD_U_NEXT],
                                  s->f[FLUIDB200_FIELD_V_NEXT], s->f[FLUIDB200_FIELD_RHS], s->dt, s->nu, s->rho, 0,
                                  s->X, 0, s->X, s->stream);
-    if (rc == 0) s->launches++;
+    s->launches += fbk::be_kernel_count() - k0;
     return rc;
 }
 
@@ -568,6 +570,11 @@ int step_poisson(fluidb200_solver* s, int sweeps) {
     // rather than full launches and a shallow remainder: a launch costs about the same at any depth.
     const int nlaunch = (sweeps + kmax - 1) / kmax;
     int left = sweeps;
+    const long long k0 = fbk::be_kernel_count();
+    struct Count {   // kernels of this call, however it returns
+        fluidb200_solver* s; long long k0;
+        ~Count() { s->launches += fbk::be_kernel_count() - k0; }
+    } count{s, k0};
     for (int i = 0; i < nlaunch; ++i) {
         const int k = (left + (nlaunch - i) - 1) / (nlaunch - i);
         int rc = fluidb200_poisson_sweeps(&g, s->f[FLUIDB200_FIELD_P], s->f[FLUIDB200_FIELD_P_NEXT],
@@ -576,7 +583,6 @@ int step_poisson(fluidb200_solver* s, int sweeps) {
         if (rc) return rc;
         std::swap(s->f[FLUIDB200_FIELD_P], s->f[FLUIDB200_FIELD_P_NEXT]);  // ping-pong instead of p = p_next
         s->p_next_is_p = true;
-        s->launches++;
         left -= k;
     }
     return 0;
@@ -585,11 +591,12 @@ int step_poisson(fluidb200_solver* s, int sweeps) {
 int step_corrector(fluidb200_solver* s) {
     fluidb200_slab g;
     fill_slab(s, &g);
+    const long long k0 = fbk::be_kernel_count();
     int rc = fluidb200_corrector(&g, s->f[FLUIDB200_FIELD_P], s->f[FLUIDB200_FIELD_U_NEXT], s->f[FLUIDB200_FIELD_V_NEXT],
                                  s->f[FLUIDB200_FIELD_U], s->f[FLUIDB200_FIELD_V], &s->edges[0], &s->edges[1],
                                  s->mask[0].set ? &s->mask[0] : nullptr, s->mask[1].set ? &s->mask[1] : nullptr, s->dt,
                                  s->rho, 0, s->X, s->stream);
-    if (rc == 0) s->launches++;
+    s->launches += fbk::be_kernel_count() - k0;
     return rc;
 }
 
@@ -628,6 +635,11 @@ extern "C" int fluidb200_create(fluidb200_solver** out, int dtype, int X, int Y,
         // Gcell-sweeps/s at depth 6, 1520 at 8; 8192^2: 1300 at 6, 1340 at 7)
         if (dtype == FLUIDB200_F64) k = std::min(k, 6);
         s->kmax = env_int("FLUIDB200_KMAX", k);
+        // Small grids are launch bound (a timestep is ~20 launches of ~10 us): solve() replays each
+        // timestep as a CUDA graph there (41^2: 231 -> 190 ms per 1000 steps, 1000^2: 287 -> 242 ms).
+        // fluidb200_set_use_graph / FLUIDB200_GRAPH override; a stream that cannot be captured falls
+        // back to plain launches.
+        s->use_graph = env_int("FLUIDB200_GRAPH", cells <= 4000000LL ? 1 : 0) != 0;
     }
     fluidb200_set_domain(s, domain_x, domain_y);
     if (fbk::be_stream_create(&s->stream) != 0) {
@@ -773,6 +785,7 @@ extern "C" int fluidb200_solve(fluidb200_solver* s) {
             const int rc = one_step(s);  // recorded, not executed
             void* exec = nullptr;
             const int rc2 = fbk::be_graph_end(s->stream, &exec);
+            s->graph_kernels[parity] = s->launches - before;
             s->launches = before;
             if (odd) std::swap(s->f[FLUIDB200_FIELD_P], s->f[FLUIDB200_FIELD_P_NEXT]);  // undo recorded swaps
             if (rc) return rc;
@@ -780,7 +793,7 @@ extern "C" int fluidb200_solve(fluidb200_solver* s) {
             s->graph[parity] = exec;
         }
         BE_CHECK(fbk::be_graph_launch(s->graph[parity], s->stream), "graph launch");
-        s->launches += launches_per_step(s);
+        s->launches += s->graph_kernels[parity];
         if (s->K > 0) s->p_next_is_p = true;
         if (odd) std::swap(s->f[FLUIDB200_FIELD_P], s->f[FLUIDB200_FIELD_P_NEXT]);
     }

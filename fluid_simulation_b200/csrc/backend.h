@@ -25,6 +25,9 @@ int be_stream_create(void** stream);
 int be_stream_destroy(void* stream);
 int be_stream_sync(void* stream);
 const char* be_last_error_string();
+// Kernels launched (or recorded into a graph capture) by the calling host thread so far: a split
+// Jacobi launch counts its three kernels. The solver handle keeps its launch count with it.
+long long be_kernel_count();
 
 // CUDA-graph capture of a launch sequence (returns non-zero when unsupported).
 int be_graph_begin(void* stream);

@@ -13,6 +13,7 @@
 namespace {
 
 thread_local cudaError_t g_last = cudaSuccess;
+thread_local long long g_kernels = 0;   // kernels launched by this host thread (see be_kernel_count)
 inline int rc_of(cudaError_t e) {
     if (e != cudaSuccess) {
         g_last = e;
@@ -130,6 +131,7 @@ template <typename T, int K> int launch_jacobi_k(const fb::JacobiArgs<T>& a, boo
         const dim3 grid = grid_for(a.g.nstrips, nchunks);
         if (mask) jacobi_kernel<T, V, K, true><<<grid, kThreads, smem, st>>>(all);
         else jacobi_kernel<T, V, K, false><<<grid, kThreads, smem, st>>>(all);
+        ++g_kernels;
         return rc_of(cudaGetLastError());
     }
     // split launch: GENERAL (wall chunks) and EDGE (y-edge strips) tasks on the side stream, FAST tasks
@@ -143,16 +145,19 @@ template <typename T, int K> int launch_jacobi_k(const fb::JacobiArgs<T>& a, boo
     if (nedge > 0) {
         const dim3 egrid((unsigned)((nedge + fb::kWarpsPerCta - 1) / fb::kWarpsPerCta), 1, 1);
         jacobi_edge_kernel<T, V, K><<<egrid, kThreads, smem, side->stream>>>(edge);
+        ++g_kernels;
         if (rc_of(cudaGetLastError())) return -1;
     }
     if (ngen > 0) {
         const dim3 ggrid((unsigned)((ngen + fb::kWarpsPerCta - 1) / fb::kWarpsPerCta), 1, 1);
         if (mask) jacobi_kernel<T, V, K, true><<<ggrid, kThreads, smem, side->stream>>>(gen);
         else jacobi_kernel<T, V, K, false><<<ggrid, kThreads, smem, side->stream>>>(gen);
+        ++g_kernels;
         if (rc_of(cudaGetLastError())) return -1;
     }
     if (rc_of(cudaEventRecord(side->join, side->stream))) return -1;
     jacobi_fast_kernel<T, V, K><<<grid_for(a.sf_hi - a.sf_lo, a.cf_hi - a.cf_lo), kThreads, smem, st>>>(fast);
+    ++g_kernels;
     if (rc_of(cudaGetLastError())) return -1;
     return rc_of(cudaStreamWaitEvent(st, side->join, 0));
 }
@@ -163,6 +168,7 @@ namespace fbk {
 
 const char* backend_name() { return "cuda-sm_100a"; }
 const char* be_last_error_string() { return cudaGetErrorString(g_last); }
+long long be_kernel_count() { return g_kernels; }
 int be_set_device(int device) { return rc_of(cudaSetDevice(device)); }
 int be_sm_count() {
     static thread_local int cached_dev = -1, cached = 148;
@@ -244,6 +250,7 @@ template <typename T> int launch_predictor(const fb::PredictorArgs<T>& a, int nc
     if (sizeof(T) == 4 && a.m.mode == 2) predictor_kernel<T, V, (sizeof(T) == 4 ? 2 : 0)><<<grid, kThreads, smem, st>>>(a);
     else if (sizeof(T) == 4 && a.m.mode == 1) predictor_kernel<T, V, (sizeof(T) == 4 ? 1 : 0)><<<grid, kThreads, smem, st>>>(a);
     else predictor_kernel<T, V, 0><<<grid, kThreads, smem, st>>>(a);
+    ++g_kernels;
     return rc_of(cudaGetLastError());
 }
 
@@ -258,6 +265,7 @@ template <typename T> int launch_corrector(const fb::CorrectorArgs<T>& a, bool m
     } else if (mode == 2) corrector_kernel<T, V, false, (sizeof(T) == 4 ? 2 : 0)><<<grid, kThreads, 0, st>>>(a);
     else if (mode == 1) corrector_kernel<T, V, false, (sizeof(T) == 4 ? 1 : 0)><<<grid, kThreads, 0, st>>>(a);
     else corrector_kernel<T, V, false, 0><<<grid, kThreads, 0, st>>>(a);
+    ++g_kernels;
     return rc_of(cudaGetLastError());
 }
 
@@ -270,6 +278,7 @@ int launch_init_cavity(T* const fields[7], long long pitch, int X, int Y, int ro
     long long blocks = (n + 255) / 256;
     if (blocks > 148LL * 16) blocks = 148LL * 16;
     init_cavity_kernel<T><<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(F, pitch, Y, n, lid);
+    ++g_kernels;
     return rc_of(cudaGetLastError());
 }
 

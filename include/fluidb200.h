@@ -260,7 +260,7 @@ int fluidb200_set_stream(fluidb200_solver* s, void* stream);       /* default: o
 int fluidb200_set_sweeps_per_launch(fluidb200_solver* s, int k);   /* temporal-blocking depth   */
 int fluidb200_set_use_graph(fluidb200_solver* s, int enable);      /* replay steps as CUDA graph */
 /* Kernels launched by this solver since creation (for bench.py's gpu_launches). */
-int64_t fluidb200_launch_count(const fluidb200_solver* s);
+int64_t fluidb200_launch_count(const fluidb200_solver* s);         /* kernels launched so far (a split Jacobi launch = 3) */
 
 /* ====================================================================================
  * Library-level

@@ -69,9 +69,12 @@ struct WarpRunner {
     }
 };
 
+static thread_local long long g_kernels = 0;  // one per emulated kernel launch (be_kernel_count)
+
 // run fn(strip, chunk, lane) for every warp task. Tasks are independent (disjoint outputs), so they
 // are spread over the host cores; each OS thread emulates one warp at a time.
 template <typename F> void run_grid(int nstrips, int nchunks, F fn) {
+    ++g_kernels;
     const int njobs = nstrips * nchunks;
     std::atomic<int> next{0};
     auto worker = [&] {
@@ -118,6 +121,7 @@ int be_stream_sync(void*) { return 0; }
 int be_graph_begin(void*) { return -1; }
 int be_graph_end(void*, void**) { return -1; }
 int be_graph_launch(void*, void*) { return -1; }
+long long be_kernel_count() { return g_kernels; }
 int be_graph_destroy(void*) { return 0; }
 
 static void set_ranges(std::initializer_list<const void*> ptrs, size_t bytes) {
