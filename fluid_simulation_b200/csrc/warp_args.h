@@ -32,9 +32,9 @@ struct Geom {
 
 // Grid spacing as the kernels consume it. hx2 = 2*hx (exact). The reciprocals feed the fp32
 // build's division-free arithmetic (see Ar<float> in warp_kernels.cuh); hx*hy is exact in double
-// (two 24-bit significands). `mode` selects that arithmetic: 0 = IEEE divisions (always valid,
-// the only mode of the fp64 build), 1 = division-free with flagged exact fallback, 2 = both
-// spacings are powers of two, divisions are exact scalings.
+// (two 24-bit significands). `mode` selects that arithmetic: 0 = IEEE divisions (always valid),
+// 1 = division-free with flagged exact fallback (fp32 only), 2 = both spacings are powers of two,
+// divisions are exact scalings (fp32 and fp64).
 template <typename T> struct Metric {
     T hx, hy, hx2, hy2;
     double inv_hx2, inv_hy2, inv_hxhy;
@@ -66,11 +66,12 @@ template <typename T> inline Metric<T> make_metric(T hx, T hy, int forced_mode =
         lo.f = (float)(7.52316384526264e-37 /* 2^-120 */ * (hxhy > 1.0 ? hxhy : 1.0));
         m.pow2_lo_m1 = lo.u - 1u;
     }
-    if (sizeof(T) == 4) {
+    {
         const double lo = 9.094947017729282e-13 /* 2^-40 */, hi = 1099511627776.0 /* 2^40 */;
         const bool sane = (double)hx >= lo && (double)hx <= hi && (double)hy >= lo && (double)hy <= hi;
-        if (sane) m.mode = (metric_is_pow2((double)hx) && metric_is_pow2((double)hy)) ? 2 : 1;
-        if (forced_mode >= 0 && forced_mode < m.mode) m.mode = forced_mode;  // only ever towards "more exact"
+        const bool pow2 = metric_is_pow2((double)hx) && metric_is_pow2((double)hy);
+        if (sane) m.mode = pow2 ? 2 : (sizeof(T) == 4 ? 1 : 0);  // fp64: exact reciprocals or IEEE divisions
+        if (forced_mode >= 0 && forced_mode < m.mode) m.mode = sizeof(T) == 4 ? forced_mode : 0;  // only ever towards "more exact"
     }
     return m;
 }

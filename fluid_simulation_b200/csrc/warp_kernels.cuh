@@ -138,12 +138,21 @@ template <> struct Ar<double> {
     static FB_DEV double add(double a, double b) { return __dadd_rn(a, b); }
     static FB_DEV double sub(double a, double b) { return __dsub_rn(a, b); }
     static FB_DEV double mul(double a, double b) { return __dmul_rn(a, b); }
-    template <int MODE> static FB_DEV double cdiff(double a, double b, double h, double h2, double, double, Flags&) {
+    // DIV_POW2 (hx, hy powers of two): x / h and x * (1/h) are the same real number rounded once, for
+    // every x including subnormal results, so each division becomes one multiplication by an exact
+    // reciprocal and nothing needs a flag. (fp64 has no division-free mode for other spacings.)
+    template <int MODE> static FB_DEV double cdiff(double a, double b, double h, double h2, double inv_h2, double, Flags&) {
         (void)h2;
-        return __ddiv_rn(__dmul_rn(__dsub_rn(a, b), 0.5), h);  // "/ 2." is an exact halving
+        const double half = __dmul_rn(__dsub_rn(a, b), 0.5);  // "/ 2." is an exact halving
+        if (MODE == DIV_POW2) return __dmul_rn(half, inv_h2 * 2.0);
+        return __ddiv_rn(half, h);
     }
-    template <int MODE> static FB_DEV double lap_tail(double s, double c, double hx, double hy, double, double, Flags&) {
+    template <int MODE> static FB_DEV double lap_tail(double s, double c, double hx, double hy, double inv_hxhy, double, Flags&) {
         double d = __fma_rn(-4.0, c, s);  // 4.*c exact -> single rounding
+        if (MODE == DIV_POW2) {
+            d = __dmul_rn(d, inv_hxhy * hy);       // 1/hx, exact
+            return __dmul_rn(d, inv_hxhy * hx);    // 1/hy, exact
+        }
         d = __ddiv_rn(d, hx);
         return __ddiv_rn(d, hy);
     }

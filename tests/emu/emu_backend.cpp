@@ -188,8 +188,8 @@ template <typename T> int launch_jacobi(const fb::JacobiArgs<T>& a, int sweeps, 
 template <typename T> int launch_predictor(const fb::PredictorArgs<T>& a, int nchunks, void*) {
     constexpr int V = fb::VecWidth<T>::V;
     set_ranges({a.u, a.v, a.us, a.vs, a.rhs}, (size_t)a.g.rows * a.g.pitch * sizeof(T));
-    const int mode = sizeof(T) == 4 ? a.m.mode : 0;
-    if (mode == 2) run_grid(a.g.nstrips, nchunks, [&](int s, int c, int l) { fb::predictor_task<T, V, (sizeof(T) == 4 ? 2 : 0)>(a, s, c, l, l, 32); });
+    const int mode = a.m.mode;
+    if (mode == 2) run_grid(a.g.nstrips, nchunks, [&](int s, int c, int l) { fb::predictor_task<T, V, 2>(a, s, c, l, l, 32); });
     else if (mode == 1) run_grid(a.g.nstrips, nchunks, [&](int s, int c, int l) { fb::predictor_task<T, V, (sizeof(T) == 4 ? 1 : 0)>(a, s, c, l, l, 32); });
     else run_grid(a.g.nstrips, nchunks, [&](int s, int c, int l) { fb::predictor_task<T, V, 0>(a, s, c, l, l, 32); });
     return 0;
@@ -197,11 +197,11 @@ template <typename T> int launch_predictor(const fb::PredictorArgs<T>& a, int nc
 template <typename T> int launch_corrector(const fb::CorrectorArgs<T>& a, bool mask, int nchunks, void*) {
     constexpr int V = fb::VecWidth<T>::V;
     set_ranges({a.p, a.us, a.vs, a.u, a.v}, (size_t)a.g.rows * a.g.pitch * sizeof(T));
-    const int mode = sizeof(T) == 4 ? a.m.mode : 0;
+    const int mode = a.m.mode;
     if (mask) {
         if (mode != 0) run_grid(a.g.nstrips, nchunks, [&](int s, int c, int l) { fb::corrector_task<T, V, true, (sizeof(T) == 4 ? 1 : 0)>(a, s, c, l); });
         else run_grid(a.g.nstrips, nchunks, [&](int s, int c, int l) { fb::corrector_task<T, V, true, 0>(a, s, c, l); });
-    } else if (mode == 2) run_grid(a.g.nstrips, nchunks, [&](int s, int c, int l) { fb::corrector_task<T, V, false, (sizeof(T) == 4 ? 2 : 0)>(a, s, c, l); });
+    } else if (mode == 2) run_grid(a.g.nstrips, nchunks, [&](int s, int c, int l) { fb::corrector_task<T, V, false, 2>(a, s, c, l); });
     else if (mode == 1) run_grid(a.g.nstrips, nchunks, [&](int s, int c, int l) { fb::corrector_task<T, V, false, (sizeof(T) == 4 ? 1 : 0)>(a, s, c, l); });
     else run_grid(a.g.nstrips, nchunks, [&](int s, int c, int l) { fb::corrector_task<T, V, false, 0>(a, s, c, l); });
     return 0;
@@ -250,6 +250,22 @@ template <int MODE> static void lap_hook(const float* s, const float* c, float h
     }
 }
 extern "C" int emu_metric_mode_f32(float hx, float hy) { return fb::make_metric<float>(hx, hy).mode; }
+extern "C" int emu_metric_mode_f64(double hx, double hy) { return fb::make_metric<double>(hx, hy).mode; }
+// fp64: mode 2 (power-of-two spacing) against mode 0, element-wise
+extern "C" void emu_cdiff_f64(int mode, const double* a, const double* b, double h, long long n, double* out) {
+    const fb::Metric<double> m = fb::make_metric<double>(h, h);
+    fb::Flags fl;
+    for (long long i = 0; i < n; ++i)
+        out[i] = mode == 2 ? fb::Ar<double>::cdiff<2>(a[i], b[i], m.hx, m.hx2, m.inv_hx2, 0.0, fl)
+                           : fb::Ar<double>::cdiff<0>(a[i], b[i], m.hx, m.hx2, m.inv_hx2, 0.0, fl);
+}
+extern "C" void emu_lap_tail_f64(int mode, const double* s, const double* c, double hx, double hy, long long n, double* out) {
+    const fb::Metric<double> m = fb::make_metric<double>(hx, hy);
+    fb::Flags fl;
+    for (long long i = 0; i < n; ++i)
+        out[i] = mode == 2 ? fb::Ar<double>::lap_tail<2>(s[i], c[i], m.hx, m.hy, m.inv_hxhy, 0.0, fl)
+                           : fb::Ar<double>::lap_tail<0>(s[i], c[i], m.hx, m.hy, m.inv_hxhy, 0.0, fl);
+}
 extern "C" void emu_cdiff_f32(int mode, const float* a, const float* b, float h, long long n, float* out) {
     if (mode == 2) cdiff_hook<2>(a, b, h, n, out); else if (mode == 1) cdiff_hook<1>(a, b, h, n, out); else cdiff_hook<0>(a, b, h, n, out);
 }

@@ -93,3 +93,36 @@ def test_laplacian_tail_ambiguous_cases_take_the_exact_path(emu):
     emu.emu_lap_tail_f32(1, s.ctypes.data, c.ctypes.data, hx32, hy32, s.size, out.ctypes.data)
     want = (s.astype(np.float64) / np.float64(hx32) / np.float64(hy32)).astype(np.float32)
     assert np.array_equal(out.view(np.uint32), want.view(np.uint32))
+
+
+@pytest.mark.parametrize("hx,hy", [(1.0, 1.0), (1.0 / 128, 1.0 / 256), (4.0, 0.25), (2.0 ** -30, 2.0 ** -30), (2.0 ** 20, 2.0 ** 20)])
+def test_fp64_power_of_two_mode_is_the_division(emu, hx, hy):
+    """fp64 has one division-free mode: with power-of-two spacings every division is a multiplication
+    by an exact reciprocal, i.e. the same real number rounded once -- for every input, subnormal
+    results included, so there is nothing to flag."""
+    emu.emu_cdiff_f64.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_double, C.c_longlong, C.c_void_p]
+    emu.emu_lap_tail_f64.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_double, C.c_double, C.c_longlong, C.c_void_p]
+    emu.emu_metric_mode_f64.argtypes = [C.c_double, C.c_double]
+    assert emu.emu_metric_mode_f64(hx, hy) == 2 and emu.emu_metric_mode_f64(0.1, hy) == 0
+    n = 200_000
+    rng = np.random.default_rng(11)
+    def inputs(seed):
+        r = np.random.default_rng(seed)
+        x = r.uniform(1.0, 2.0, n) * np.exp2(r.integers(-1074, 200, n).astype(np.float64)) * r.choice([-1.0, 1.0], n)
+        x[r.integers(0, n, n // 50)] = 0.0
+        x[r.integers(0, n, n // 50)] = -0.0
+        x[r.integers(0, n, n // 20)] = r.integers(1, 1 << 52, n // 20).astype(np.uint64).view(np.float64)  # subnormals
+        return x
+    a, b, c = inputs(1), inputs(2), inputs(3)
+    s = 4.0 * c * (1 + rng.normal(0, 1e-9, n))
+    s[: n // 3] = inputs(5)[: n // 3]
+    with np.errstate(all="ignore"):
+        want_c = (a - b) / 2.0 / hx
+        want_l = (s - 4.0 * c) / hx / hy     # numpy rounds s - 4c twice (4c is exact, so once): same as the fma
+    for want, call in ((want_c, lambda m, o: emu.emu_cdiff_f64(m, a.ctypes.data, b.ctypes.data, hx, n, o.ctypes.data)),
+                       (want_l, lambda m, o: emu.emu_lap_tail_f64(m, s.ctypes.data, c.ctypes.data, hx, hy, n, o.ctypes.data))):
+        for mode in (0, 2):
+            out = np.empty(n, np.float64)
+            call(mode, out)
+            ok = (out.view(np.uint64) == want.view(np.uint64)) | (np.isnan(out) & np.isnan(want))
+            assert ok.all(), f"mode {mode}: {np.count_nonzero(~ok)} mismatches"

@@ -206,19 +206,20 @@ def test_division_modes_agree_with_the_reference(Solver, env, X, Y, divmode):
     s.close()
 
 
+@pytest.mark.parametrize("dtype", ["float32", "float64"])
 @pytest.mark.parametrize("kmax", [2, 5])
-def test_unit_spacing(Solver, kmax):
-    """domain = (X-1, Y-1) => hx = hy = 1: the benchmark's spacing (power-of-two arithmetic mode, and
-    the Jacobi kernel skips the exact multiplications of rhs by hx and hy)."""
+def test_unit_spacing(Solver, kmax, dtype):
+    """domain = (X-1, Y-1) => hx = hy = 1: the benchmark's spacing (power-of-two arithmetic mode in fp32
+    and fp64, and the Jacobi kernel skips the exact multiplications of rhs by hx and hy)."""
     X, Y = 48, 300
-    o = Oracle(X, Y, float(X - 1), float(Y - 1)).set_cavity()
+    o = Oracle(X, Y, float(X - 1), float(Y - 1), np.dtype(dtype)).set_cavity()
     o.time_step, o.num_iterations, o.num_poisson_iterations = 0.001, 3, 7
-    s = Solver(X, Y, float(X - 1), float(Y - 1)).set_cavity()
+    s = Solver(X, Y, float(X - 1), float(Y - 1), np.dtype(dtype)).set_cavity()
     s.time_step, s.num_iterations, s.num_poisson_iterations = 0.001, 3, 7
     s.set_sweeps_per_launch(kmax)
     s.migrateSolve()
     o.solve()
-    H.compare_with(s, o, tag=f"unit/k{kmax}")
+    H.compare_with(s, o, tag=f"unit/k{kmax}/{dtype}")
     s.close()
 
 
@@ -342,4 +343,17 @@ def test_cavity_with_obstacles_keeps_lean_kernels(Solver, env, depth):
     s.migrateSolve()
     o.solve()
     H.compare_with(s, o, tag=f"obstacles/depth{depth}")
+    s.close()
+
+
+@pytest.mark.parametrize("X,Y", [(33, 257), (65, 129)])
+def test_fp64_power_of_two_spacing(Solver, X, Y):
+    """2^k + 1 points on the unit box in fp64: divisions become multiplications by exact reciprocals."""
+    o = Oracle(X, Y, 1.0, 1.0, np.dtype("float64")).set_cavity()
+    o.time_step, o.num_iterations, o.num_poisson_iterations = 2e-5, 3, 9
+    s = Solver(X, Y, 1.0, 1.0, np.dtype("float64")).set_cavity()
+    s.time_step, s.num_iterations, s.num_poisson_iterations = 2e-5, 3, 9
+    s.migrateSolve()
+    o.solve()
+    H.compare_with(s, o, tag=f"f64-pow2/{X}x{Y}")
     s.close()
