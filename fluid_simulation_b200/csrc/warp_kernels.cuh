@@ -8,7 +8,8 @@
 //     so every global access is a coalesced 128-bit load/store) and marches along x;
 //   * x-neighbours live in the lane's own registers (a sliding window of rows),
 //     y-neighbours of the lane's outer elements come from the adjacent lane by one
-//     warp shuffle -- no shared memory, no block barrier, no atomics;
+//     warp shuffle -- no block barrier, no atomics; shared memory only as a per-lane
+//     prefetch ring (cp.async), never to exchange data between lanes;
 //   * strips overlap by a 2*H column halo and x-chunks by the stencil radius, the overlap is
 //     recomputed (a few percent) so that warps never communicate.
 //
@@ -673,9 +674,11 @@ FB_DEV void jacobi_task(const JacobiArgs<T>& A, int strip, int chunk, int lane, 
 
 // The FAST-ONLY twin of jacobi_task: same pipeline, same arithmetic, but compiled without any of
 // the general path (walls, y-edges, masks, range checks), which is what sets the register count
-// of jacobi_task (K=5: 149 -> 126 registers, K=8: 210 -> 168), i.e. one more resident CTA per SM.
-// The host (split_jacobi in api.cpp) only sends it tasks for which EVERY step is a fast step:
-// strip without a y-edge column, r_begin = c0-K >= max(row0, K+2), r_end = c1-1+K <= X-2.
+// of jacobi_task (K=6: 166 -> 128 registers, K=8: 214 -> 162), i.e. one more resident CTA per SM.
+// The host (split_jacobi in api.cpp) only sends it tasks for which EVERY step is a plain step in x:
+// r_begin = c0-K >= max(row0, K+2), r_end = c1-1+K <= X-2. YEDGE = false: the strip holds no y-edge
+// column (FAST kernel); YEDGE = true: it does and the two y-edge cells of every level are added,
+// branch-free, for constant / copy edges (EDGE kernel). SCALE_B: the grid is not unit spaced.
 // The step count is rounded UP to a multiple of U; the extra steps read clamped rows and are
 // never stored.
 template <typename T, int V, int K, bool SCALE_B, bool YEDGE>

@@ -130,7 +130,7 @@ static void set_ranges(std::initializer_list<const void*> ptrs, size_t bytes) {
         if (p) emu_ranges[emu_nranges++] = {(const char*)p, (const char*)p + bytes};
 }
 // Emulates the CUDA wrappers literally: (blockIdx.x, blockIdx.y, warp) -> task through the same
-// jacobi_decode_task, so the split launch (FAST twin + GENERAL kernel) is what gets tested.
+// jacobi_decode_task, so the split launch (FAST, EDGE and GENERAL kernel) is what gets tested.
 template <typename T, int K>
 static void jac_k(const fb::JacobiArgs<T>& a, bool mask, int nchunks) {
     set_ranges({a.p_in, a.p_out, a.rhs}, (size_t)a.g.rows * a.g.pitch * sizeof(T));
