@@ -326,6 +326,8 @@ extern "C" int fluidb200_poisson_sweeps(const fluidb200_slab* g, const void* p_i
                     FLUIDB200_MAX_SWEEPS_PER_LAUNCH, sweeps);
     if (mask && mask->set) {
         if (!mask->val) return fail(FLUIDB200_EINVAL, "mask.val is NULL");
+        if ((uintptr_t)mask->set % 4 != 0 || (uintptr_t)mask->val % 16 != 0)
+            return fail(FLUIDB200_EINVAL, "mask.set must be 4-byte and mask.val 16-byte aligned");
     }
     if ((rc = check_range(g, out_lo, out_hi, sweeps, "poisson"))) return rc;
     return g->dtype == FLUIDB200_F32
@@ -549,7 +551,7 @@ int step_predictor(fluidb200_solver* s) {
 // run the general path, which is instruction and latency bound (no row prefetch), so a deep pipeline
 // only makes those few tasks the critical path of the launch. Measured at 8192^2, us per sweep:
 //   no tile summary (every task general): depth 1 255, depth 2 192, depth 4 203, depth 8 366 -> 2;
-//   tile summary, one 64 x 64 obstacle  : depth 1 155, depth 2 79, depth 4 50, depth 6 53, depth 8 61 -> 4
+//   tile summary, one 64 x 64 obstacle  : depth 2 76, depth 4 41, depth 6 40, depth 8 41 -> 4
 //   (the same grid without flags: 23 at depth 8).
 constexpr int kMaskedKmaxDefault = 2, kSparseMaskedKmax = 4;
 int masked_kmax() { return std::max(1, env_int("FLUIDB200_MASK_KMAX", kMaskedKmaxDefault)); }

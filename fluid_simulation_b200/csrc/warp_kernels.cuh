@@ -198,6 +198,13 @@ template <typename T, int V> FB_DEV void st_vec(T* p, const Vec<T, V>& v) {
 }
 
 
+// V consecutive flag bytes as one integer (byte e = flag of element e); the address is V-aligned
+template <int V> FB_DEV unsigned load_flags(const uint8_t* p) {
+    static_assert(V == 2 || V == 4, "16 bytes per lane: 4 floats or 2 doubles");
+    if (V == 4) return *reinterpret_cast<const uint32_t*>(p);
+    return *reinterpret_cast<const uint16_t*>(p);
+}
+
 // Per-lane view of a strip.
 template <int V, int H> struct Strip {
     static constexpr int W = 32 * V;      // columns loaded by the warp
@@ -568,6 +575,9 @@ FB_DEV void jacobi_task(const JacobiArgs<T>& A, int strip, int chunk, int lane, 
     nfast -= nfast % U;
     const int fast_hi = fast_lo + nfast - 1;
 
+    unsigned fw[K], fnext = 0u;  // MASK: flags of rows r-1 .. r-K, and of row r (nothing precedes r_begin)
+#pragma unroll
+    for (int t = 0; t < K; ++t) fw[t] = 0u;
     int r = r_begin;
 #pragma unroll 1
     for (int phase = 0; phase < 2; ++phase) {
@@ -584,6 +594,16 @@ FB_DEV void jacobi_task(const JacobiArgs<T>& A, int strip, int chunk, int lane, 
             if (r >= load_hi) cur = vzero<T, V>();
             if (!(r - 1 >= r_begin && r - 1 < load_hi && r - 1 >= 1 && r - 1 <= X - 2)) bnew = vzero<T, V>();
             push_b(bnew);
+            if (MASK) {
+                // The flags of a row travel down the levels like its right-hand side: read once, one step
+                // before level 1 needs them (V flag bytes in one load: col0 and the pitch are multiples
+                // of V), instead of once per level with the load latency inside every level.
+#pragma unroll
+                for (int t = K - 1; t > 0; --t) fw[t] = fw[t - 1];
+                fw[0] = fnext;
+                fnext = (st.ld_ok && r < load_hi)
+                            ? load_flags<V>(A.mset + (long long)(r - g.row0) * g.pitch + st.col0) : 0u;
+            }
 #pragma unroll
             for (int t = 1; t <= K; ++t) {
                 const int rr = r - t;  // row this level produces now
@@ -599,13 +619,15 @@ FB_DEV void jacobi_task(const JacobiArgs<T>& A, int strip, int chunk, int lane, 
                         if (rr == X - 2) xp = wall_row<T, V>(A.e, RIGHT, c, st.col0, Y);
                     }
                     out = jacobi_row<T, V>(xm, c, xp, bw[t - 1]);
-                    if (MASK) {  // interior flags (:154-160)
-                        const long long off = (long long)(rr - g.row0) * g.pitch + st.col0;
-                        if (st.ld_ok && rr >= r_begin && rr < load_hi) {
+                    if (MASK) {  // interior flags (:154-160); fw[t-1] = this lane's flags of row rr
+                        const unsigned f4 = fw[t - 1];
+                        if (f4) {  // rare: only then are the values fetched
+                            const long long off = (long long)(rr - g.row0) * g.pitch + st.col0;
+                            const VT mv = *reinterpret_cast<const VT*>(A.mval + off);
 #pragma unroll
                             for (int e = 0; e < V; ++e) {
                                 const int col = st.col0 + e;
-                                if (col >= 1 && col <= Y - 2 && A.mset[off + e]) out.a[e] = A.mval[off + e];
+                                if (col >= 1 && col <= Y - 2 && ((f4 >> (8 * e)) & 0xffu)) out.a[e] = mv.a[e];
                             }
                         }
                     }

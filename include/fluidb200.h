@@ -99,8 +99,8 @@ typedef struct fluidb200_edges {
  * lid-driven cavity and the fast path (SerialNavierStokes.cpp:154-160 / :224-233 then do
  * nothing). */
 typedef struct fluidb200_mask {
-    const uint8_t* set;       /* device uint8[rows*pitch] or NULL                         */
-    const void* val;          /* device T[rows*pitch]     or NULL                         */
+    const uint8_t* set;       /* device uint8[rows*pitch] or NULL (4-byte aligned)        */
+    const void* val;          /* device T[rows*pitch]     or NULL (16-byte aligned)       */
     /* Optional (pressure mask only, may be NULL): a summary of `set`, one byte per tile of
      * FLUIDB200_MASK_TILE_ROWS x FLUIDB200_MASK_TILE_COLS cells (local rows, columns from 0),
      * tile (tr, tc) at tiles[tr * ceil(Y / TILE_COLS) + tc], non-zero when the tile holds a
