@@ -29,8 +29,37 @@ constexpr int kThreads = fb::kWarpsPerCta * 32;
 #ifndef FLUIDB200_JACOBI_MIN_BLOCKS
 #define FLUIDB200_JACOBI_MIN_BLOCKS(K) ((K) <= 2 ? 5 : (K) <= 4 ? 4 : (K) <= 6 ? 3 : 2)
 #endif
+// Programmatic dependent launch (sm_90+): a kernel launched with the attribute below may be scheduled
+// while its predecessor in the stream is still running; it announces at once that its own successor
+// may do the same and then waits, before touching any memory, until the predecessor has completed
+// and its writes are visible. What overlaps is launch latency and CTA scheduling, which is most of
+// a ~10 us launch on a small grid. Without the attribute both instructions are no-ops.
+__device__ __forceinline__ void pdl_prologue() {
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+    asm volatile("griddepcontrol.wait;" ::: "memory");
+}
+bool pdl_enabled() {
+    static const bool on = [] { const char* e = getenv("FLUIDB200_PDL"); return !e || atoi(e) != 0; }();
+    return on;
+}
+template <typename A>
+cudaError_t launch_k(void (*kern)(A), dim3 grid, size_t smem, cudaStream_t st, const A& arg) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid;
+    cfg.blockDim = dim3(kThreads, 1, 1);
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = st;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = at;
+    cfg.numAttrs = pdl_enabled() ? 1 : 0;
+    return cudaLaunchKernelEx(&cfg, kern, arg);
+}
+
 template <typename T, int V, int K, bool MASK>
 __global__ void __launch_bounds__(kThreads, FLUIDB200_JACOBI_MIN_BLOCKS(K)) jacobi_kernel(const __grid_constant__ fb::JacobiArgs<T> A) {
+    pdl_prologue();
     int strip, chunk;  // whole warps only; the tasks use no block barrier
     if (!fb::jacobi_decode_task(A, (int)blockIdx.x, (int)blockIdx.y, (int)(threadIdx.x >> 5), fb::kWarpsPerCta, &strip, &chunk)) return;
     fb::jacobi_general_task<T, V, K, MASK>(A, strip, chunk, threadIdx.x & 31, threadIdx.x, kThreads);
@@ -43,6 +72,7 @@ __global__ void __launch_bounds__(kThreads, FLUIDB200_JACOBI_MIN_BLOCKS(K)) jaco
 #endif
 template <typename T, int V, int K>
 __global__ void __launch_bounds__(kThreads, FLUIDB200_JACOBI_FAST_MIN_BLOCKS(K)) jacobi_fast_kernel(const __grid_constant__ fb::JacobiArgs<T> A) {
+    pdl_prologue();
     int strip, chunk;
     if (!fb::jacobi_decode_task(A, (int)blockIdx.x, (int)blockIdx.y, (int)(threadIdx.x >> 5), fb::kWarpsPerCta, &strip, &chunk)) return;
     fb::jacobi_fast_task<T, V, K>(A, strip, chunk, threadIdx.x & 31, threadIdx.x, kThreads);
@@ -54,6 +84,7 @@ __global__ void __launch_bounds__(kThreads, FLUIDB200_JACOBI_FAST_MIN_BLOCKS(K))
 #endif
 template <typename T, int V, int K>
 __global__ void __launch_bounds__(kThreads, FLUIDB200_JACOBI_EDGE_MIN_BLOCKS(K)) jacobi_edge_kernel(const __grid_constant__ fb::JacobiArgs<T> A) {
+    pdl_prologue();
     int strip, chunk;
     if (!fb::jacobi_decode_task(A, (int)blockIdx.x, (int)blockIdx.y, (int)(threadIdx.x >> 5), fb::kWarpsPerCta, &strip, &chunk)) return;
     fb::jacobi_edge_task<T, V, K>(A, strip, chunk, threadIdx.x & 31, threadIdx.x, kThreads);
@@ -61,6 +92,7 @@ __global__ void __launch_bounds__(kThreads, FLUIDB200_JACOBI_EDGE_MIN_BLOCKS(K))
 
 template <typename T, int V, int MODE>
 __global__ void __launch_bounds__(kThreads) predictor_kernel(const __grid_constant__ fb::PredictorArgs<T> A) {
+    pdl_prologue();
     const int strip = blockIdx.x * fb::kWarpsPerCta + (threadIdx.x >> 5);
     if (strip >= A.g.nstrips) return;
     fb::predictor_task<T, V, MODE>(A, strip, blockIdx.y, threadIdx.x & 31, threadIdx.x, kThreads);
@@ -68,6 +100,7 @@ __global__ void __launch_bounds__(kThreads) predictor_kernel(const __grid_consta
 
 template <typename T, int V, bool MASK, int MODE>
 __global__ void __launch_bounds__(kThreads, 4) corrector_kernel(const __grid_constant__ fb::CorrectorArgs<T> A) {
+    pdl_prologue();
     const int strip = blockIdx.x * fb::kWarpsPerCta + (threadIdx.x >> 5);
     if (strip >= A.g.nstrips) return;
     fb::corrector_task<T, V, MASK, MODE>(A, strip, blockIdx.y, threadIdx.x & 31);
@@ -129,8 +162,8 @@ template <typename T, int K> int launch_jacobi_k(const fb::JacobiArgs<T>& a, boo
         fb::JacobiArgs<T> all = a;
         all.part = 0;
         const dim3 grid = grid_for(a.g.nstrips, nchunks);
-        if (mask) jacobi_kernel<T, V, K, true><<<grid, kThreads, smem, st>>>(all);
-        else jacobi_kernel<T, V, K, false><<<grid, kThreads, smem, st>>>(all);
+        if (mask) launch_k(jacobi_kernel<T, V, K, true>, grid, smem, st, all);
+        else launch_k(jacobi_kernel<T, V, K, false>, grid, smem, st, all);
         ++g_kernels;
         return rc_of(cudaGetLastError());
     }
@@ -156,7 +189,7 @@ template <typename T, int K> int launch_jacobi_k(const fb::JacobiArgs<T>& a, boo
         if (rc_of(cudaGetLastError())) return -1;
     }
     if (rc_of(cudaEventRecord(side->join, side->stream))) return -1;
-    jacobi_fast_kernel<T, V, K><<<grid_for(a.sf_hi - a.sf_lo, a.cf_hi - a.cf_lo), kThreads, smem, st>>>(fast);
+    launch_k(jacobi_fast_kernel<T, V, K>, grid_for(a.sf_hi - a.sf_lo, a.cf_hi - a.cf_lo), smem, st, fast);
     ++g_kernels;
     if (rc_of(cudaGetLastError())) return -1;
     return rc_of(cudaStreamWaitEvent(st, side->join, 0));
@@ -247,9 +280,9 @@ template <typename T> int launch_predictor(const fb::PredictorArgs<T>& a, int nc
     cudaStream_t st = (cudaStream_t)stream;
     // the arithmetic mode is a compile-time property of the kernel (see Metric::mode); fp64 has modes 0 and 2
     const size_t smem = (size_t)FLUIDB200_PRED_D * 2 * 16 * kThreads;  // per-lane cp.async ring: D slots x {u, v} x 16 B
-    if (a.m.mode == 2) predictor_kernel<T, V, 2><<<grid, kThreads, smem, st>>>(a);
-    else if (sizeof(T) == 4 && a.m.mode == 1) predictor_kernel<T, V, (sizeof(T) == 4 ? 1 : 0)><<<grid, kThreads, smem, st>>>(a);
-    else predictor_kernel<T, V, 0><<<grid, kThreads, smem, st>>>(a);
+    if (a.m.mode == 2) launch_k(predictor_kernel<T, V, 2>, grid, smem, st, a);
+    else if (sizeof(T) == 4 && a.m.mode == 1) launch_k(predictor_kernel<T, V, (sizeof(T) == 4 ? 1 : 0)>, grid, smem, st, a);
+    else launch_k(predictor_kernel<T, V, 0>, grid, smem, st, a);
     ++g_kernels;
     return rc_of(cudaGetLastError());
 }
@@ -260,11 +293,11 @@ template <typename T> int launch_corrector(const fb::CorrectorArgs<T>& a, bool m
     cudaStream_t st = (cudaStream_t)stream;
     const int mode = a.m.mode;  // (fp64 never reports mode 1)
     if (mask) {  // the general-BC path is not specialised further
-        if (mode != 0) corrector_kernel<T, V, true, (sizeof(T) == 4 ? 1 : 0)><<<grid, kThreads, 0, st>>>(a);
-        else corrector_kernel<T, V, true, 0><<<grid, kThreads, 0, st>>>(a);
-    } else if (mode == 2) corrector_kernel<T, V, false, 2><<<grid, kThreads, 0, st>>>(a);
-    else if (mode == 1) corrector_kernel<T, V, false, (sizeof(T) == 4 ? 1 : 0)><<<grid, kThreads, 0, st>>>(a);
-    else corrector_kernel<T, V, false, 0><<<grid, kThreads, 0, st>>>(a);
+        if (mode != 0) launch_k(corrector_kernel<T, V, true, (sizeof(T) == 4 ? 1 : 0)>, grid, 0, st, a);
+        else launch_k(corrector_kernel<T, V, true, 0>, grid, 0, st, a);
+    } else if (mode == 2) launch_k(corrector_kernel<T, V, false, 2>, grid, 0, st, a);
+    else if (mode == 1) launch_k(corrector_kernel<T, V, false, (sizeof(T) == 4 ? 1 : 0)>, grid, 0, st, a);
+    else launch_k(corrector_kernel<T, V, false, 0>, grid, 0, st, a);
     ++g_kernels;
     return rc_of(cudaGetLastError());
 }
