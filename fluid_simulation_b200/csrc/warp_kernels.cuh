@@ -522,6 +522,9 @@ FB_DEV void jacobi_task(const JacobiArgs<T>& A, int strip, int chunk, int lane, 
     const T* rin = A.rhs + base;
     T* pout = A.p_out + (long long)st.col0 - (long long)g.row0 * g.pitch;
     const bool y_edges = st.has_bottom || st.has_top;
+    const bool ye_uniform = A.e.mode[BOTTOM] != EDGE_ARRAY && A.e.mode[TOP] != EDGE_ARRAY;
+    YEdgeUniform<T, V> ye;
+    ye.init(A.e, st);
 
     VT w[K][2];
     VT bw[K];
@@ -631,7 +634,10 @@ FB_DEV void jacobi_task(const JacobiArgs<T>& A, int strip, int chunk, int lane, 
                             }
                         }
                     }
-                    if (y_edges) apply_y_edges<T, V, H>(A.e, st, rr, out, out, out);  // (:163-175)
+                    if (y_edges) {  // (:163-175)
+                        if (ye_uniform) ye.apply(out);  // constant / copy edges: a shuffle and a few selects
+                        else apply_y_edges<T, V, H>(A.e, st, rr, out, out, out);
+                    }
                     if (t == K) {
                         if (rr >= c0 && rr < c1 && st.st_ok) st_vec<T, V>(pout + (long long)rr * g.pitch, out);
                         if (rr == 1 && c0 == 0) {
