@@ -511,7 +511,7 @@ int upload_bc_t(fluidb200_solver* s, int f, const T* val, const uint8_t* set) {
         BE_CHECK(fbk::be_memcpy2d_async(ds, s->pitch, set, Y, Y, X, fbk::H2D, s->stream), "mask upload");
         BE_CHECK(fbk::be_memcpy2d_async(dv, s->pitch * sizeof(T), val, Y * sizeof(T), Y * sizeof(T), X, fbk::H2D,
                                         s->stream), "mask upload");
-        if (f == 2) {
+        if (f == 2 && !env_int("FLUIDB200_NO_MASK_TILES", 0)) {
             // tile summary of the interior pressure flags: lets a masked Jacobi launch keep its lean kernels
             // wherever there is no flag (see fluidb200_mask::tiles)
             const int TR = FLUIDB200_MASK_TILE_ROWS, TC = FLUIDB200_MASK_TILE_COLS;
