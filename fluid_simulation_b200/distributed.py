@@ -229,11 +229,43 @@ class SlabSolver:
 
     def step(self):
         """One projection timestep (phase order of SerialNavierStokes.cpp:49-67)."""
+        mark = self._phase_marks()
         if self.world > 1:
             self.exchange(["u", "v"], self.H)
+        mark("exchange_uv")
         self.predictor()
+        mark("predictor")
         self.poisson(self.num_poisson_iterations)
+        mark("poisson")
         self.corrector()
+        mark("corrector")
+
+    def _phase_marks(self):
+        """FLUIDB200_SLAB_TIMING=1: CUDA events on the main stream around the phases of a step, collected
+        for phase_ms(). Otherwise a no-op. (The first phase also absorbs any wait for a slower neighbour.)"""
+        if not (self.on_gpu and os.environ.get("FLUIDB200_SLAB_TIMING")):
+            return lambda name: None
+        torch = self.torch
+        if not hasattr(self, "_phase_events"):
+            self._phase_events = []
+        prev = [torch.cuda.Event(enable_timing=True)]
+        prev[0].record(self.main)
+
+        def mark(name):
+            ev = torch.cuda.Event(enable_timing=True)
+            ev.record(self.main)
+            self._phase_events.append((name, prev[0], ev))
+            prev[0] = ev
+        return mark
+
+    def phase_ms(self):
+        """Milliseconds per phase summed over the steps since the last call (synchronizes)."""
+        self.synchronize()
+        out = {}
+        for name, a, b in getattr(self, "_phase_events", []):
+            out[name] = out.get(name, 0.0) + a.elapsed_time(b)
+        self._phase_events = []
+        return out
 
     def solve(self):
         for _ in range(int(self.num_iterations)):
