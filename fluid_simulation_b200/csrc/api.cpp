@@ -13,6 +13,7 @@
 
 #include "../../include/fluidb200.h"
 #include "backend.h"
+#include "internal.h"
 
 namespace {
 
@@ -228,7 +229,7 @@ void split_jacobi(fb::JacobiArgs<T>* a, const fluidb200_slab* g, int K, int nchu
 template <typename T>
 int poisson_t(const fluidb200_slab* g, const void* p_in, void* p_out, const void* rhs,
               const fluidb200_edges* e, const fluidb200_mask* mask, int sweeps, int out_lo, int out_hi,
-              void* stream) {
+              void* stream, bool allow_split) {
     fb::JacobiArgs<T> a;
     a.p_in = (const T*)p_in; a.p_out = (T*)p_out; a.rhs = (const T*)rhs;
     const bool use_mask = mask && mask->set;
@@ -251,7 +252,7 @@ int poisson_t(const fluidb200_slab* g, const void* p_in, void* p_out, const void
     a.head = out_lo == 0 ? 2 * sweeps + 2 : 0;
     a.tail = out_hi == g->X ? sweeps + 1 : 0;
     a.part = 0;
-    if ((!use_mask || a.mtiles) && (a.head || a.tail) && n - a.head - a.tail >= 4 * sweeps + 8) {
+    if (allow_split && (!use_mask || a.mtiles) && (a.head || a.tail) && n - a.head - a.tail >= 4 * sweeps + 8) {
         plan_chunks(n - a.head - a.tail, sweeps, nstrips, ctas_per_sm, tasks, &rpc, &nchunks);
         nchunks += (a.head > 0) + (a.tail > 0);
         a.g = make_geom(g, nstrips, rpc);
@@ -262,6 +263,7 @@ int poisson_t(const fluidb200_slab* g, const void* p_in, void* p_out, const void
         plan_chunks(n, sweeps, nstrips, ctas_per_sm, tasks, &rpc, &nchunks);
         a.g = make_geom(g, nstrips, rpc);
         split_jacobi<T>(&a, g, sweeps, nchunks, use_mask);
+        if (!allow_split) a.part = 0;
     }
     BE_CHECK(fbk::launch_jacobi<T>(a, sweeps, use_mask, nchunks, stream), "poisson launch");
     return 0;
@@ -315,6 +317,12 @@ extern "C" int fluidb200_poisson_sweeps(const fluidb200_slab* g, const void* p_i
                                         const void* rhs, const fluidb200_edges* p_edges,
                                         const fluidb200_mask* mask, int sweeps, int out_lo, int out_hi,
                                         void* stream) {
+    return fbapi::poisson_sweeps(g, p_in, p_out, rhs, p_edges, mask, sweeps, out_lo, out_hi, stream, 0);
+}
+
+int fbapi::poisson_sweeps(const fluidb200_slab* g, const void* p_in, void* p_out, const void* rhs,
+                          const fluidb200_edges* p_edges, const fluidb200_mask* mask, int sweeps, int out_lo,
+                          int out_hi, void* stream, int flags) {
     int rc;
     if ((rc = check_slab(g))) return rc;
     if ((rc = check_ptr(p_in, "p_in")) || (rc = check_ptr(p_out, "p_out")) || (rc = check_ptr(rhs, "rhs")))
@@ -330,9 +338,11 @@ extern "C" int fluidb200_poisson_sweeps(const fluidb200_slab* g, const void* p_i
             return fail(FLUIDB200_EINVAL, "mask.set must be 4-byte and mask.val 16-byte aligned");
     }
     if ((rc = check_range(g, out_lo, out_hi, sweeps, "poisson"))) return rc;
+    if (flags & POISSON_VALIDATE_ONLY) return 0;
+    const bool allow_split = !(flags & POISSON_NO_SPLIT);
     return g->dtype == FLUIDB200_F32
-               ? poisson_t<float>(g, p_in, p_out, rhs, p_edges, mask, sweeps, out_lo, out_hi, stream)
-               : poisson_t<double>(g, p_in, p_out, rhs, p_edges, mask, sweeps, out_lo, out_hi, stream);
+               ? poisson_t<float>(g, p_in, p_out, rhs, p_edges, mask, sweeps, out_lo, out_hi, stream, allow_split)
+               : poisson_t<double>(g, p_in, p_out, rhs, p_edges, mask, sweeps, out_lo, out_hi, stream, allow_split);
 }
 
 extern "C" int fluidb200_corrector(const fluidb200_slab* g, const void* p, const void* u_next,
@@ -791,7 +801,14 @@ extern "C" int fluidb200_solve(fluidb200_solver* s) {
             s->launches = before;
             if (odd) std::swap(s->f[FLUIDB200_FIELD_P], s->f[FLUIDB200_FIELD_P_NEXT]);  // undo recorded swaps
             if (rc) return rc;
-            if (rc2 != 0) return fail_backend("graph capture");
+            if (rc2 != 0) {  // the capture did not yield a graph (nothing ran): plain launches from this step on
+                s->use_graph = false;
+                for (; i < s->S; ++i) {
+                    int rc3 = one_step(s);
+                    if (rc3) return rc3;
+                }
+                return 0;
+            }
             s->graph[parity] = exec;
         }
         BE_CHECK(fbk::be_graph_launch(s->graph[parity], s->stream), "graph launch");

@@ -24,6 +24,8 @@ int be_memcpy2d_async(void* dst, size_t dpitch, const void* src, size_t spitch, 
 int be_stream_create(void** stream);
 int be_stream_destroy(void* stream);
 int be_stream_sync(void* stream);
+// Drop the helper stream a split Jacobi launch forked from `stream` (if any); be_stream_destroy does it too.
+void be_side_stream_release(void* stream);
 const char* be_last_error_string();
 // Kernels launched (or recorded into a graph capture) by the calling host thread so far: a split
 // Jacobi launch counts its three kernels. The solver handle keeps its launch count with it.

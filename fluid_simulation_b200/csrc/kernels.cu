@@ -7,6 +7,10 @@
 #include <cuda_runtime.h>
 #include <stdio.h>
 
+#include <map>
+#include <mutex>
+#include <utility>
+
 #include "backend.h"
 #include "warp_kernels.cuh"
 
@@ -126,29 +130,35 @@ inline dim3 grid_for(int nstrips, int nchunks) {
     return dim3((unsigned)((nstrips + fb::kWarpsPerCta - 1) / fb::kWarpsPerCta), (unsigned)nchunks, 1);
 }
 
-// Side stream for the GENERAL part of a split Jacobi launch: forked from and joined back into the
-// caller's stream with events, high priority so that its few, long tasks start first and run
-// underneath the FAST kernel instead of after it. One per host thread and device.
+// Side stream for the GENERAL and EDGE parts of a split Jacobi launch: forked from and joined back
+// into the caller's stream with events, high priority so that its few, long tasks start first and
+// run underneath the FAST kernel instead of after it. One per (device, caller stream): two solver
+// handles (each on its own stream) never share one, whichever host threads drive them. Created on
+// the first split launch from a stream (one cudaStreamCreateWithPriority + two cudaEventCreate);
+// be_side_stream_release() gives it back when the caller's stream goes away.
 struct SideStream {
-    int device = -1;
     cudaStream_t stream = nullptr;
     cudaEvent_t fork = nullptr, join = nullptr;
 };
-SideStream* side_stream() {
-    static thread_local SideStream table[64];
+std::mutex g_side_mutex;
+std::map<std::pair<int, cudaStream_t>, SideStream> g_side_streams;
+SideStream* side_stream(cudaStream_t caller) {
     int dev = 0;
-    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return nullptr;
-    SideStream& s = table[dev];
+    if (cudaGetDevice(&dev) != cudaSuccess) return nullptr;
+    std::lock_guard<std::mutex> lock(g_side_mutex);
+    SideStream& s = g_side_streams[std::make_pair(dev, caller)];  // (references into a std::map stay valid)
     if (!s.stream) {
         int lo = 0, hi = 0;
         cudaDeviceGetStreamPriorityRange(&lo, &hi);  // hi = numerically smallest = highest priority
         if (cudaStreamCreateWithPriority(&s.stream, cudaStreamNonBlocking, hi) != cudaSuccess ||
             cudaEventCreateWithFlags(&s.fork, cudaEventDisableTiming) != cudaSuccess ||
             cudaEventCreateWithFlags(&s.join, cudaEventDisableTiming) != cudaSuccess) {
-            s.stream = nullptr;
+            (void)cudaGetLastError();
+            if (s.stream) cudaStreamDestroy(s.stream);
+            if (s.fork) cudaEventDestroy(s.fork);
+            g_side_streams.erase(std::make_pair(dev, caller));
             return nullptr;
         }
-        s.device = dev;
     }
     return &s;
 }
@@ -157,7 +167,7 @@ template <typename T, int K> int launch_jacobi_k(const fb::JacobiArgs<T>& a, boo
     constexpr int V = fb::VecWidth<T>::V;
     // dynamic shared memory: the per-lane cp.async prefetch ring (D slots x 2 arrays x 16 B per thread)
     const size_t smem = (size_t)fb::JacobiRing<K>::D * 2 * 16 * kThreads;
-    SideStream* side = a.part != 0 ? side_stream() : nullptr;
+    SideStream* side = a.part != 0 ? side_stream(st) : nullptr;
     if (!side) {  // one kernel does every task
         fb::JacobiArgs<T> all = a;
         all.part = 0;
@@ -236,20 +246,46 @@ int be_stream_create(void** stream) {
     *stream = rc ? nullptr : (void*)s;
     return rc;
 }
-int be_stream_destroy(void* stream) { return rc_of(cudaStreamDestroy((cudaStream_t)stream)); }
+int be_stream_destroy(void* stream) {
+    be_side_stream_release(stream);
+    return rc_of(cudaStreamDestroy((cudaStream_t)stream));
+}
+void be_side_stream_release(void* stream) {
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess) return;
+    std::lock_guard<std::mutex> lock(g_side_mutex);
+    auto it = g_side_streams.find(std::make_pair(dev, (cudaStream_t)stream));
+    if (it == g_side_streams.end()) return;
+    cudaStreamSynchronize(it->second.stream);
+    cudaEventDestroy(it->second.fork);
+    cudaEventDestroy(it->second.join);
+    cudaStreamDestroy(it->second.stream);
+    g_side_streams.erase(it);
+}
 int be_stream_sync(void* stream) { return rc_of(cudaStreamSynchronize((cudaStream_t)stream)); }
 
+// A failed capture call leaves its (non-sticky) error in the runtime's per-thread slot, where the
+// next launch's cudaGetLastError() would find it: the caller falls back to plain launches, so the
+// slot is cleared here.
 int be_graph_begin(void* stream) {
-    return rc_of(cudaStreamBeginCapture((cudaStream_t)stream, cudaStreamCaptureModeThreadLocal));
+    const int rc = rc_of(cudaStreamBeginCapture((cudaStream_t)stream, cudaStreamCaptureModeThreadLocal));
+    if (rc) (void)cudaGetLastError();
+    return rc;
 }
 int be_graph_end(void* stream, void** graph_exec) {
     cudaGraph_t g = nullptr;
     *graph_exec = nullptr;
-    if (rc_of(cudaStreamEndCapture((cudaStream_t)stream, &g))) return -1;
+    if (rc_of(cudaStreamEndCapture((cudaStream_t)stream, &g))) {
+        (void)cudaGetLastError();
+        return -1;
+    }
     cudaGraphExec_t ex = nullptr;
     const int rc = rc_of(cudaGraphInstantiate(&ex, g, 0));
     cudaGraphDestroy(g);
-    if (rc) return rc;
+    if (rc) {
+        (void)cudaGetLastError();
+        return rc;
+    }
     *graph_exec = (void*)ex;
     return 0;
 }
@@ -336,9 +372,7 @@ INSTANTIATE(double)
 // any allocation of its own. For them the partner buffer lives in this module's own image:
 // a file-scope __device__ array, reserved on every GPU that loads the library, for the life of
 // the process.
-#include "../../include/fluidb200.h"
-
-#include <mutex>
+#include "internal.h"
 
 static __device__ __align__(256) unsigned char g_noalloc_scratch[FLUIDB200_NOALLOC_MAX_BYTES];
 
@@ -387,13 +421,18 @@ extern "C" int fluidb200_poisson_solve_noalloc(const fluidb200_slab* g, void* p,
                  need, (unsigned long long)FLUIDB200_NOALLOC_MAX_BYTES);
         return fluidb200_report_error(FLUIDB200_EINVAL, g_noalloc_err);
     }
-    if (sweeps == 0) return 0;
     void* scratch = nullptr;
     if (noalloc_scratch_for_current_device(&scratch)) {
         snprintf(g_noalloc_err, sizeof(g_noalloc_err), "poisson_solve_noalloc: cannot resolve the scratch symbol: %s",
                  cudaGetErrorString(g_last));
         return fluidb200_report_error(FLUIDB200_ECUDA, g_noalloc_err);
     }
+    {   // the full argument check of a launch (dtype, pitch, alignment, edges), also when sweeps == 0
+        const int rc = fbapi::poisson_sweeps(g, p, scratch, rhs, p_edges, nullptr, 1, 0, g->X, stream,
+                                             fbapi::POISSON_VALIDATE_ONLY);
+        if (rc) return rc;
+    }
+    if (sweeps == 0) return 0;
     // Split the sweeps into launches of at most 4, and into an EVEN number of launches when
     // possible, so the ping-pong ends in the caller's buffer. A single sweep ends in the scratch
     // and is copied back.
@@ -405,7 +444,9 @@ extern "C" int fluidb200_poisson_solve_noalloc(const fluidb200_slab* g, void* p,
     int left = sweeps;
     for (int i = 0; i < nl; ++i) {
         const int k = (left + (nl - i) - 1) / (nl - i);   // spread the sweeps evenly over the launches
-        const int rc = fluidb200_poisson_sweeps(g, src, dst, rhs, p_edges, nullptr, k, 0, g->X, stream);
+        // always the single-kernel form of a launch: the split form would fork onto a helper stream,
+        // which the library creates on first use -- a driver-side allocation this entry point promises not to make
+        const int rc = fbapi::poisson_sweeps(g, src, dst, rhs, p_edges, nullptr, k, 0, g->X, stream, fbapi::POISSON_NO_SPLIT);
         if (rc) return rc;
         left -= k;
         void* t = src; src = dst; dst = t;

@@ -38,6 +38,21 @@ protected:
 
     static int dtypeCode() { return sizeof(T) == 4 ? FLUIDB200_F32 : FLUIDB200_F64; }
     void note(int rc) { if (rc != 0) last_error = rc; }
+    // setBoxDimenension (NavierStokesSolver.h:31) is a base-class method that knows nothing of the
+    // device: the reference's CUDA class keeps its old d_cells after a resize. Here every device
+    // call first checks that the handle still has the host grid's dimensions and re-creates it
+    // (pristine, zero-filled, no flags -- what a newly constructed solver holds) when it does not.
+    void ensureHandle() {
+        fluidb200_slab g;
+        if (handle && fluidb200_get_slab(handle, &g) == 0 && g.X == this->box_dimension_x && g.Y == this->box_dimension_y)
+            return;
+        if (handle) fluidb200_destroy(handle);
+        handle = nullptr;
+        note(fluidb200_create(&handle, dtypeCode(), this->box_dimension_x, this->box_dimension_y,
+                              (double)this->domain_size_x, (double)this->domain_size_y));
+        if (handle && sweeps_per_launch > 0) note(fluidb200_set_sweeps_per_launch(handle, sweeps_per_launch));
+    }
+    int sweeps_per_launch = 0;  // 0 = the library's choice by grid size
     void pushParams() {
         note(fluidb200_set_domain(handle, (double)this->domain_size_x, (double)this->domain_size_y));
         note(fluidb200_set_params(handle, (double)this->time_step, (double)this->kinematic_viscosity,
@@ -56,6 +71,7 @@ public:
     ParallelNavierStokes& operator=(const ParallelNavierStokes&) = delete;
 
     void migrateHostToDevice() {
+        ensureHandle();
         const int X = this->box_dimension_x, Y = this->box_dimension_y;
         const void* fields[FLUIDB200_NUM_FIELDS];
         const void* bcv[3];
@@ -93,6 +109,7 @@ public:
     }
 
     void migrateDeviceToHost() {
+        ensureHandle();
 #ifdef NAVIERSTOKESCELL_H
         const int X = this->box_dimension_x, Y = this->box_dimension_y;
         const std::size_t n = (std::size_t)X * Y;
@@ -117,6 +134,7 @@ public:
 
     // asynchronous, like the reference (:269-288); callers synchronise (cuda_main.cu:98) or migrate
     void solve() {
+        ensureHandle();
         pushParams();
         note(fluidb200_solve(handle));
     }
@@ -128,10 +146,10 @@ public:
 
     // additions (not in the reference)
     void synchronize() { note(fluidb200_synchronize(handle)); }
-    void uploadCavity(T lid_velocity) { note(fluidb200_upload_cavity(handle, (double)lid_velocity)); }
+    void uploadCavity(T lid_velocity) { ensureHandle(); note(fluidb200_upload_cavity(handle, (double)lid_velocity)); }
     int lastError() const { return last_error; }
     const char* lastErrorMessage() const { return fluidb200_last_error(); }
-    fluidb200_solver* nativeHandle() { return handle; }
+    fluidb200_solver* nativeHandle() { ensureHandle(); return handle; }
 };
 
 // explicit instantiation allows float and double precision types (ParallelNavierStokes.cuh:50-51)

@@ -16,6 +16,7 @@ class TiledNavierStokes : public ParallelNavierStokes<T> {
 public:
     TiledNavierStokes(int box_dim_x, int box_dim_y, T dom_x, T dom_y)
         : ParallelNavierStokes<T>(box_dim_x, box_dim_y, dom_x, dom_y) {
+        this->sweeps_per_launch = 6;
         this->note(fluidb200_set_sweeps_per_launch(this->handle, 6));
     }
     ~TiledNavierStokes() {}

@@ -149,7 +149,11 @@ int fluidb200_predictor(const fluidb200_slab* g, const void* u, const void* v, v
  * range touches them). Needs p_in on rows [out_lo-sweeps, out_hi+sweeps) and rhs on rows
  * [out_lo-sweeps+1, out_hi+sweeps-1), both clipped to the box; the range must be present
  * locally. `mask` (may be NULL) enables interior pressure flags (SerialNavierStokes.cpp:154-160),
- * applied at every one of the `sweeps` levels; masked launches always use the general kernel. */
+ * applied at every one of the `sweeps` levels. A masked launch runs the general kernel on every
+ * task unless mask->tiles is given (see fluidb200_mask).
+ * Large launches are split over the caller's stream and a high-priority helper stream the library
+ * keeps per (device, caller stream); the first such launch from a stream creates it (one stream,
+ * two events), so make that first call outside any stream capture. */
 int fluidb200_poisson_sweeps(const fluidb200_slab* g, const void* p_in, void* p_out,
                              const void* rhs, const fluidb200_edges* p_edges,
                              const fluidb200_mask* mask, int sweeps, int out_lo, int out_hi,
@@ -183,9 +187,11 @@ int fluidb200_corrector(const fluidb200_slab* g, const void* p, const void* u_ne
  *   - Limit: g->rows * g->pitch * sizeof(T) must not exceed FLUIDB200_NOALLOC_MAX_BYTES (16 MiB: a
  *     2048 x 2048 fp32 or 2048 x 1024 fp64 grid). Larger grids are refused with FLUIDB200_EINVAL
  *     and a message that says so; use fluidb200_poisson_sweeps with a buffer of your own.
- *   - The function calls no cudaMalloc / cudaFree and no routine that allocates. The first call on
- *     each device looks the array's device address up (one cudaGetSymbolAddress, with that device
- *     current) and caches it; make that first call outside any stream capture.
+ *   - The function calls no cudaMalloc / cudaFree and no routine that allocates, and creates no
+ *     stream or event: every launch takes the single-kernel form (never the split form of
+ *     fluidb200_poisson_sweeps, whose first use on a stream creates a helper stream). The first call
+ *     on each device looks the array's device address up (one cudaGetSymbolAddress, with that
+ *     device current) and caches it; make that first call outside any stream capture.
  *   - One array serves every call on a device and is not cleared between calls. Nothing needs to
  *     start at zero: each launch writes every cell that a later launch of the same call reads for
  *     a result, so leftovers of an earlier call (even of another grid size) cannot reach `p`.

@@ -103,6 +103,10 @@ int main(int argc, char** argv) {
     OracleRun unit_solver(num_x_bins, num_y_bins);
     ParallelNavierStokes<float> tested_solver(num_x_bins, num_y_bins, width, height);
     TiledNavierStokes<float> tiled_solver(num_x_bins, num_y_bins, width, height);
+    // constructed with another shape, then resized through the base-class method
+    // (NavierStokesSolver.h:31): the device state must follow
+    ParallelNavierStokes<float> resized_solver(20, 30, width, height);
+    if (resized_solver.setBoxDimenension(num_x_bins, num_y_bins) != 0) { std::cerr << "resize failed" << std::endl; return 4; }
 
     tested_solver.density = 1.0;
     tested_solver.kinematic_viscosity = 0.1;
@@ -115,10 +119,16 @@ int main(int argc, char** argv) {
     tiled_solver.num_iterations = tested_solver.num_iterations;
     tiled_solver.num_poisson_iterations = tested_solver.num_poisson_iterations;
     tiled_solver.time_step = tested_solver.time_step;
+    resized_solver.density = tested_solver.density;
+    resized_solver.kinematic_viscosity = tested_solver.kinematic_viscosity;
+    resized_solver.num_iterations = tested_solver.num_iterations;
+    resized_solver.num_poisson_iterations = tested_solver.num_poisson_iterations;
+    resized_solver.time_step = tested_solver.time_step;
 
     cavity(unit_solver, num_x_bins, num_y_bins);
     cavity(tested_solver, num_x_bins, num_y_bins);
     cavity(tiled_solver, num_x_bins, num_y_bins);
+    cavity(resized_solver, num_x_bins, num_y_bins);
 
     OracleStateF32& st = unit_solver.st;
     st.X = num_x_bins; st.Y = num_y_bins;
@@ -133,11 +143,13 @@ int main(int argc, char** argv) {
     oracle_solve(&st);
     tested_solver.migrateSolve();
     tiled_solver.migrateSolve();
-    if (tested_solver.lastError() || tiled_solver.lastError()) {
+    resized_solver.migrateSolve();
+    if (tested_solver.lastError() || tiled_solver.lastError() || resized_solver.lastError()) {
         std::cerr << "fluidb200 error: " << tested_solver.lastErrorMessage() << std::endl;
         return 3;
     }
     int errors = compare("ParallelNavierStokes<float>", tested_solver, unit_solver, num_x_bins, num_y_bins, true);
     errors += compare("TiledNavierStokes<float>", tiled_solver, unit_solver, num_x_bins, num_y_bins, true);
+    errors += compare("ParallelNavierStokes<float> after setBoxDimenension", resized_solver, unit_solver, num_x_bins, num_y_bins, true);
     return errors == 0 ? 0 : 1;
 }

@@ -118,6 +118,7 @@ int be_memcpy2d_async(void* d, size_t dp, const void* s, size_t sp, size_t w, si
 int be_stream_create(void** s) { *s = nullptr; return 0; }
 int be_stream_destroy(void*) { return 0; }
 int be_stream_sync(void*) { return 0; }
+void be_side_stream_release(void*) {}
 int be_graph_begin(void*) { return -1; }
 int be_graph_end(void*, void**) { return -1; }
 int be_graph_launch(void*, void*) { return -1; }

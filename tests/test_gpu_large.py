@@ -136,3 +136,48 @@ def test_random_shapes_gpu(Solver, X, Y, K, kmax):
     o.solve()
     H.compare_with(s, o, tag=f"random/{X}x{Y}/K{K}/k{kmax}")
     s.close()
+
+
+@pytest.mark.parametrize("N,divmode", [(4096, None), (2048, "1")])
+def test_bench_configuration_against_the_oracle(Solver, N, divmode):
+    """The code path bench.py times, checked against the oracle instead of against itself: unit spacing
+    (domain (N-1) x (N-1), so hx = hy = 1: the power-of-two arithmetic mode, right-hand-side scaling
+    skipped), dt = 0.001, K = 100 sweeps spread over 13 launches (9 of depth 8, 4 of depth 7), the
+    wave-aligned chunk plan of a large grid, one timestep, all seven fields bit-equal. 4096^2 is the
+    largest grid the serial oracle finishes in about a minute; the second case forces the general
+    division-free arithmetic (FLUIDB200_DIVMODE=1) on the same path."""
+    import os
+    saved = os.environ.get("FLUIDB200_DIVMODE")
+    if divmode is not None:
+        os.environ["FLUIDB200_DIVMODE"] = divmode
+    try:
+        s = Solver(N, N, float(N - 1), float(N - 1)).set_cavity(1.0)
+        s.time_step, s.num_iterations, s.num_poisson_iterations = 0.001, 1, 100
+        s.set_sweeps_per_launch(8)
+        s.migrateSolve()
+        assert s.launch_count() >= 2 + 13
+    finally:
+        if saved is None:
+            os.environ.pop("FLUIDB200_DIVMODE", None)
+        else:
+            os.environ["FLUIDB200_DIVMODE"] = saved
+    o = Oracle(N, N, float(N - 1), float(N - 1)).set_cavity(1.0)
+    assert o.hx == 1.0 and o.hy == 1.0
+    o.time_step, o.num_iterations, o.num_poisson_iterations = 0.001, 1, 100
+    o.solve()
+    H.compare_with(s, o, tag=f"bench-path/{N}/divmode{divmode}")
+    s.close()
+
+
+def test_solve_on_a_stream_that_cannot_be_captured(Solver, golden):
+    """Small grids replay their timesteps as CUDA graphs. The legacy default stream (NULL) cannot be
+    captured: solve() must fall back to plain launches without tripping over the failed capture's
+    error code, and give the same bits."""
+    from fluid_simulation_b200 import _lib
+    rec = dict(golden["cavity41_S10_K50"])
+    s = H.golden_case_setup(rec, Solver)
+    s.set_use_graph(True)
+    _lib.check(s._lib, s._lib.fluidb200_set_stream(s._h, None))
+    s.migrateSolve()
+    H.compare_with(s, H.load_fields(golden["cavity41_S10_K50"]), tag="legacy-stream")
+    s.close()
