@@ -71,6 +71,8 @@ _SIGS = {
     "fluidb200_set_sweeps_per_launch": (C.c_int, [C.c_void_p, C.c_int]),
     "fluidb200_set_use_graph": (C.c_int, [C.c_void_p, C.c_int]),
     "fluidb200_launch_count": (C.c_int64, [C.c_void_p]),
+    "fluidb200_set_resident": (C.c_int, [C.c_void_p, C.c_int]),
+    "fluidb200_resident_launch_count": (C.c_int64, [C.c_void_p]),
     "fluidb200_set_device": (C.c_int, [C.c_int]),
     "fluidb200_last_error": (C.c_char_p, []),
     "fluidb200_report_error": (C.c_int, [C.c_int, C.c_char_p]),

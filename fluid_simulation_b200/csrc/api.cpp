@@ -428,6 +428,12 @@ struct fluidb200_solver {
     double graph_key[6] = {};
     void* graph_home_p = nullptr;     // where p lived when graph[0] was captured
     int64_t launches = 0;
+    // resident solver for small grids (resident_kernels.cuh)
+    int resident = -1;                // -1: by FLUIDB200_RESIDENT (default on), 0 / 1: fluidb200_set_resident
+    bool res_planned = false, res_ok = false;
+    fb::ResidentPlan res_plan = {};
+    void* res_scratch = nullptr;      // device: tile counters + 4 values for the corner rule
+    int64_t resident_launches = 0;
 };
 
 namespace {
@@ -619,6 +625,103 @@ int one_step(fluidb200_solver* s) {
     return step_corrector(s);
 }
 
+// ---- resident solver: whole timesteps of a small grid in one cooperative launch -----------------
+// Tiling: a thread owns R rows x 16 bytes, a warp 32 such patches side by side, a CTA wx x wy warps,
+// the grid tiles_x x tiles_y CTAs, at most one per SM (they wait for each other). A sweep costs about
+// R rows of arithmetic per warp, times the warps sharing a scheduler, plus -- once tiles exist -- a
+// round trip through L2 to the neighbouring tile, which is worth roughly 1000 cycles: so a grid that
+// fits one CTA stays in one CTA, and a larger one spreads as widely as it can.
+template <typename T> bool plan_resident(int X, int Y, fb::ResidentPlan* out) {
+    const int V = 16 / (int)sizeof(T), W = 32 * V;
+    const int nsm = fbk::be_sm_count();
+    const int ncw = (Y + W - 1) / W;
+    const int fR = env_int("FLUIDB200_RESIDENT_R", 0), fwy = env_int("FLUIDB200_RESIDENT_WY", 0),
+              fwx = env_int("FLUIDB200_RESIDENT_WX", 0);   // (measurement knobs)
+    double best = 1e300;
+    bool found = false;
+    const int Rs[3] = {8, 4, 2};
+    for (int R : Rs) {
+        if (fR && R != fR) continue;
+        const int maxw = fbk::be_resident_max_threads(R) / 32;
+        if (maxw <= 0) continue;
+        const int nrw = (X + R - 1) / R;
+        for (int wy = 1; wy <= std::min(ncw, maxw); ++wy) {
+            if (fwy && wy != fwy) continue;
+            const int ty = (ncw + wy - 1) / wy;
+            for (int wx = 1; wx * wy <= maxw && wx <= nrw; ++wx) {
+                if (fwx && wx != fwx) continue;
+                const int tx = (nrw + wx - 1) / wx;
+                if ((long long)ty * tx > nsm) continue;
+                const size_t smem = fb::resident_smem_bytes<T>(R, wy, wx);
+                if (smem > 220u * 1024u) continue;
+                const int warps = wx * wy;
+                const double cost = R * ((warps + 3) / 4) * 30.0 + (ty * tx > 1 ? 1000.0 : 0.0);
+                if (cost < best) {   // (ties keep the taller patch: fewer rows cross shared memory per sweep)
+                    best = cost;
+                    found = true;
+                    out->R = R; out->wy = wy; out->wx = wx; out->tiles_y = ty; out->tiles_x = tx;
+                    out->threads = warps * 32; out->smem = smem;
+                }
+            }
+        }
+    }
+    return found;
+}
+
+bool resident_wanted(const fluidb200_solver* s) {
+    const int on = s->resident >= 0 ? s->resident : env_int("FLUIDB200_RESIDENT", 1);
+    if (!on) return false;
+    if ((long long)s->S * s->K < 2) return false;   // the corner rule needs a sweep before the last one
+    for (int f = 0; f < 3; ++f)
+        if (s->mask[f].set) return false;
+    for (int e = 0; e < 4; ++e) {
+        if (s->edges[0].mode[e] != FLUIDB200_EDGE_CONST || s->edges[1].mode[e] != FLUIDB200_EDGE_CONST) return false;
+        if (s->edges[2].mode[e] == FLUIDB200_EDGE_ARRAY) return false;
+    }
+    return true;
+}
+
+template <typename T> int solve_resident_t(fluidb200_solver* s, bool* done) {
+    *done = false;
+    if (!s->res_planned) {
+        s->res_planned = true;
+        s->res_ok = fbk::be_resident_max_threads(2) > 0 && plan_resident<T>(s->X, s->Y, &s->res_plan) &&
+                    fbk::resident_capacity<T>(s->res_plan) >= s->res_plan.tiles_x * s->res_plan.tiles_y;
+        if (s->res_ok) {
+            const size_t words = fb::resident_sync_words(s->res_plan.tiles_x * s->res_plan.tiles_y);
+            if (fbk::be_malloc(&s->res_scratch, words * sizeof(unsigned) + 64) != 0) s->res_ok = false;
+        }
+    }
+    if (!s->res_ok) return 0;
+    const fb::ResidentPlan& pl = s->res_plan;
+    fb::ResidentArgs<T> a = {};
+    for (int i = 0; i < FLUIDB200_NUM_FIELDS; ++i) a.f[i] = (T*)s->f[i];
+    a.pitch = s->pitch; a.X = s->X; a.Y = s->Y;
+    a.pa.m = fb::make_metric<T>((T)s->hx, (T)s->hy, env_int("FLUIDB200_DIVMODE", -1));
+    a.pa.nu = (T)s->nu; a.pa.dt = (T)s->dt;
+    a.pa.rho_over_dt = (T)s->rho / (T)s->dt;   // SerialNavierStokes.cpp:332
+    a.ca.m = a.pa.m;
+    a.ca.dt_over_rho = (T)s->dt / (T)s->rho;   // :346
+    a.hx = (T)s->hx; a.hy = (T)s->hy;
+    a.K = s->K; a.S = s->S;
+    a.wy = pl.wy; a.wx = pl.wx; a.tiles_y = pl.tiles_y; a.tiles_x = pl.tiles_x;
+    for (int e = 0; e < 4; ++e) {
+        a.pmode[e] = s->edges[2].mode[e];
+        a.pval[e] = (T)s->edges[2].cval[e];
+        a.uval[e] = (T)s->edges[0].cval[e];
+        a.vval[e] = (T)s->edges[1].cval[e];
+    }
+    const size_t words = fb::resident_sync_words(pl.tiles_x * pl.tiles_y);
+    a.sync = (unsigned*)s->res_scratch;
+    a.stash = (T*)((char*)s->res_scratch + words * sizeof(unsigned));
+    BE_CHECK(fbk::launch_resident<T>(a, pl, s->stream), "resident launch");
+    s->launches += 1;
+    s->resident_launches += 1;
+    s->p_next_is_p = true;
+    *done = true;
+    return 0;
+}
+
 int launches_per_step(const fluidb200_solver* s) {
     const int kmax = poisson_kmax(s);
     return 2 + (s->K + kmax - 1) / kmax;
@@ -679,6 +782,7 @@ extern "C" int fluidb200_destroy(fluidb200_solver* s) {
     for (int f = 0; f < 3; ++f) free_bc(s, f);
     for (int i = 0; i < FLUIDB200_NUM_FIELDS; ++i)
         if (s->f[i]) fbk::be_free(s->f[i]);
+    if (s->res_scratch) fbk::be_free(s->res_scratch);
     if (s->own_stream && s->stream) fbk::be_stream_destroy(s->stream);
     delete s;
     return 0;
@@ -765,6 +869,12 @@ extern "C" int fluidb200_step_corrector(fluidb200_solver* s) {
 extern "C" int fluidb200_solve(fluidb200_solver* s) {
     if (!s) return fail(FLUIDB200_EINVAL, "solver is NULL");
     if (s->S == 0) return 0;
+    if (!(s->dt != 0) || !(s->rho != 0)) return fail(FLUIDB200_EINVAL, "time_step and density must be non-zero");
+    if (resident_wanted(s)) {   // small grid, cavity-style boundaries: every timestep in ONE launch
+        bool done = false;
+        const int rc = s->dtype == FLUIDB200_F32 ? solve_resident_t<float>(s, &done) : solve_resident_t<double>(s, &done);
+        if (rc || done) return rc;
+    }
     if (!s->use_graph) {
         for (int i = 0; i < s->S; ++i) {
             int rc = one_step(s);
@@ -872,6 +982,12 @@ extern "C" int fluidb200_set_use_graph(fluidb200_solver* s, int enable) {
     if (!enable) drop_graphs(s);
     return 0;
 }
+extern "C" int fluidb200_set_resident(fluidb200_solver* s, int enable) {
+    if (!s) return fail(FLUIDB200_EINVAL, "solver is NULL");
+    s->resident = enable < 0 ? -1 : (enable != 0);
+    return 0;
+}
+extern "C" int64_t fluidb200_resident_launch_count(const fluidb200_solver* s) { return s ? s->resident_launches : 0; }
 extern "C" int64_t fluidb200_launch_count(const fluidb200_solver* s) { return s ? s->launches : 0; }
 
 extern "C" int fluidb200_set_device(int device) {

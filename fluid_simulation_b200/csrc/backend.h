@@ -44,4 +44,12 @@ template <typename T> int launch_corrector(const fb::CorrectorArgs<T>& a, bool m
 template <typename T>
 int launch_init_cavity(T* const fields[7], long long pitch, int X, int Y, int row0, int rows, T lid, void* stream);
 
+
+// Resident solver for small grids (resident_kernels.cuh). be_resident_max_threads: threads per CTA the
+// kernel with patch height R may be launched with (0: no such kernel, or no resident kernels at all in
+// this backend); resident_capacity: CTAs of that plan that can be co-resident on the current device.
+int be_resident_max_threads(int R);
+template <typename T> int resident_capacity(const fb::ResidentPlan& plan);
+template <typename T> int launch_resident(const fb::ResidentArgs<T>& a, const fb::ResidentPlan& plan, void* stream);
+
 }  // namespace fbk

@@ -13,6 +13,7 @@
 
 #include "backend.h"
 #include "warp_kernels.cuh"
+#include "resident_kernels.cuh"
 
 namespace {
 
@@ -108,6 +109,25 @@ __global__ void __launch_bounds__(kThreads, 4) corrector_kernel(const __grid_con
     const int strip = blockIdx.x * fb::kWarpsPerCta + (threadIdx.x >> 5);
     if (strip >= A.g.nstrips) return;
     fb::corrector_task<T, V, MASK, MODE>(A, strip, blockIdx.y, threadIdx.x & 31);
+}
+
+// Whole timesteps of a small grid in one cooperative launch (resident_kernels.cuh). One CTA per SM;
+// the patch height R fixes how many threads the registers allow.
+constexpr int resident_max_threads(int R) { return R <= 2 ? 768 : R <= 4 ? 512 : 256; }
+template <typename T, int V, int R>
+__global__ void __launch_bounds__(resident_max_threads(R), 1) resident_kernel(const __grid_constant__ fb::ResidentArgs<T> A) {
+    fb::resident_body<T, V, R>(A);
+}
+template <typename T, int R> void (*resident_entry())(fb::ResidentArgs<T>) {
+    return resident_kernel<T, fb::VecWidth<T>::V, R>;
+}
+template <typename T> void (*resident_entry_r(int R))(fb::ResidentArgs<T>) {
+    switch (R) {
+        case 2: return resident_entry<T, 2>();
+        case 4: return resident_entry<T, 4>();
+        case 8: return resident_entry<T, 8>();
+        default: return nullptr;
+    }
 }
 
 template <typename T> struct FieldPtrs {
@@ -351,11 +371,50 @@ int launch_init_cavity(T* const fields[7], long long pitch, int X, int Y, int ro
     return rc_of(cudaGetLastError());
 }
 
+int be_resident_max_threads(int R) { return (R == 2 || R == 4 || R == 8) ? resident_max_threads(R) : 0; }
+
+// CTAs of the resident kernel that can be co-resident on the current device (0: not launchable)
+template <typename T> int resident_capacity(const fb::ResidentPlan& pl) {
+    auto kern = resident_entry_r<T>(pl.R);
+    if (!kern || pl.threads > resident_max_threads(pl.R)) return 0;
+    int dev = 0, coop = 0, max_optin = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess) return 0;
+    cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, dev);
+    cudaDeviceGetAttribute(&max_optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev);
+    if (!coop || pl.smem > (size_t)max_optin) return 0;
+    if (cudaFuncSetAttribute((const void*)kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl.smem) != cudaSuccess) {
+        (void)cudaGetLastError();
+        return 0;
+    }
+    int per_sm = 0;
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, (const void*)kern, pl.threads, pl.smem) != cudaSuccess) {
+        (void)cudaGetLastError();
+        return 0;
+    }
+    return per_sm * be_sm_count();
+}
+template <typename T> int launch_resident(const fb::ResidentArgs<T>& a, const fb::ResidentPlan& pl, void* stream) {
+    auto kern = resident_entry_r<T>(pl.R);
+    if (!kern) { g_last = cudaErrorInvalidValue; return -1; }
+    cudaStream_t st = (cudaStream_t)stream;
+    const int ntiles = pl.tiles_x * pl.tiles_y;
+    if (rc_of(cudaMemsetAsync(a.sync, 0, fb::resident_sync_words(ntiles) * sizeof(unsigned), st))) return -1;
+    if (rc_of(cudaFuncSetAttribute((const void*)kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl.smem))) return -1;
+    fb::ResidentArgs<T> args = a;
+    void* params[1] = {(void*)&args};
+    if (rc_of(cudaLaunchCooperativeKernel((const void*)kern, dim3((unsigned)ntiles), dim3((unsigned)pl.threads), params, pl.smem, st)))
+        return -1;
+    ++g_kernels;
+    return 0;
+}
+
 #define INSTANTIATE(T)                                                                                   \
     template int launch_jacobi<T>(const fb::JacobiArgs<T>&, int, bool, int, void*);                     \
     template int launch_predictor<T>(const fb::PredictorArgs<T>&, int, void*);                          \
     template int launch_corrector<T>(const fb::CorrectorArgs<T>&, bool, int, void*);                    \
-    template int launch_init_cavity<T>(T* const[7], long long, int, int, int, int, T, void*);
+    template int launch_init_cavity<T>(T* const[7], long long, int, int, int, int, T, void*);       \
+    template int resident_capacity<T>(const fb::ResidentPlan&);                                          \
+    template int launch_resident<T>(const fb::ResidentArgs<T>&, const fb::ResidentPlan&, void*);
 INSTANTIATE(float)
 INSTANTIATE(double)
 

@@ -213,3 +213,42 @@ template <typename T> struct CorrectorArgs {
 };
 
 }  // namespace fb
+
+// ---------------------------------------------------------------------------------------
+// Resident solver (resident_kernels.cuh): whole timesteps of a SMALL grid in one cooperative
+// launch, the pressure field living in registers, one patch of R rows x 16 bytes per thread.
+// ---------------------------------------------------------------------------------------
+namespace fb {
+
+template <typename T> struct ResidentArgs {
+    T* f[7];                  // u, v, p, u_next, v_next, p_next, rhs (device, pitched, whole grid)
+    long long pitch;
+    int X, Y;
+    PredictorArgs<T> pa;      // m, nu, dt, rho_over_dt are used
+    CorrectorArgs<T> ca;      // m, dt_over_rho are used
+    T hx, hy;
+    int K, S;                 // sweeps per step, steps in this launch (K * S >= 2)
+    int wy, wx;               // warps of a CTA along y and along x
+    int tiles_y, tiles_x;     // CTAs along y and along x; tile = blockIdx.x = ty + tiles_y * tx
+    int pmode[4];             // pressure edges: EDGE_UNSET or EDGE_CONST
+    T pval[4];
+    T uval[4], vval[4];       // velocity edges: all EDGE_CONST
+    unsigned* sync;           // zeroed before the launch: [0] grid barrier, [32 * (1 + tile)] rows published by a tile
+    T* stash;                 // 4 values for the stale-corner rule
+};
+
+struct ResidentPlan {
+    int R, wy, wx, tiles_y, tiles_x, threads;
+    size_t smem;
+};
+constexpr int kResidentRowHalo = 2;  // rows of u, v kept around a tile: u_next at x +- 1 of the rhs stencil
+constexpr int kResidentColHalo = 4;  // columns: 2 are needed, 4 keep a lane's 16 bytes aligned inside the frame
+template <typename T> inline size_t resident_smem_bytes(int R, int wy, int wx) {
+    const int W = 32 * (16 / (int)sizeof(T));
+    const size_t FR = (size_t)wx * R + 2 * kResidentRowHalo, FP = (size_t)wy * W + 2 * kResidentColHalo;
+    const size_t nwarps = (size_t)wy * wx;
+    return (4 * FR * FP + 2 * nwarps * 2 * W + 2 * nwarps * 2 * R) * sizeof(T);
+}
+inline size_t resident_sync_words(int ntiles) { return 32 * (size_t)(1 + ntiles); }
+
+}  // namespace fb

@@ -461,12 +461,12 @@ FB_DEV float2 fsub2(float2 a, float2 b) {  // two correctly rounded differences 
 #endif
 
 // One Jacobi update of a row strip: out = ((b - (((xm + xp) + yp) + ym)) * -0.25
-// (SerialNavierStokes.cpp:144-146, operand order kept).
+// (SerialNavierStokes.cpp:144-146, operand order kept). ym / yp: the y-neighbours of every element.
 template <typename T, int V>
-FB_DEV Vec<T, V> jacobi_row(const Vec<T, V>& xm, const Vec<T, V>& c, const Vec<T, V>& xp, const Vec<T, V>& b) {
+FB_DEV Vec<T, V> jacobi_row_yn(const Vec<T, V>& xm, const Vec<T, V>& xp, const Vec<T, V>& ym, const Vec<T, V>& yp,
+                               const Vec<T, V>& b) {
     using A_ = Ar<T>;
-    Vec<T, V> ym, yp, out;
-    y_neighbours<T, V>(c, ym, yp);
+    Vec<T, V> out;
 #if !defined(FLUIDB200_NO_PACKED_F32X2) && !defined(FLUIDB200_HOST_EMU)
     if constexpr (sizeof(T) == 4 && V == 4) {
         // sm_100 packed fp32: one FADD2 rounds two independent sums exactly like two FADDs. Only the
@@ -492,6 +492,12 @@ FB_DEV Vec<T, V> jacobi_row(const Vec<T, V>& xm, const Vec<T, V>& c, const Vec<T
         out.a[e] = A_::neg_quarter(A_::sub(b.a[e], s));
     }
     return out;
+}
+template <typename T, int V>
+FB_DEV Vec<T, V> jacobi_row(const Vec<T, V>& xm, const Vec<T, V>& c, const Vec<T, V>& xp, const Vec<T, V>& b) {
+    Vec<T, V> ym, yp;
+    y_neighbours<T, V>(c, ym, yp);
+    return jacobi_row_yn<T, V>(xm, xp, ym, yp, b);
 }
 
 // Pipeline: at step r the warp loads row r of p (level 0) and level t = 1..K produces row r-t

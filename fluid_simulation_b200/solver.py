@@ -195,6 +195,13 @@ class ParallelNavierStokes:
     def set_use_graph(self, enable=True):
         _lib.check(self._lib, self._lib.fluidb200_set_use_graph(self._h, int(bool(enable))))
 
+    def set_resident(self, enable=True):
+        """Small grids with cavity-style boundaries: run solve() as one cooperative launch (default on)."""
+        _lib.check(self._lib, self._lib.fluidb200_set_resident(self._h, -1 if enable is None else int(bool(enable))))
+
+    def resident_launch_count(self):
+        return int(self._lib.fluidb200_resident_launch_count(self._h))
+
     def launch_count(self):
         return int(self._lib.fluidb200_launch_count(self._h))
 

@@ -265,6 +265,13 @@ void* fluidb200_field_ptr(fluidb200_solver* s, int field);        /* device poin
 int fluidb200_set_stream(fluidb200_solver* s, void* stream);       /* default: own stream       */
 int fluidb200_set_sweeps_per_launch(fluidb200_solver* s, int k);   /* temporal-blocking depth   */
 int fluidb200_set_use_graph(fluidb200_solver* s, int enable);      /* replay steps as CUDA graph */
+/* solve() on a small grid (up to about 1.2 M cells fp32) whose boundaries are the cavity's kind (every
+ * velocity edge one constant, every pressure edge unset or one constant, no interior flags) runs all
+ * num_iterations timesteps in ONE cooperative launch with the pressure held in registers, instead of
+ * the 4 + 3K launches per step of fluid_cpp/cuda/ParallelNavierStokes.cu:269-288. Same bits either way.
+ * enable: 1 / 0, or -1 for the default (on; FLUIDB200_RESIDENT=0 turns it off). */
+int fluidb200_set_resident(fluidb200_solver* s, int enable);
+int64_t fluidb200_resident_launch_count(const fluidb200_solver* s); /* solve() calls that took that path */
 /* Kernels launched by this solver since creation (for bench.py's gpu_launches). */
 int64_t fluidb200_launch_count(const fluidb200_solver* s);         /* kernels launched so far (a split Jacobi launch = 3) */
 

@@ -216,11 +216,17 @@ int launch_init_cavity(T* const f[7], long long pitch, int, int Y, int, int rows
     }
     return 0;
 }
+// the resident (cooperative, shared-memory) kernels are not emulated: the host logic never selects them here
+int be_resident_max_threads(int) { return 0; }
+template <typename T> int resident_capacity(const fb::ResidentPlan&) { return 0; }
+template <typename T> int launch_resident(const fb::ResidentArgs<T>&, const fb::ResidentPlan&, void*) { return -1; }
 #define INSTANTIATE(T)                                                                \
     template int launch_jacobi<T>(const fb::JacobiArgs<T>&, int, bool, int, void*);  \
     template int launch_predictor<T>(const fb::PredictorArgs<T>&, int, void*);       \
     template int launch_corrector<T>(const fb::CorrectorArgs<T>&, bool, int, void*); \
-    template int launch_init_cavity<T>(T* const[7], long long, int, int, int, int, T, void*);
+    template int launch_init_cavity<T>(T* const[7], long long, int, int, int, int, T, void*); \
+    template int resident_capacity<T>(const fb::ResidentPlan&);                      \
+    template int launch_resident<T>(const fb::ResidentArgs<T>&, const fb::ResidentPlan&, void*);
 INSTANTIATE(float)
 INSTANTIATE(double)
 }  // namespace fbk

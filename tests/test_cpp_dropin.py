@@ -16,6 +16,11 @@ import pytest
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
 
+def _default_env():
+    """The C++ programs run the library as a user gets it, without the suite's path-forcing knobs."""
+    return {k: v for k, v in os.environ.items() if not k.startswith("FLUIDB200_")}
+
+
 def test_shim_headers_compile_standalone():
     """CPU: the shim is plain C++ -- it must compile and link without nvcc and without the reference."""
     import __graft_entry__ as g
@@ -31,7 +36,7 @@ def test_cpp_parity_program():
         import __graft_entry__ as g
         g.build_cpp_tests()
     r = subprocess.run([exe, os.path.join(ROOT, "oracle", "liboracle.so")], capture_output=True, text=True, cwd=ROOT,
-                       timeout=300)
+                       timeout=300, env=_default_env())
     assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
     assert r.stdout.count("Passed 100% cells") == 9, r.stdout
 
@@ -41,7 +46,7 @@ def test_reference_own_test_main_runs_unmodified_against_the_shim():
     exe = os.path.join(ROOT, "oracle", "_ref", "ref_test_main")
     if not os.path.exists(exe):
         pytest.skip("oracle/_ref/ref_test_main not built (needs /root/reference at build time)")
-    r = subprocess.run([exe], capture_output=True, text=True, cwd=ROOT, timeout=300)
+    r = subprocess.run([exe], capture_output=True, text=True, cwd=ROOT, timeout=300, env=_default_env())
     assert r.returncode == 0
     assert "FAILURE" not in r.stdout
     assert r.stdout.count("SUCCESS") == 41 * 41

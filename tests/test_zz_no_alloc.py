@@ -57,7 +57,7 @@ def _run_case(lib, _lib, torch, X, Y, sweeps, dtype, seed):
     # expected (2): the CPU oracle's sweeps on the same data (the reference's arithmetic, not CUDA against CUDA)
     o = Oracle(X, Y, 1.0, 1.0, npdt)
     assert o.hx == hx and o.hy == hy
-    o.p[:] = p0; o.rhs[:] = rhs
+    o.p[:] = p0; o.p_next[:] = p0; o.rhs[:] = rhs    # (the reference has p_next == p between sweeps)
     o.p_bc[:, Y - 1] = 0.0; o.p_set[:, Y - 1] = 1      # the cavity's pressure edges: lid Dirichlet 0, rest copy
     o.poisson_sweeps(sweeps)
     view = np.uint32 if npdt == np.float32 else np.uint64
