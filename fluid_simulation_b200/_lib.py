@@ -73,6 +73,7 @@ _SIGS = {
     "fluidb200_launch_count": (C.c_int64, [C.c_void_p]),
     "fluidb200_set_resident": (C.c_int, [C.c_void_p, C.c_int]),
     "fluidb200_resident_launch_count": (C.c_int64, [C.c_void_p]),
+    "fluidb200_resident_profile": (C.c_int, [C.c_void_p, C.POINTER(C.c_uint64)]),
     "fluidb200_set_device": (C.c_int, [C.c_int]),
     "fluidb200_last_error": (C.c_char_p, []),
     "fluidb200_report_error": (C.c_int, [C.c_int, C.c_char_p]),

@@ -639,7 +639,7 @@ template <typename T> bool plan_resident(int X, int Y, fb::ResidentPlan* out) {
               fwx = env_int("FLUIDB200_RESIDENT_WX", 0);   // (measurement knobs)
     double best = 1e300;
     bool found = false;
-    const int Rs[3] = {8, 4, 2};
+    const int Rs[2] = {8, 4};
     for (int R : Rs) {
         if (fR && R != fR) continue;
         const int maxw = fbk::be_resident_max_threads(R) / 32;
@@ -655,7 +655,8 @@ template <typename T> bool plan_resident(int X, int Y, fb::ResidentPlan* out) {
                 const size_t smem = fb::resident_smem_bytes<T>(R, wy, wx);
                 if (smem > 220u * 1024u) continue;
                 const int warps = wx * wy;
-                const double cost = R * ((warps + 3) / 4) * 30.0 + (ty * tx > 1 ? 1000.0 : 0.0);
+                // (columns crossing tiles cannot leave before the whole patch is computed; rows leave first)
+                const double cost = (R * 20.0 + 40.0) * ((warps + 3) / 4) + (ty * tx > 1 ? 1500.0 : 0.0) + (ty > 1 ? 1000.0 : 0.0);
                 if (cost < best) {   // (ties keep the taller patch: fewer rows cross shared memory per sweep)
                     best = cost;
                     found = true;
@@ -685,11 +686,10 @@ template <typename T> int solve_resident_t(fluidb200_solver* s, bool* done) {
     *done = false;
     if (!s->res_planned) {
         s->res_planned = true;
-        s->res_ok = fbk::be_resident_max_threads(2) > 0 && plan_resident<T>(s->X, s->Y, &s->res_plan) &&
+        s->res_ok = fbk::be_resident_max_threads(4) > 0 && plan_resident<T>(s->X, s->Y, &s->res_plan) &&
                     fbk::resident_capacity<T>(s->res_plan) >= s->res_plan.tiles_x * s->res_plan.tiles_y;
         if (s->res_ok) {
-            const size_t words = fb::resident_sync_words(s->res_plan.tiles_x * s->res_plan.tiles_y);
-            if (fbk::be_malloc(&s->res_scratch, words * sizeof(unsigned) + 64) != 0) s->res_ok = false;
+            if (fbk::be_malloc(&s->res_scratch, fb::resident_scratch_bytes<T>(s->res_plan)) != 0) s->res_ok = false;
         }
     }
     if (!s->res_ok) return 0;
@@ -714,6 +714,9 @@ template <typename T> int solve_resident_t(fluidb200_solver* s, bool* done) {
     const size_t words = fb::resident_sync_words(pl.tiles_x * pl.tiles_y);
     a.sync = (unsigned*)s->res_scratch;
     a.stash = (T*)((char*)s->res_scratch + words * sizeof(unsigned));
+    a.band = (char*)s->res_scratch + words * sizeof(unsigned) + 256;
+    a.band_len = fb::resident_band_len<T>(pl);
+    a.prof = env_int("FLUIDB200_RESIDENT_PROF", 0) ? (unsigned long long*)((char*)s->res_scratch + words * sizeof(unsigned) + 64) : nullptr;
     BE_CHECK(fbk::launch_resident<T>(a, pl, s->stream), "resident launch");
     s->launches += 1;
     s->resident_launches += 1;
@@ -985,6 +988,16 @@ extern "C" int fluidb200_set_use_graph(fluidb200_solver* s, int enable) {
 extern "C" int fluidb200_set_resident(fluidb200_solver* s, int enable) {
     if (!s) return fail(FLUIDB200_EINVAL, "solver is NULL");
     s->resident = enable < 0 ? -1 : (enable != 0);
+    return 0;
+}
+// (measurement aid) cycles per phase of the last resident launch made with FLUIDB200_RESIDENT_PROF=1:
+// out[0..7] = ring load + grid barrier, tentative velocity, right-hand side, sweeps, corrector, write-back, -, -
+extern "C" int fluidb200_resident_profile(fluidb200_solver* s, unsigned long long out[8]) {
+    if (!s || !out || !s->res_scratch) return fail(FLUIDB200_ESTATE, "no resident launch to report on");
+    BE_CHECK(fbk::be_stream_sync(s->stream), "resident profile");
+    const size_t words = fb::resident_sync_words(s->res_plan.tiles_x * s->res_plan.tiles_y);
+    BE_CHECK(fbk::be_memcpy_async(out, (char*)s->res_scratch + words * sizeof(unsigned) + 64, 64, fbk::D2H, s->stream), "resident profile");
+    BE_CHECK(fbk::be_stream_sync(s->stream), "resident profile");
     return 0;
 }
 extern "C" int64_t fluidb200_resident_launch_count(const fluidb200_solver* s) { return s ? s->resident_launches : 0; }

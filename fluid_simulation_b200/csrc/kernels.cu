@@ -113,7 +113,7 @@ __global__ void __launch_bounds__(kThreads, 4) corrector_kernel(const __grid_con
 
 // Whole timesteps of a small grid in one cooperative launch (resident_kernels.cuh). One CTA per SM;
 // the patch height R fixes how many threads the registers allow.
-constexpr int resident_max_threads(int R) { return R <= 2 ? 768 : R <= 4 ? 512 : 256; }
+constexpr int resident_max_threads(int R) { return R <= 4 ? 384 : 256; }
 template <typename T, int V, int R>
 __global__ void __launch_bounds__(resident_max_threads(R), 1) resident_kernel(const __grid_constant__ fb::ResidentArgs<T> A) {
     fb::resident_body<T, V, R>(A);
@@ -123,7 +123,6 @@ template <typename T, int R> void (*resident_entry())(fb::ResidentArgs<T>) {
 }
 template <typename T> void (*resident_entry_r(int R))(fb::ResidentArgs<T>) {
     switch (R) {
-        case 2: return resident_entry<T, 2>();
         case 4: return resident_entry<T, 4>();
         case 8: return resident_entry<T, 8>();
         default: return nullptr;
@@ -371,7 +370,7 @@ int launch_init_cavity(T* const fields[7], long long pitch, int X, int Y, int ro
     return rc_of(cudaGetLastError());
 }
 
-int be_resident_max_threads(int R) { return (R == 2 || R == 4 || R == 8) ? resident_max_threads(R) : 0; }
+int be_resident_max_threads(int R) { return (R == 4 || R == 8) ? resident_max_threads(R) : 0; }
 
 // CTAs of the resident kernel that can be co-resident on the current device (0: not launchable)
 template <typename T> int resident_capacity(const fb::ResidentPlan& pl) {
@@ -398,7 +397,7 @@ template <typename T> int launch_resident(const fb::ResidentArgs<T>& a, const fb
     if (!kern) { g_last = cudaErrorInvalidValue; return -1; }
     cudaStream_t st = (cudaStream_t)stream;
     const int ntiles = pl.tiles_x * pl.tiles_y;
-    if (rc_of(cudaMemsetAsync(a.sync, 0, fb::resident_sync_words(ntiles) * sizeof(unsigned), st))) return -1;
+    if (rc_of(cudaMemsetAsync(a.sync, 0, fb::resident_scratch_bytes<T>(pl), st))) return -1;   // counters, packets
     if (rc_of(cudaFuncSetAttribute((const void*)kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl.smem))) return -1;
     fb::ResidentArgs<T> args = a;
     void* params[1] = {(void*)&args};

@@ -61,6 +61,32 @@ FB_DEV void resident_grid_barrier(unsigned* bar, unsigned& epoch, unsigned nctas
 }
 
 template <int M> struct ModeTag { static constexpr int value = M; };
+template <bool B> struct BoolTag { static constexpr bool value = B; };
+
+// N consecutive elements (N * sizeof(T) is 8 or a multiple of 16 bytes, the address aligned likewise) from
+// shared memory, or -- CG -- from L2 past this SM's L1.
+template <typename T, int N, bool CG> FB_DEV void load_run(const T* src, T (&out)[N]) {
+    if constexpr ((N * sizeof(T)) % 16 == 0) {
+#pragma unroll
+        for (int k = 0; k < (int)(N * sizeof(T) / 16); ++k) {
+            const int4 q = CG ? __ldcg(reinterpret_cast<const int4*>(src) + k) : reinterpret_cast<const int4*>(src)[k];
+            *reinterpret_cast<int4*>(&out[k * (16 / sizeof(T))]) = q;
+        }
+    } else {
+        static_assert(N * sizeof(T) == 8, "runs are 8 bytes or whole 16-byte vectors");
+        const int2 q = CG ? __ldcg(reinterpret_cast<const int2*>(src)) : *reinterpret_cast<const int2*>(src);
+        *reinterpret_cast<int2*>(&out[0]) = q;
+    }
+}
+template <typename T, int N> FB_DEV void store_run(T* dst, const T (&v)[N]) {
+    if constexpr ((N * sizeof(T)) % 16 == 0) {
+#pragma unroll
+        for (int k = 0; k < (int)(N * sizeof(T) / 16); ++k)
+            reinterpret_cast<int4*>(dst)[k] = *reinterpret_cast<const int4*>(&v[k * (16 / sizeof(T))]);
+    } else {
+        *reinterpret_cast<int2*>(dst) = *reinterpret_cast<const int2*>(&v[0]);
+    }
+}
 
 template <typename T, int V, int R>
 FB_DEV void resident_body(const ResidentArgs<T>& A) {
@@ -80,10 +106,12 @@ FB_DEV void resident_body(const ResidentArgs<T>& A) {
     const int TR = wx * R, TC = wy * W;
     const int tr0 = txi * TR, tc0 = tyi * TC;   // first row / column of the tile
     const int x0 = tr0 + wxi * R;               // first row of this thread's patch
-    const int c0 = tc0 + wyi * W + lane * V;    // first column of this thread's patch
+    const int wc0 = tc0 + wyi * W;              // first column of this warp
+    const int c0 = wc0 + lane * V;              // first column of this thread's patch
     const bool col_ok = (long long)c0 + V <= pitch;   // the lane's 16 bytes exist in memory
+    const bool l0 = lane == 0, l31 = lane == 31;
 
-    // shared memory: four frames (tile + halo) for the predictor, then the exchange buffers of the sweeps
+    // shared memory: four frames (tile + halo) for the predictor / corrector, then the exchange buffers of the sweeps
     const int FR = TR + 2 * RH, FP = TC + 2 * CH;
     T* su = reinterpret_cast<T*>(fb_res_smem);
     T* sv = su + FR * FP;
@@ -91,36 +119,77 @@ FB_DEV void resident_body(const ResidentArgs<T>& A) {
     T* svs = sus + FR * FP;     // v_next
     T* rowbuf = svs + FR * FP;                  // [parity][warp][first / last row of the patch][W]
     T* colbuf = rowbuf + 2 * nwarps * 2 * W;    // [parity][warp][first / last column of the warp][R]
+    const int rowpar = nwarps * 2 * W, colpar = nwarps * 2 * R;   // elements between the two parities
     const int fbase = (x0 - tr0 + RH) * FP + (c0 - tc0 + CH);   // frame index of patch cell (row 0, element 0)
 
     T* const U = A.f[0];
     T* const Vf = A.f[1];
-    T* const gp[2] = {A.f[5], A.f[2]};   // pressure as published for the neighbours: p_g lives in gp[g & 1]; the
-                                         // state before the first sweep (g = -1) is the solver's p
-    unsigned* const my_cnt = A.sync + 32 * (1 + tile);
-    const bool bwarp = ntiles > 1 && (wxi == 0 || wxi == wx - 1 || wyi == 0 || wyi == wy - 1);
-    const unsigned nbw = (unsigned)(nwarps - (wx > 2 ? wx - 2 : 0) * (wy > 2 ? wy - 2 : 0));  // boundary warps of a tile
 
-    // y edges of this warp (SerialNavierStokes.cpp:163-175)
-    const int wc0 = tc0 + wyi * W;
-    const bool has_yedge = (wc0 == 0) || (wc0 <= Y - 1 && Y - 1 < wc0 + W);
-    YEdgeUniform<T, V> ye;
-    ye.lane0_bottom = (wc0 == 0) && lane == 0;
-    ye.bot_use = A.pmode[BOTTOM] == EDGE_CONST;
-    ye.top_use = A.pmode[TOP] == EDGE_CONST;
-    ye.bot_v = A.pval[BOTTOM];
-    ye.top_v = A.pval[TOP];
-    ye.top_bits = 0u;
-#pragma unroll
-    for (int e = 0; e < V; ++e) ye.top_bits |= (c0 + e == Y - 1) ? (1u << e) : 0u;
+    // ---- who this thread exchanges with (all of it fixed for the launch) -------------------------------
+    // kinds: 0 nothing there (box wall), 1 another warp of this CTA (shared memory), 2 another tile (L2 band)
+    const int up_kind = wxi > 0 ? 1 : (txi > 0 ? 2 : 0);
+    const int dn_kind = wxi < wx - 1 ? 1 : (txi < tiles_x - 1 ? 2 : 0);
+    const int lf_kind = wyi > 0 ? 1 : (tyi > 0 ? 2 : 0);
+    const int rt_kind = wyi < wy - 1 ? 1 : (tyi < tiles_y - 1 ? 2 : 0);
+    // (kept as 32-bit offsets: the pointers would cost two registers each)
+    const int pub_row = (warp * 2) * W + lane * V;             // into rowbuf
+    const int pub_col = (warp * 2) * R;                         // into colbuf
+    const int up_s = ((warp - wy) * 2 + 1) * W + lane * V;
+    const int dn_s = ((warp + wy) * 2) * W + lane * V;
+    const int lf_s = ((warp - 1) * 2 + 1) * R;
+    const int rt_s = ((warp + 1) * 2) * R;
+    // Between tiles a border travels as 8-byte PACKETS {32 data bits, sequence number}: an aligned 8-byte
+    // store is seen whole or not at all, so the reader spins on the data itself until every packet carries
+    // the number of the publication it waits for -- no flag, no fence, one trip through L2. A border of the
+    // tile is `band_words` packets: [parity][tile][top row, bottom row, left column, right column].
+    constexpr int WPE = sizeof(T) / 4;                          // 32-bit words per element
+    constexpr int ROWW = V * WPE, COLW = R * WPE;               // packets of a lane's row piece / of a warp's column piece
+    const int LW = A.band_len * WPE;
+    const int bandpar = ntiles * 4 * LW;                        // packets between the two parities
+    const int roffw = (wyi * W + lane * V) * WPE, coffw = wxi * R * WPE;
+    auto band_off = [&](int t, int side, int o) { return (t * 4 + side) * LW + o; };   // (packets; < 2^31)
+    const int up_g = up_kind == 2 ? band_off(tile - tiles_y, 1, roffw) : 0;
+    const int dn_g = dn_kind == 2 ? band_off(tile + tiles_y, 0, roffw) : 0;
+    const int lf_g = lf_kind == 2 ? band_off(tile - 1, 3, coffw) : 0;
+    const int rt_g = rt_kind == 2 ? band_off(tile + 1, 2, coffw) : 0;
+    const int gb_top = (wxi == 0 && txi > 0) ? band_off(tile, 0, roffw) : -1;
+    const int gb_bot = (wxi == wx - 1 && txi < tiles_x - 1) ? band_off(tile, 1, roffw) : -1;
+    const int gb_lf = (wyi == 0 && tyi > 0) ? band_off(tile, 2, coffw) : -1;
+    const int gb_rt = (wyi == wy - 1 && tyi < tiles_y - 1) ? band_off(tile, 3, coffw) : -1;
+    unsigned long long* const band = reinterpret_cast<unsigned long long*>(A.band);
+
+    // ---- boundary rules of this thread (SerialNavierStokes.cpp:152-189) -----------------------------
     const bool lconst = A.pmode[LEFT] == EDGE_CONST, rconst = A.pmode[RIGHT] == EDGE_CONST;
+    const bool bot_use = A.pmode[BOTTOM] == EDGE_CONST, top_use = A.pmode[TOP] == EDGE_CONST;
+    const T bot_v = A.pval[BOTTOM], top_v = A.pval[TOP];
     // Column Y-1 can be the FIRST column of a warp (Y = 1 + m * 32V: 129, 257, 1025 ...): its inward
     // neighbour Y-2 then belongs to another warp, so the column cannot be refreshed in the same sweep.
-    // It is treated like an x wall instead: not stored, substituted where column Y-2 needs it, written
-    // at the end.
+    // It is not kept during the sweeps: column Y-2 substitutes the value it would hold, and it is written
+    // at the end. Likewise row X-1 when it is the first row of a patch (`wall_below`).
     const bool top_detached = ((Y - 1) % W) == 0;
-    if (top_detached) ye.top_bits = 0u;
     const bool warp_top_det = top_detached && (wc0 + W - 1 == Y - 2);   // this warp's last column is Y-2
+    const bool has_bottom = wc0 == 0;
+    const bool has_top = !top_detached && wc0 <= Y - 1 && Y - 1 < wc0 + W;
+    const int eT = (Y - 1) % V;                           // element that holds column Y-1 (in the lane that has it)
+    const bool top_lane = has_top && (c0 + eT == Y - 1);
+    const bool bconst = has_bottom && l0 && bot_use, bcopy = has_bottom && l0 && !bot_use;
+    const bool tconst = top_lane && top_use, tcopy = top_lane && !top_use;
+    const int rX1 = X - 1 - x0;                            // index of row X-1 in this patch (if in [1, R-1]: kept here)
+    const bool wall_below = x0 + R - 1 == X - 2;           // row X-1 is the first row of the patch below
+    // warps that have anything to fix up around the plain sweep
+    const bool general = has_bottom || has_top || warp_top_det || x0 == 0 || (rX1 >= 1 && rX1 <= R - 1) || wall_below;
+
+    // Values the sweep loop uses over and over. Made opaque so that the compiler keeps them in registers
+    // instead of recomputing each from the kernel arguments in every sweep (which it did: ~150
+    // instructions per sweep).
+    const int rb0 = (int)(rowbuf - su), cb0 = (int)(colbuf - su);   // (offsets below count from the start of shared memory)
+    int o_general = general, o_pub_row = rb0 + pub_row, o_pub_col = cb0 + pub_col, o_up_s = rb0 + up_s, o_dn_s = rb0 + dn_s,
+        o_lf_s = cb0 + lf_s, o_rt_s = cb0 + rt_s, o_up_k = up_kind, o_dn_k = dn_kind, o_lf_k = lf_kind, o_rt_k = rt_kind, o_up_g = up_g, o_dn_g = dn_g,
+        o_lf_g = lf_g, o_rt_g = rt_g, o_gb_top = gb_top, o_gb_bot = gb_bot, o_gb_lf = gb_lf, o_gb_rt = gb_rt,
+        o_rowpar = rowpar, o_colpar = colpar, o_bandpar = bandpar;
+    asm volatile("" : "+r"(o_general), "+r"(o_pub_row), "+r"(o_pub_col), "+r"(o_up_s), "+r"(o_dn_s), "+r"(o_lf_s), "+r"(o_rt_s));
+    asm volatile("" : "+r"(o_up_k), "+r"(o_dn_k), "+r"(o_lf_k), "+r"(o_rt_k), "+r"(o_up_g), "+r"(o_dn_g), "+r"(o_lf_g), "+r"(o_rt_g));
+    asm volatile("" : "+r"(o_gb_top), "+r"(o_gb_bot), "+r"(o_gb_lf), "+r"(o_gb_rt), "+r"(o_rowpar), "+r"(o_colpar), "+r"(o_bandpar));
 
     VT p[R], b[R];
 #pragma unroll
@@ -131,93 +200,69 @@ FB_DEV void resident_body(const ResidentArgs<T>& A) {
     }
 
     // ---- exchange of patch borders ----------------------------------------------------------
-    auto publish = [&](int par, T* gdst) {
-        T* rb = rowbuf + (size_t)((par * nwarps + warp) * 2) * W + lane * V;
-        st_vec<T, V>(rb, p[0]);
-        st_vec<T, V>(rb + W, p[R - 1]);
-        T* cb = colbuf + (size_t)((par * nwarps + warp) * 2) * R;
-        if (lane == 0) {
+    // NW 32-bit words -> NW packets carrying sequence number `seq`, stored 16 bytes (two packets) at a time
+    auto put_packets = [&](unsigned long long* dst, const unsigned* w, auto nw_tag, unsigned seq) {
+        constexpr int NW = decltype(nw_tag)::value;
+        static_assert(NW % 2 == 0, "packets are stored in pairs");
 #pragma unroll
-            for (int r = 0; r < R; ++r) cb[r] = p[r].a[0];
-        }
-        if (lane == 31) {
-#pragma unroll
-            for (int r = 0; r < R; ++r) cb[R + r] = p[r].a[V - 1];
-        }
-        if (bwarp && gdst) {   // (warp-uniform) the tile's outer rows and columns, for the adjacent tiles
-            if (wxi == 0 && txi > 0 && col_ok && x0 < X) st_vec<T, V>(gdst + (long long)x0 * pitch + c0, p[0]);
-            if (wxi == wx - 1 && txi < tiles_x - 1 && col_ok && x0 + R - 1 < X)
-                st_vec<T, V>(gdst + (long long)(x0 + R - 1) * pitch + c0, p[R - 1]);
-            if (wyi == 0 && tyi > 0 && lane == 0) {
-#pragma unroll
-                for (int r = 0; r < R; ++r)
-                    if (x0 + r < X) gdst[(long long)(x0 + r) * pitch + c0] = p[r].a[0];
-            }
-            if (wyi == wy - 1 && tyi < tiles_y - 1 && lane == 31) {
-#pragma unroll
-                for (int r = 0; r < R; ++r)
-                    if (x0 + r < X) gdst[(long long)(x0 + r) * pitch + c0 + V - 1] = p[r].a[V - 1];
-            }
-            __syncwarp();
-            if (lane == 0) {
-                __threadfence();
-                red_release_gpu(my_cnt, 1u);
-            }
+        for (int k = 0; k < NW; k += 2) {
+            const unsigned long long a = (unsigned long long)w[k] | ((unsigned long long)seq << 32);
+            const unsigned long long c = (unsigned long long)w[k + 1] | ((unsigned long long)seq << 32);
+            asm volatile("st.volatile.global.v2.u64 [%0], {%1, %2};" ::"l"(dst + k), "l"(a), "l"(c) : "memory");
         }
     };
-    auto wait_tile = [&](int other, unsigned need) {
-        const unsigned* c = A.sync + 32 * (1 + other);
-        while (ld_acquire_gpu(c) < need) {}
+    auto get_packets = [&](const unsigned long long* src, unsigned* w, auto nw_tag, unsigned seq) {
+        constexpr int NW = decltype(nw_tag)::value;
+        bool ok;
+        do {
+            ok = true;
+#pragma unroll
+            for (int k = 0; k < NW; k += 2) {
+                unsigned long long a, c;
+                asm volatile("ld.volatile.global.v2.u64 {%0, %1}, [%2];" : "=l"(a), "=l"(c) : "l"(src + k) : "memory");
+                w[k] = (unsigned)a;
+                w[k + 1] = (unsigned)c;
+                ok = ok && (unsigned)(a >> 32) == seq && (unsigned)(c >> 32) == seq;
+            }
+        } while (!ok);
     };
-    // the four sides of the patch as published with parity `par` (`need` publications of a neighbouring tile)
-    auto fetch = [&](int par, const T* gsrc, unsigned need, VT& up, VT& dn, T (&lf)[R], T (&rt)[R]) {
-        const T* rb = rowbuf + (size_t)(par * nwarps * 2) * W + lane * V;
-        const T* cb = colbuf + (size_t)(par * nwarps * 2) * R;
+    // publication number `seq` (>= 1) of this patch's borders, into parity `par`: first and last row ...
+    auto publish_rows = [&](int par, unsigned seq, const VT& first, const VT& last) {
+        T* rb = su + (o_pub_row + par * o_rowpar);
+        st_vec<T, V>(rb, first);
+        st_vec<T, V>(rb + W, last);
+        if (o_gb_top >= 0) put_packets(band + (o_gb_top + par * o_bandpar), reinterpret_cast<const unsigned*>(&first), ModeTag<ROWW>{}, seq);
+        if (o_gb_bot >= 0) put_packets(band + (o_gb_bot + par * o_bandpar), reinterpret_cast<const unsigned*>(&last), ModeTag<ROWW>{}, seq);
+    };
+    // ... and first and last column of the warp
+    auto publish_cols = [&](int par, unsigned seq) {
+        if (l0 || l31) {
+            T edge[R];
+#pragma unroll
+            for (int r = 0; r < R; ++r) edge[r] = l0 ? p[r].a[0] : p[r].a[V - 1];
+            store_run<T, R>(su + (o_pub_col + par * o_colpar + (l0 ? 0 : R)), edge);
+            const int g_off = l0 ? o_gb_lf : o_gb_rt;
+            if (g_off >= 0) put_packets(band + (g_off + par * o_bandpar), reinterpret_cast<const unsigned*>(edge), ModeTag<COLW>{}, seq);
+        }
+    };
+    // the four sides of the patch as published (number `seq`) with parity `par`
+    auto fetch = [&](int par, unsigned seq, VT& up, VT& dn, T (&lf)[R], T (&rt)[R]) {
         up = vzero<T, V>();
         dn = vzero<T, V>();
-        if (wxi > 0) {
-            up = *reinterpret_cast<const VT*>(rb + (size_t)((warp - wy) * 2 + 1) * W);
-        } else if (txi > 0) {
-            wait_tile(tile - tiles_y, need);
-            if (col_ok) up = ld_cg<T, V>(gsrc + (long long)(x0 - 1) * pitch + c0);
-        }
-        if (wxi < wx - 1) {
-            dn = *reinterpret_cast<const VT*>(rb + (size_t)((warp + wy) * 2) * W);
-        } else if (txi < tiles_x - 1) {
-            wait_tile(tile + tiles_y, need);
-            if (col_ok && x0 + R < X) dn = ld_cg<T, V>(gsrc + (long long)(x0 + R) * pitch + c0);
-        }
 #pragma unroll
         for (int r = 0; r < R; ++r) {
             lf[r] = T(0);
             rt[r] = T(0);
         }
-        if (wyi > 0) {
-            if (lane == 0) {
-#pragma unroll
-                for (int r = 0; r < R; ++r) lf[r] = cb[(size_t)((warp - 1) * 2 + 1) * R + r];
-            }
-        } else if (tyi > 0) {
-            wait_tile(tile - 1, need);
-            if (lane == 0) {
-#pragma unroll
-                for (int r = 0; r < R; ++r)
-                    if (x0 + r < X) lf[r] = ld_cg1<T>(gsrc + (long long)(x0 + r) * pitch + c0 - 1);
-            }
-        }
-        if (wyi < wy - 1) {
-            if (lane == 31) {
-#pragma unroll
-                for (int r = 0; r < R; ++r) rt[r] = cb[(size_t)((warp + 1) * 2) * R + r];
-            }
-        } else if (tyi < tiles_y - 1) {
-            wait_tile(tile + 1, need);
-            if (lane == 31) {
-#pragma unroll
-                for (int r = 0; r < R; ++r)
-                    if (x0 + r < X) rt[r] = ld_cg1<T>(gsrc + (long long)(x0 + r) * pitch + c0 + V);
-            }
-        }
+        if (o_up_k == 1) up = *reinterpret_cast<const VT*>(su + o_up_s + par * o_rowpar);
+        else if (o_up_k == 2) get_packets(band + o_up_g + par * o_bandpar, reinterpret_cast<unsigned*>(&up), ModeTag<ROWW>{}, seq);
+        if (o_dn_k == 1) dn = *reinterpret_cast<const VT*>(su + o_dn_s + par * o_rowpar);
+        else if (o_dn_k == 2) get_packets(band + o_dn_g + par * o_bandpar, reinterpret_cast<unsigned*>(&dn), ModeTag<ROWW>{}, seq);
+        // (every lane reads the same run: one broadcast access; only lane 0 / 31 use it)
+        if (o_lf_k == 1) load_run<T, R, false>(su + o_lf_s + par * o_colpar, lf);
+        else if (o_lf_k == 2) get_packets(band + o_lf_g + par * o_bandpar, reinterpret_cast<unsigned*>(lf), ModeTag<COLW>{}, seq);
+        if (o_rt_k == 1) load_run<T, R, false>(su + o_rt_s + par * o_colpar, rt);
+        else if (o_rt_k == 2) get_packets(band + o_rt_g + par * o_bandpar, reinterpret_cast<unsigned*>(rt), ModeTag<COLW>{}, seq);
     };
     auto splat = [](T v) {
         VT r;
@@ -225,76 +270,148 @@ FB_DEV void resident_body(const ResidentArgs<T>& A) {
         for (int e = 0; e < V; ++e) r.a[e] = v;
         return r;
     };
+    // What a `general` warp adds around the plain arithmetic. BEFORE: neighbours that are not kept
+    // (row X-1 below this patch, column Y-1 beside this warp) take the value they would hold -- the
+    // constant, or a copy of this patch's own border as of the previous sweep; the first sweep of a
+    // launch (`subst` false) reads them as they were uploaded instead.
+    auto fix_neighbours = [&](bool subst, VT& dn, T (&rt)[R]) {
+        if (!subst) return;
+        if (wall_below) dn = rconst ? splat(A.pval[RIGHT]) : p[R - 1];                      // :183-187
+        if (warp_top_det) {
+#pragma unroll
+            for (int r = 0; r < R; ++r) rt[r] = top_use ? top_v : p[r].a[V - 1];            // :170-174
+        }
+    };
+    // AFTER: the boundary cells this patch does keep are refreshed from their freshly computed inward
+    // neighbours (or the constant): wall rows 0 and X-1 (:177-188), columns 0 and Y-1 (:163-175). Corners
+    // end up with placeholders; they feed no stencil and are written at the end of the launch.
+    auto fix_boundary_cells = [&]() {
+        if (x0 == 0) p[0] = lconst ? splat(A.pval[LEFT]) : p[1];
+        if (rX1 >= 1 && rX1 <= R - 1) {
+#pragma unroll
+            for (int r = 1; r < R; ++r)
+                if (r == rX1) p[r] = rconst ? splat(A.pval[RIGHT]) : p[r - 1];
+        }
+        if (has_bottom) {
+#pragma unroll
+            for (int r = 0; r < R; ++r) p[r].a[0] = bcopy ? p[r].a[1] : (bconst ? bot_v : p[r].a[0]);
+        }
+        if (has_top) {   // (warp-uniform, like eT)
+            if (eT == 0) {
+#pragma unroll
+                for (int r = 0; r < R; ++r) {
+                    const T below = shfl_up1(p[r].a[V - 1]);
+                    p[r].a[0] = tcopy ? below : (tconst ? top_v : p[r].a[0]);
+                }
+            }
+#pragma unroll
+            for (int e = 1; e < V; ++e) {
+                if (eT == e) {
+#pragma unroll
+                    for (int r = 0; r < R; ++r) p[r].a[e] = tcopy ? p[r].a[e - 1] : (tconst ? top_v : p[r].a[e]);
+                }
+            }
+        }
+    };
 
     // ---- one Jacobi sweep: p_g from p_{g-1} (SerialNavierStokes.cpp:140-198) ---------------------
+    // Every row of the patch is computed, wall rows and rows beyond the box included: what must not
+    // change is put right by fix_boundary_cells, what lies outside is never stored and feeds nothing.
+    // The first and the last row are computed FIRST and published at once: they are what the patches
+    // above and below (other warps, other tiles) wait for, and the rows between are computed while
+    // those travel.
+    auto one_row = [&](const VT& xm, const VT& cur, const VT& xp, T lfv, T rtv, const VT& bb) {
+        VT ym, yp;
+        y_neighbours<T, V>(cur, ym, yp);
+        ym.a[0] = l0 ? lfv : ym.a[0];
+        yp.a[V - 1] = l31 ? rtv : yp.a[V - 1];
+        return jacobi_row_yn<T, V>(xm, xp, ym, yp, bb);
+    };
     auto sweep = [&](int g) {
-        const int sp = (g + 1) & 1;   // parity of g - 1
+        static_assert(R >= 2, "a patch holds its wall row and the row next to it");
         VT up, dn;
         T lf[R], rt[R];
-        fetch(sp, gp[sp], nbw * (unsigned)g, up, dn, lf, rt);
-        const bool subst = g > 0;     // the first sweep of a launch reads the wall rows as they were uploaded
-        VT prev = up;
+        fetch((g + 1) & 1, (unsigned)(g + 1), up, dn, lf, rt);
+        if (o_general) fix_neighbours(g > 0, dn, rt);
+        const VT old0 = p[0], oldL = p[R - 1];
+        const VT new0 = one_row(up, old0, p[1], lf[0], rt[0], b[0]);
+        const VT newL = one_row(p[R - 2], oldL, dn, lf[R - 1], rt[R - 1], b[R - 1]);
+        publish_rows(g & 1, (unsigned)(g + 2), new0, newL);
+        VT prev = old0;
 #pragma unroll
-        for (int r = 0; r < R; ++r) {
-            const int x = x0 + r;
+        for (int r = 1; r < R - 1; ++r) {
             const VT cur = p[r];
-            const VT nxt = (r < R - 1) ? p[r < R - 1 ? r + 1 : r] : dn;
-            if (x >= 1 && x <= X - 2) {   // (warp-uniform)
-                VT xm = prev, xp = nxt;
-                if (subst && x == 1) xm = lconst ? splat(A.pval[LEFT]) : cur;         // :177-181 as of the previous sweep
-                if (subst && x == X - 2) xp = rconst ? splat(A.pval[RIGHT]) : cur;    // :183-187
-                VT ym, yp;
-                y_neighbours<T, V>(cur, ym, yp);
-                ym.a[0] = (lane == 0) ? lf[r] : ym.a[0];
-                yp.a[V - 1] = (lane == 31) ? rt[r] : yp.a[V - 1];
-                if (warp_top_det && subst) yp.a[V - 1] = (lane == 31) ? (ye.top_use ? ye.top_v : cur.a[V - 1]) : yp.a[V - 1];
-                VT out = jacobi_row_yn<T, V>(xm, xp, ym, yp, b[r]);
-                if (has_yedge) ye.apply(out);   // columns 0 and Y-1 of this row (:163-175)
-                p[r] = out;
-            }
+            const VT nxt = (r < R - 2) ? p[r < R - 2 ? r + 1 : r] : oldL;
+            p[r] = one_row(prev, cur, nxt, lf[r], rt[r], b[r]);
             prev = cur;
         }
-        publish(g & 1, gp[g & 1]);
+        p[0] = new0;
+        p[R - 1] = newL;
+        if (o_general) fix_boundary_cells();
+        publish_cols(g & 1, (unsigned)(g + 2));
     };
 
     // ---- predictor: u_next, v_next on the tile + 1 ring, rhs on the patch (SerialNavierStokes.cpp:298-335) ----
-    auto load_frames = [&]() {
-        for (int idx = tid; idx < FR * FP; idx += nthreads) {
-            const int i = idx / FP, j = idx - i * FP;
+    // u and v of the tile live in the frames su / sv for the whole launch (the corrector writes them there);
+    // only the two-cell ring around the tile comes from the other tiles, through L2, once per step.
+    auto load_ring = [&]() {
+        const int nj = TC + 4, n1 = 2 * RH * nj, n = n1 + TR * 4;
+        for (int idx = tid; idx < n; idx += nthreads) {
+            int i, j;
+            if (idx < n1) {
+                const int q = idx / nj;
+                i = q < RH ? q : RH + TR + (q - RH);
+                j = CH - 2 + (idx - q * nj);
+            } else {
+                const int k = idx - n1, q = k >> 2, m = k & 3;
+                i = RH + q;
+                j = m < 2 ? CH - 2 + m : CH + TC + (m - 2);
+            }
             const int gx = tr0 - RH + i, gy = tc0 - CH + j;
-            T uu = T(0), vv = T(0), us = T(0), vs = T(0);
             if (gx >= 0 && gx < X && gy >= 0 && gy < Y) {
                 const long long o = (long long)gx * pitch + gy;
-                uu = ld_cg1<T>(U + o);
-                vv = ld_cg1<T>(Vf + o);
-                if (gx == 0 || gx == X - 1 || gy == 0 || gy == Y - 1) {  // edge u_next / v_next: stored values, never written
-                    us = A.f[3][o];
-                    vs = A.f[4][o];
-                }
+                su[i * FP + j] = ld_cg1<T>(U + o);
+                sv[i * FP + j] = ld_cg1<T>(Vf + o);
             }
-            su[idx] = uu;
-            sv[idx] = vv;
-            sus[idx] = us;
-            svs[idx] = vs;
         }
     };
-    auto tentative_frame = [&](auto mode_tag) {
+    auto tentative_scalar = [&](auto mode_tag, int c) {   // one frame cell (an interior cell of the box)
         constexpr int MODE = decltype(mode_tag)::value;
-        const int nj = TC + 2, n = (TR + 2) * nj;
+        Flags fl;
+        UV<T> r = tentative_cell<T, MODE>(A.pa, su[c], sv[c], su[c - FP], su[c + FP], su[c - 1], su[c + 1], sv[c - FP],
+                                          sv[c + FP], sv[c - 1], sv[c + 1], fl);
+        if (MODE != DIV_EXACT && fl.raised(A.pa.m.pow2_lo_m1))
+            r = tentative_cell_exact<T>(A.pa, su[c], sv[c], su[c - FP], su[c + FP], su[c - 1], su[c + 1], sv[c - FP],
+                                        sv[c + FP], sv[c - 1], sv[c + 1]);
+        sus[c] = r.u;
+        svs[c] = r.v;
+    };
+    auto tentative = [&](auto mode_tag) {
+        // the patch
+#pragma unroll
+        for (int r = 0; r < R; ++r) {
+            const int x = x0 + r;
+            if (x < 1 || x > X - 2) continue;
+#pragma unroll
+            for (int e = 0; e < V; ++e) {
+                const int col = c0 + e;
+                if (col >= 1 && col <= Y - 2) tentative_scalar(mode_tag, fbase + r * FP + e);
+            }
+        }
+        // the one-cell ring around the tile (its cells belong to other tiles, which compute them too)
+        const int nj = TC + 2, n1 = 2 * nj, n = n1 + 2 * TR;
         for (int idx = tid; idx < n; idx += nthreads) {
-            const int ii = idx / nj, jj = idx - ii * nj;
-            const int i = RH - 1 + ii, j = CH - 1 + jj;
+            int i, j;
+            if (idx < n1) {
+                i = idx < nj ? RH - 1 : RH + TR;
+                j = CH - 1 + (idx < nj ? idx : idx - nj);
+            } else {
+                const int k = idx - n1;
+                i = RH + (k >> 1);
+                j = (k & 1) ? CH + TC : CH - 1;
+            }
             const int gx = tr0 - RH + i, gy = tc0 - CH + j;
-            if (gx < 1 || gx > X - 2 || gy < 1 || gy > Y - 2) continue;
-            const int c = i * FP + j;
-            Flags fl;
-            UV<T> r = tentative_cell<T, MODE>(A.pa, su[c], sv[c], su[c - FP], su[c + FP], su[c - 1], su[c + 1], sv[c - FP],
-                                              sv[c + FP], sv[c - 1], sv[c + 1], fl);
-            if (MODE != DIV_EXACT && fl.raised(A.pa.m.pow2_lo_m1))
-                r = tentative_cell_exact<T>(A.pa, su[c], sv[c], su[c - FP], su[c + FP], su[c - 1], su[c + 1], sv[c - FP],
-                                            sv[c + FP], sv[c - 1], sv[c + 1]);
-            sus[c] = r.u;
-            svs[c] = r.v;
+            if (gx >= 1 && gx <= X - 2 && gy >= 1 && gy <= Y - 2) tentative_scalar(mode_tag, i * FP + j);
         }
     };
     auto rhs_patch = [&](auto mode_tag, bool last_step) {
@@ -324,11 +441,10 @@ FB_DEV void resident_body(const ResidentArgs<T>& A) {
     // ---- corrector: u, v from the final p of the step, velocity edges (SerialNavierStokes.cpp:338-350, :222-295) ----
     auto corrector = [&](auto mode_tag, int g_done) {
         constexpr int MODE = decltype(mode_tag)::value;
-        const int sp = (g_done + 1) & 1;
         VT up, dn;
         T lf[R], rt[R];
-        fetch(sp, gp[sp], nbw * (unsigned)g_done, up, dn, lf, rt);
-        const bool subst = g_done > 0;
+        fetch((g_done + 1) & 1, (unsigned)(g_done + 1), up, dn, lf, rt);
+        if (o_general) fix_neighbours(g_done > 0, dn, rt);
         VT prev = up;
 #pragma unroll
         for (int r = 0; r < R; ++r) {
@@ -338,14 +454,11 @@ FB_DEV void resident_body(const ResidentArgs<T>& A) {
             if (x < X) {   // (warp-uniform)
                 VT un = vzero<T, V>(), vn = vzero<T, V>();
                 if (x >= 1 && x <= X - 2) {
-                    VT pm = prev, pp = nxt;
-                    if (subst && x == 1) pm = lconst ? splat(A.pval[LEFT]) : cur;
-                    if (subst && x == X - 2) pp = rconst ? splat(A.pval[RIGHT]) : cur;
+                    const VT pm = prev, pp = nxt;   // (wall rows are kept up to date in the patch, or were fixed above)
                     VT pym, pyp;
                     y_neighbours<T, V>(cur, pym, pyp);
-                    pym.a[0] = (lane == 0) ? lf[r] : pym.a[0];
-                    pyp.a[V - 1] = (lane == 31) ? rt[r] : pyp.a[V - 1];
-                    if (warp_top_det && subst) pyp.a[V - 1] = (lane == 31) ? (ye.top_use ? ye.top_v : cur.a[V - 1]) : pyp.a[V - 1];
+                    pym.a[0] = l0 ? lf[r] : pym.a[0];
+                    pyp.a[V - 1] = l31 ? rt[r] : pyp.a[V - 1];
                     const int c = fbase + r * FP;
 #pragma unroll
                     for (int e = 0; e < V; ++e) {
@@ -373,6 +486,8 @@ FB_DEV void resident_body(const ResidentArgs<T>& A) {
                         else if (col < Y - 1) { un.a[e] = A.uval[edge]; vn.a[e] = A.vval[edge]; }
                     }
                 }
+                st_vec<T, V>(su + fbase + r * FP, un);   // next step's predictor reads them here
+                st_vec<T, V>(sv + fbase + r * FP, vn);
                 if (col_ok) {
                     st_vec<T, V>(U + (long long)x * pitch + c0, un);
                     st_vec<T, V>(Vf + (long long)x * pitch + c0, vn);
@@ -387,19 +502,50 @@ FB_DEV void resident_body(const ResidentArgs<T>& A) {
     const int mode = A.pa.m.mode;   // (grid-uniform)
 
     // ---- the launch -------------------------------------------------------------------------------
-    publish(1, nullptr);   // the uploaded p, for the first sweep's fetch (its global copy is the solver's p itself)
+    // frames: this patch's u, v; the stored u_next / v_next of the box edges (never written, read by the rhs)
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+        const int x = x0 + r;
+        const bool in = x < X && col_ok;
+        st_vec<T, V>(su + fbase + r * FP, in ? ld_cg<T, V>(U + (long long)x * pitch + c0) : vzero<T, V>());
+        st_vec<T, V>(sv + fbase + r * FP, in ? ld_cg<T, V>(Vf + (long long)x * pitch + c0) : vzero<T, V>());
+    }
+    for (int idx = tid; idx < FR * FP; idx += nthreads) {
+        const int i = idx / FP, j = idx - i * FP;
+        const int gx = tr0 - RH + i, gy = tc0 - CH + j;
+        T us = T(0), vs = T(0);
+        if (gx >= 0 && gx < X && gy >= 0 && gy < Y && (gx == 0 || gx == X - 1 || gy == 0 || gy == Y - 1)) {
+            us = A.f[3][(long long)gx * pitch + gy];
+            vs = A.f[4][(long long)gx * pitch + gy];
+        }
+        sus[idx] = us;
+        svs[idx] = vs;
+    }
+    publish_rows(1, 1u, p[0], p[R - 1]);   // the uploaded p, for the first sweep's fetch
+    publish_cols(1, 1u);
     __syncthreads();
     unsigned epoch = 0;
+    long long t_prev = clock64();
+    auto tick = [&](int k) {   // (only when asked for: one thread of a middle tile adds up its cycles per phase)
+        if (A.prof && tid == 0 && tile == ntiles / 2) {
+            const long long t = clock64();
+            A.prof[k] += (unsigned long long)(t - t_prev);
+            t_prev = t;
+        }
+    };
     const int G = A.S * A.K;
     int g = 0;
     for (int step = 0; step < A.S; ++step) {
         if (step > 0) resident_grid_barrier(A.sync, epoch, (unsigned)ntiles);   // every tile's new u, v are in L2
-        load_frames();
+        load_ring();
         __syncthreads();
-        if (mode == 2) tentative_frame(M2{}); else if (mode == 1) tentative_frame(M1{}); else tentative_frame(M0{});
+        tick(0);
+        if (mode == 2) tentative(M2{}); else if (mode == 1) tentative(M1{}); else tentative(M0{});
         __syncthreads();
+        tick(1);
         const bool last = step == A.S - 1;
         if (mode == 2) rhs_patch(M2{}, last); else if (mode == 1) rhs_patch(M1{}, last); else rhs_patch(M0{}, last);
+        tick(2);
         for (int s = 0; s < A.K; ++s, ++g) {
             if (g == G - 1) {   // the values an unset corner copies are one sweep old
 #pragma unroll
@@ -419,34 +565,22 @@ FB_DEV void resident_body(const ResidentArgs<T>& A) {
         }
         // a tile may overwrite u, v only when no other tile still reads them for ITS predictor: three
         // sweeps of neighbour hand-shakes order that even for the diagonal tiles; fewer do not
+        tick(3);
         if (A.K < 3) resident_grid_barrier(A.sync, epoch, (unsigned)ntiles);
         if (mode == 2) corrector(M2{}, g); else if (mode == 1) corrector(M1{}, g); else corrector(M0{}, g);
+        tick(4);
     }
 
     // ---- write the state back: p with its wall rows and corners, u_next, v_next ----------------------
     resident_grid_barrier(A.sync, epoch, (unsigned)ntiles);   // nobody reads a published border any more
     T* const P = A.f[2];
-    bool deferred = false;   // row X-1 is the first row of this patch: its inward neighbour is another thread's
+    // (the wall rows and y-edge columns this patch keeps are final already; corners are fixed below)
+    const bool deferred = x0 == X - 1;   // row X-1 is the first row of this patch: its inward neighbour is another thread's
 #pragma unroll
     for (int r = 0; r < R; ++r) {
         const int x = x0 + r;
         if (x >= X) continue;
-        VT out = p[r];
-        if (x == 0 || x == X - 1) {   // x walls, columns 1 .. Y-2 (:177-188); corners are fixed below
-            const bool cst = (x == 0) ? lconst : rconst;
-            const T cv = (x == 0) ? A.pval[LEFT] : A.pval[RIGHT];
-            if (x == X - 1 && r == 0) {
-                deferred = true;
-            } else {
-                const VT inner = (x == 0) ? p[r < R - 1 ? r + 1 : r] : p[r > 0 ? r - 1 : 0];
-#pragma unroll
-                for (int e = 0; e < V; ++e) {
-                    const int col = c0 + e;
-                    if (col >= 1 && col <= Y - 2) out.a[e] = cst ? cv : inner.a[e];
-                }
-            }
-        }
-        if (col_ok && !(x == X - 1 && r == 0)) st_vec<T, V>(P + (long long)x * pitch + c0, out);
+        if (col_ok && !(deferred && r == 0)) st_vec<T, V>(P + (long long)x * pitch + c0, p[r]);
         if (x >= 1 && x <= X - 2 && col_ok) {
             const int c = fbase + r * FP;
             st_interior<T, V>(A.f[3] + (long long)x * pitch, c0, Y, *reinterpret_cast<const VT*>(sus + c));
@@ -466,18 +600,19 @@ FB_DEV void resident_body(const ResidentArgs<T>& A) {
         for (int r = 0; r < R; ++r) {
             const int x = x0 + r;
             if (x >= 1 && x <= X - 2)
-                P[(long long)x * pitch + Y - 1] = ye.top_use ? ye.top_v : ld_cg1<T>(P + (long long)x * pitch + Y - 2);
+                P[(long long)x * pitch + Y - 1] = top_use ? top_v : ld_cg1<T>(P + (long long)x * pitch + Y - 2);
         }
     }
     if (tile == 0 && tid == 0) {   // corners: the y-edge loop runs first (:163-175), so an unset corner copies the
                                    // wall cell next to it as it was BEFORE this sweep's x-edge loop refreshed it
-        const T l0 = lconst ? A.pval[LEFT] : ld_cg1<T>(A.stash + 0), l1 = lconst ? A.pval[LEFT] : ld_cg1<T>(A.stash + 1);
-        const T r0 = rconst ? A.pval[RIGHT] : ld_cg1<T>(A.stash + 2), r1 = rconst ? A.pval[RIGHT] : ld_cg1<T>(A.stash + 3);
-        P[0] = ye.bot_use ? ye.bot_v : l0;
-        P[Y - 1] = ye.top_use ? ye.top_v : l1;
-        P[(long long)(X - 1) * pitch] = ye.bot_use ? ye.bot_v : r0;
-        P[(long long)(X - 1) * pitch + Y - 1] = ye.top_use ? ye.top_v : r1;
+        const T c00 = lconst ? A.pval[LEFT] : ld_cg1<T>(A.stash + 0), c01 = lconst ? A.pval[LEFT] : ld_cg1<T>(A.stash + 1);
+        const T c10 = rconst ? A.pval[RIGHT] : ld_cg1<T>(A.stash + 2), c11 = rconst ? A.pval[RIGHT] : ld_cg1<T>(A.stash + 3);
+        P[0] = bot_use ? bot_v : c00;
+        P[Y - 1] = top_use ? top_v : c01;
+        P[(long long)(X - 1) * pitch] = bot_use ? bot_v : c10;
+        P[(long long)(X - 1) * pitch + Y - 1] = top_use ? top_v : c11;
     }
+    tick(5);
 }
 
 }  // namespace fb

@@ -235,6 +235,12 @@ template <typename T> struct ResidentArgs {
     T uval[4], vval[4];       // velocity edges: all EDGE_CONST
     unsigned* sync;           // zeroed before the launch: [0] grid barrier, [32 * (1 + tile)] rows published by a tile
     T* stash;                 // 4 values for the stale-corner rule
+    // Rows and columns a tile publishes for its neighbours: [parity][tile][top row, bottom row, left column,
+    // right column][band_len elements, as 8-byte packets of 32 data bits + sequence number], zeroed before
+    // the launch; band_len >= max(columns, rows) of a tile
+    void* band;
+    int band_len;
+    unsigned long long* prof;  // optional (may be NULL): cycles per phase of one tile, for measurements
 };
 
 struct ResidentPlan {
@@ -250,5 +256,15 @@ template <typename T> inline size_t resident_smem_bytes(int R, int wy, int wx) {
     return (4 * FR * FP + 2 * nwarps * 2 * W + 2 * nwarps * 2 * R) * sizeof(T);
 }
 inline size_t resident_sync_words(int ntiles) { return 32 * (size_t)(1 + ntiles); }
+// device scratch of a launch: [counters][256 bytes: corner values][bands]
+template <typename T> inline int resident_band_len(const ResidentPlan& pl) {
+    const int W = 32 * (16 / (int)sizeof(T));
+    const int n = pl.wy * W > pl.wx * pl.R ? pl.wy * W : pl.wx * pl.R;
+    return (n + 31) / 32 * 32;
+}
+template <typename T> inline size_t resident_scratch_bytes(const ResidentPlan& pl) {
+    const size_t nt = (size_t)pl.tiles_x * pl.tiles_y;
+    return resident_sync_words((int)nt) * sizeof(unsigned) + 256 + 2 * nt * 4 * (size_t)resident_band_len<T>(pl) * sizeof(T) * 2;
+}
 
 }  // namespace fb

@@ -120,8 +120,9 @@ def test_random_initial_state_and_pressure_edge_kinds(Solver, env, X, Y, dtype, 
 
 
 @pytest.mark.parametrize("X,Y,R,wy,wx,dtype", [
-    (300, 200, 2, 1, 4, "float32"), (300, 200, 4, 2, 3, "float32"), (200, 520, 2, 1, 8, "float32"), (97, 1030, 8, 2, 2, "float32"),
-    (150, 257, 4, 1, 2, "float32"), (120, 300, 2, 2, 5, "float64"), (31, 129, 2, 1, 3, "float64"), (64, 64, 2, 1, 1, "float32"),
+    (300, 200, 4, 1, 4, "float32"), (300, 200, 4, 2, 3, "float32"), (200, 520, 4, 1, 8, "float32"), (97, 1030, 8, 2, 2, "float32"),
+    (150, 257, 4, 1, 2, "float32"), (120, 300, 4, 2, 5, "float64"), (31, 129, 4, 1, 3, "float64"), (64, 64, 4, 1, 1, "float32"),
+    (200, 130, 8, 2, 4, "float32"), (90, 700, 8, 1, 1, "float32"),
 ])
 def test_forced_tilings_exchange_across_tiles(Solver, env, X, Y, R, wy, wx, dtype):
     """Small grids cut into many tiles on purpose (FLUIDB200_RESIDENT_R / _WY / _WX): rows and columns

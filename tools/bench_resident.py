@@ -22,5 +22,10 @@ for n in sizes:
         out[key + "_us_per_step"] = round(ms * 1e3 / S, 2)
         if resident:
             out["took_resident_path"] = s.resident_launch_count() == 2
+            if os.environ.get("FLUIDB200_RESIDENT_PROF"):
+                import ctypes as C
+                buf = (C.c_uint64 * 8)()
+                s._lib.fluidb200_resident_profile(s._h, buf)
+                out["cycles_per_step"] = {k: round(buf[i] / S) for i, k in enumerate(("halo+barrier", "tentative", "rhs", "sweeps", "corrector", "writeback"))}
         s.close()
     print(json.dumps(out), flush=True)
