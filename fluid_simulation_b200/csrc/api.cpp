@@ -637,6 +637,15 @@ template <typename T> bool plan_resident(int X, int Y, fb::ResidentPlan* out) {
     const int ncw = (Y + W - 1) / W;
     const int fR = env_int("FLUIDB200_RESIDENT_R", 0), fwy = env_int("FLUIDB200_RESIDENT_WY", 0),
               fwx = env_int("FLUIDB200_RESIDENT_WX", 0);   // (measurement knobs)
+    // a grid of at most 4096 cells: one CTA, a cell per thread and slot, everything in shared memory
+    // (FLUIDB200_RESIDENT_R = 4 or 8 forces the patch layout instead)
+    if (!fR && (long long)X * Y <= 4 * 1024 && fbk::be_resident_max_threads(0) > 0) {
+        const int n = X * Y;
+        out->R = 0; out->wy = n <= 2048 ? 2 : 4; out->wx = 1; out->tiles_y = out->tiles_x = 1;
+        out->threads = fbk::be_resident_max_threads(0);
+        out->smem = (size_t)(2 * (n + 4) + 4 * n) * sizeof(T);
+        return true;
+    }
     double best = 1e300;
     bool found = false;
     const int Rs[2] = {8, 4};

@@ -118,6 +118,18 @@ template <typename T, int V, int R>
 __global__ void __launch_bounds__(resident_max_threads(R), 1) resident_kernel(const __grid_constant__ fb::ResidentArgs<T> A) {
     fb::resident_body<T, V, R>(A);
 }
+// ... and grids of at most NC * 1024 cells in ONE CTA, a cell per thread and slot (plan.R == 0, plan.wy == NC)
+template <typename T, int NC>
+__global__ void __launch_bounds__(fb::kCellThreads, 1) resident_cell_kernel(const __grid_constant__ fb::ResidentArgs<T> A) {
+    fb::resident_cell_body<T, NC>(A);
+}
+template <typename T> void (*resident_cell_entry(int NC))(fb::ResidentArgs<T>) {
+    switch (NC) {
+        case 2: return resident_cell_kernel<T, 2>;
+        case 4: return resident_cell_kernel<T, 4>;
+        default: return nullptr;
+    }
+}
 template <typename T, int R> void (*resident_entry())(fb::ResidentArgs<T>) {
     return resident_kernel<T, fb::VecWidth<T>::V, R>;
 }
@@ -370,12 +382,12 @@ int launch_init_cavity(T* const fields[7], long long pitch, int X, int Y, int ro
     return rc_of(cudaGetLastError());
 }
 
-int be_resident_max_threads(int R) { return (R == 4 || R == 8) ? resident_max_threads(R) : 0; }
+int be_resident_max_threads(int R) { return R == 0 ? fb::kCellThreads : (R == 4 || R == 8) ? resident_max_threads(R) : 0; }
 
 // CTAs of the resident kernel that can be co-resident on the current device (0: not launchable)
 template <typename T> int resident_capacity(const fb::ResidentPlan& pl) {
-    auto kern = resident_entry_r<T>(pl.R);
-    if (!kern || pl.threads > resident_max_threads(pl.R)) return 0;
+    auto kern = pl.R == 0 ? resident_cell_entry<T>(pl.wy) : resident_entry_r<T>(pl.R);
+    if (!kern || pl.threads > (pl.R == 0 ? fb::kCellThreads : resident_max_threads(pl.R))) return 0;
     int dev = 0, coop = 0, max_optin = 0;
     if (cudaGetDevice(&dev) != cudaSuccess) return 0;
     cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, dev);
@@ -393,9 +405,15 @@ template <typename T> int resident_capacity(const fb::ResidentPlan& pl) {
     return per_sm * be_sm_count();
 }
 template <typename T> int launch_resident(const fb::ResidentArgs<T>& a, const fb::ResidentPlan& pl, void* stream) {
-    auto kern = resident_entry_r<T>(pl.R);
+    auto kern = pl.R == 0 ? resident_cell_entry<T>(pl.wy) : resident_entry_r<T>(pl.R);
     if (!kern) { g_last = cudaErrorInvalidValue; return -1; }
     cudaStream_t st = (cudaStream_t)stream;
+    if (pl.R == 0) {   // one CTA: an ordinary launch, no scratch
+        if (rc_of(cudaFuncSetAttribute((const void*)kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl.smem))) return -1;
+        kern<<<1, pl.threads, pl.smem, st>>>(a);
+        ++g_kernels;
+        return rc_of(cudaGetLastError());
+    }
     const int ntiles = pl.tiles_x * pl.tiles_y;
     if (rc_of(cudaMemsetAsync(a.sync, 0, fb::resident_scratch_bytes<T>(pl), st))) return -1;   // counters, packets
     if (rc_of(cudaFuncSetAttribute((const void*)kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl.smem))) return -1;

@@ -615,5 +615,192 @@ FB_DEV void resident_body(const ResidentArgs<T>& A) {
     tick(5);
 }
 
+
+// =========================================================================================
+// Grids that fit ONE CTA outright (up to 4096 cells: 41^2, 64^2): one cell per thread and slot, every
+// field in shared memory, one __syncthreads per sweep. With so few columns a 16-byte-per-lane patch
+// layout leaves two lanes in three idle; here every lane has a cell.
+//   * p ping-pongs between two shared arrays (Jacobi, SerialNavierStokes.cpp:140-198);
+//   * boundary cells are not updated during the sweeps: a cell next to a boundary reads, instead of
+//     the boundary cell, what that cell would hold -- ITSELF (the copy rule, :163-188: the boundary
+//     took this cell's value at the end of the previous sweep) or a slot holding the constant. That
+//     is a redirected neighbour ADDRESS, decided once per cell: no test in the loop. The very first
+//     sweep of a launch reads the true neighbours (the uploaded boundary values);
+//   * boundary cells and corners (one sweep stale, SURVEY A5: the other array still holds the state
+//     before the last sweep) are written once, at the end.
+// =========================================================================================
+constexpr int kCellThreads = 1024;
+
+template <typename T, int NC>
+FB_DEV void resident_cell_body(const ResidentArgs<T>& A) {
+    extern __shared__ __align__(16) unsigned char fb_res_smem[];
+    using A_ = Ar<T>;
+    const int tid = threadIdx.x;
+    const int X = A.X, Y = A.Y, n = X * Y;
+    const long long pitch = A.pitch;
+    const int NP = n + 4;                      // + one slot per edge for its constant
+    T* pbuf0 = reinterpret_cast<T*>(fb_res_smem);
+    T* pbuf1 = pbuf0 + NP;
+    T* su = pbuf1 + NP;
+    T* sv = su + n;
+    T* sus = sv + n;
+    T* svs = sus + n;
+
+    // per slot: the cell, its four (redirected) neighbours, its scaled right-hand side
+    int cell[NC], axm[NC], axp[NC], aym[NC], ayp[NC];
+    bool interior[NC];
+    T b[NC];
+    const bool lconst = A.pmode[LEFT] == EDGE_CONST, rconst = A.pmode[RIGHT] == EDGE_CONST;
+    const bool bconst = A.pmode[BOTTOM] == EDGE_CONST, tconst = A.pmode[TOP] == EDGE_CONST;
+#pragma unroll
+    for (int k = 0; k < NC; ++k) {
+        const int c = tid + k * kCellThreads;
+        const int x = c / Y, y = c - x * Y;
+        cell[k] = c;
+        interior[k] = c < n && x >= 1 && x <= X - 2 && y >= 1 && y <= Y - 2;
+        axm[k] = (x == 1) ? (lconst ? n + LEFT : c) : c - Y;
+        axp[k] = (x == X - 2) ? (rconst ? n + RIGHT : c) : c + Y;
+        aym[k] = (y == 1) ? (bconst ? n + BOTTOM : c) : c - 1;
+        ayp[k] = (y == Y - 2) ? (tconst ? n + TOP : c) : c + 1;
+        b[k] = T(0);
+    }
+    // load the state
+    for (int c = tid; c < n; c += kCellThreads) {
+        const int x = c / Y, y = c - x * Y;
+        const long long o = (long long)x * pitch + y;
+        pbuf0[c] = A.f[2][o];
+        pbuf1[c] = T(0);
+        su[c] = A.f[0][o];
+        sv[c] = A.f[1][o];
+        const bool edge = x == 0 || x == X - 1 || y == 0 || y == Y - 1;
+        sus[c] = edge ? A.f[3][o] : T(0);   // edge u_next / v_next: stored values, never written, read by the rhs
+        svs[c] = edge ? A.f[4][o] : T(0);
+    }
+    if (tid < 4) {
+        pbuf0[n + tid] = A.pval[tid];
+        pbuf1[n + tid] = A.pval[tid];
+    }
+    __syncthreads();
+
+    const int mode = A.pa.m.mode;
+    auto tentative = [&](auto mode_tag) {
+        constexpr int MODE = decltype(mode_tag)::value;
+#pragma unroll
+        for (int k = 0; k < NC; ++k) {
+            if (!interior[k]) continue;
+            const int c = cell[k];
+            Flags fl;
+            UV<T> r = tentative_cell<T, MODE>(A.pa, su[c], sv[c], su[c - Y], su[c + Y], su[c - 1], su[c + 1], sv[c - Y],
+                                              sv[c + Y], sv[c - 1], sv[c + 1], fl);
+            if (MODE != DIV_EXACT && fl.raised(A.pa.m.pow2_lo_m1))
+                r = tentative_cell_exact<T>(A.pa, su[c], sv[c], su[c - Y], su[c + Y], su[c - 1], su[c + 1], sv[c - Y], sv[c + Y],
+                                            sv[c - 1], sv[c + 1]);
+            sus[c] = r.u;
+            svs[c] = r.v;
+        }
+    };
+    auto rhs = [&](auto mode_tag, bool last_step) {
+        constexpr int MODE = decltype(mode_tag)::value;
+#pragma unroll
+        for (int k = 0; k < NC; ++k) {
+            if (!interior[k]) continue;
+            const int c = cell[k];
+            Flags fl;
+            T q = rhs_cell<T, MODE>(A.pa, sus[c - Y], sus[c + Y], svs[c - 1], svs[c + 1], fl);
+            if (MODE != DIV_EXACT && fl.raised(A.pa.m.pow2_lo_m1)) q = rhs_cell_exact<T>(A.pa, sus[c - Y], sus[c + Y], svs[c - 1], svs[c + 1]);
+            b[k] = A_::mul(A_::mul(q, A.hx), A.hy);   // (rhs * hx) * hy, :144, once per step
+            if (last_step) {
+                const int x = c / Y;
+                A.f[6][(long long)x * pitch + (c - x * Y)] = q;
+            }
+        }
+    };
+    // p neighbours of slot k in array `src`: redirected, or -- before any sweep of this launch -- the true ones
+    auto corrector = [&](auto mode_tag, const T* src, bool redirected) {
+        constexpr int MODE = decltype(mode_tag)::value;
+#pragma unroll
+        for (int k = 0; k < NC; ++k) {
+            const int c = cell[k];
+            if (c >= n) continue;
+            const int x = c / Y, y = c - x * Y;
+            T un, vn;
+            if (interior[k]) {
+                const T pxm = src[redirected ? axm[k] : c - Y], pxp = src[redirected ? axp[k] : c + Y];
+                const T pym = src[redirected ? aym[k] : c - 1], pyp = src[redirected ? ayp[k] : c + 1];
+                Flags fl;
+                UV<T> q = correct_cell<T, MODE>(A.ca, pxm, pxp, pym, pyp, sus[c], svs[c], fl);
+                if (MODE != DIV_EXACT && fl.raised(A.ca.m.pow2_lo_m1)) q = correct_cell_exact<T>(A.ca, pxm, pxp, pym, pyp, sus[c], svs[c]);
+                un = q.u;
+                vn = q.v;
+            } else {   // the y edges own their cells for all x (:236-264), the x walls the cells between (:266-294)
+                const int e = y == 0 ? BOTTOM : y == Y - 1 ? TOP : x == 0 ? LEFT : RIGHT;
+                un = A.uval[e];
+                vn = A.vval[e];
+            }
+            su[c] = un;
+            sv[c] = vn;
+        }
+    };
+    using M0 = ModeTag<DIV_EXACT>;
+    using M1 = ModeTag<(sizeof(T) == 4) ? DIV_FAST : DIV_EXACT>;
+    using M2 = ModeTag<DIV_POW2>;
+
+    T* src = pbuf0;
+    T* dst = pbuf1;
+    int g = 0;
+    for (int step = 0; step < A.S; ++step) {
+        if (mode == 2) tentative(M2{}); else if (mode == 1) tentative(M1{}); else tentative(M0{});
+        __syncthreads();
+        const bool last = step == A.S - 1;
+        if (mode == 2) rhs(M2{}, last); else if (mode == 1) rhs(M1{}, last); else rhs(M0{}, last);
+        for (int s = 0; s < A.K; ++s, ++g) {
+            if (g == 0) {   // the uploaded boundary values
+#pragma unroll
+                for (int k = 0; k < NC; ++k) {
+                    if (!interior[k]) continue;
+                    const int c = cell[k];
+                    const T sum = A_::add(A_::add(A_::add(src[c - Y], src[c + Y]), src[c + 1]), src[c - 1]);
+                    dst[c] = A_::neg_quarter(A_::sub(b[k], sum));
+                }
+            } else {
+#pragma unroll
+                for (int k = 0; k < NC; ++k) {
+                    if (!interior[k]) continue;
+                    const T sum = A_::add(A_::add(A_::add(src[axm[k]], src[axp[k]]), src[ayp[k]]), src[aym[k]]);
+                    dst[cell[k]] = A_::neg_quarter(A_::sub(b[k], sum));
+                }
+            }
+            __syncthreads();
+            T* t = src; src = dst; dst = t;
+        }
+        if (mode == 2) corrector(M2{}, src, g > 0); else if (mode == 1) corrector(M1{}, src, g > 0); else corrector(M0{}, src, g > 0);
+        __syncthreads();
+    }
+
+    // write the state back. `src` holds the final p on the interior, `dst` the state before the last sweep.
+    for (int c = tid; c < n; c += kCellThreads) {
+        const int x = c / Y, y = c - x * Y;
+        const long long o = (long long)x * pitch + y;
+        const bool xin = x >= 1 && x <= X - 2, yin = y >= 1 && y <= Y - 2;
+        T pv;
+        if (xin && yin) {
+            pv = src[c];
+            A.f[3][o] = sus[c];
+            A.f[4][o] = svs[c];
+        } else if (xin) {            // y edges, rows 1 .. X-2 (:163-175)
+            pv = y == 0 ? (bconst ? A.pval[BOTTOM] : src[c + 1]) : (tconst ? A.pval[TOP] : src[c - 1]);
+        } else if (yin) {            // x walls, columns 1 .. Y-2 (:177-188)
+            pv = x == 0 ? (lconst ? A.pval[LEFT] : src[c + Y]) : (rconst ? A.pval[RIGHT] : src[c - Y]);
+        } else {                     // corners: copy the wall cell beside them as it was one sweep earlier
+            const int inner = (x == 0 ? c + Y : c - Y) + (y == 0 ? 1 : -1);   // the interior cell diagonal to the corner
+            const T wall_prev = x == 0 ? (lconst ? A.pval[LEFT] : dst[inner]) : (rconst ? A.pval[RIGHT] : dst[inner]);
+            pv = y == 0 ? (bconst ? A.pval[BOTTOM] : wall_prev) : (tconst ? A.pval[TOP] : wall_prev);
+        }
+        A.f[2][o] = pv;
+        A.f[0][o] = su[c];
+        A.f[1][o] = sv[c];
+    }
+}
+
 }  // namespace fb
 #endif  // !FLUIDB200_HOST_EMU

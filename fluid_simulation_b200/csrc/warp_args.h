@@ -243,7 +243,7 @@ template <typename T> struct ResidentArgs {
     unsigned long long* prof;  // optional (may be NULL): cycles per phase of one tile, for measurements
 };
 
-struct ResidentPlan {
+struct ResidentPlan {   // R == 0: the one-CTA cell layout, wy = cells per thread
     int R, wy, wx, tiles_y, tiles_x, threads;
     size_t smem;
 };

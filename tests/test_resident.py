@@ -36,9 +36,14 @@ def _took_resident_path(s, calls=1):
     assert s.resident_launch_count() == calls, "solve() did not take the resident path"
 
 
+@pytest.mark.parametrize("layout", ["auto", "patch4", "patch8"])
 @pytest.mark.parametrize("name", ["cavity41_S1000_K50", "cavity41_S3_K7", "cavity41_S10_K50", "cavity67x45_S25_K30",
                                   "cavity45x131_S12_K33", "cavity41_f64_S100_K50"])
-def test_golden_fields_resident(Solver, env, golden, name):
+def test_golden_fields_resident(Solver, env, golden, name, layout):
+    """auto: grids of at most 4096 cells take the one-CTA cell layout; patch4 / patch8 force the register-patch
+    layout (4 or 8 rows per thread) that larger grids use."""
+    if layout != "auto":
+        env["FLUIDB200_RESIDENT_R"] = layout[-1]
     rec = golden[name]
     s = H.golden_case_setup(rec, Solver)
     s.migrateSolve()
@@ -104,11 +109,15 @@ def _setup_pair(Solver, X, Y, dtype, seed, p_edges="cavity", domain=None):
     (53, 129, "float32", 2, 7, "mixed"), (64, 257, "float32", 2, 6, "none"), (33, 130, "float32", 2, 9, "cavity"),
     (35, 65, "float64", 2, 5, "none"), (47, 200, "float64", 3, 6, "mixed"), (3, 3, "float32", 2, 2, "cavity"),
     (3, 700, "float32", 2, 3, "none"), (700, 3, "float32", 2, 3, "cavity"), (5, 4, "float64", 1, 2, "all_const"),
+    (64, 64, "float32", 2, 8, "none"), (63, 65, "float64", 2, 3, "mixed"), (3, 1365, "float32", 3, 2, "all_const"),
 ])
-def test_random_initial_state_and_pressure_edge_kinds(Solver, env, X, Y, dtype, S, K, p_edges):
+@pytest.mark.parametrize("layout", ["auto", "patch4"])
+def test_random_initial_state_and_pressure_edge_kinds(Solver, env, X, Y, dtype, S, K, p_edges, layout):
     """Random u, v, p, u_next, v_next (edges included: the first sweep reads the wall rows as uploaded, the
     right-hand side reads the stored edge u_next / v_next), every kind of pressure edge the resident path
     accepts, both precisions, degenerate boxes."""
+    if layout != "auto":
+        env["FLUIDB200_RESIDENT_R"] = layout[-1]
     s, o = _setup_pair(Solver, X, Y, dtype, seed=X * 1000 + Y, p_edges=p_edges)
     for q in (s, o):
         q.time_step, q.num_iterations, q.num_poisson_iterations = 1e-4, S, K
