@@ -50,6 +50,33 @@ def peaks():
         return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
 
 
+def kernel_source_hash():
+    """sha1 over the kernel sources: stamps an ncu traffic table so that it is dropped when the kernels change."""
+    import hashlib
+    h = hashlib.sha1()
+    d = os.path.join(ROOT, "fluid_simulation_b200", "csrc")
+    for f in ("warp_kernels.cuh", "warp_args.h", "kernels.cu", "api.cpp"):
+        with open(os.path.join(d, f), "rb") as fh:
+            h.update(fh.read())
+    return h.hexdigest()
+
+
+def ncu_traffic(kernels):
+    """Mean dram__bytes_read.sum + dram__bytes_write.sum per launch over `kernels`, from the newest table under
+    profiles/ whose source stamp matches the kernel sources of this tree; (None, why) otherwise."""
+    import glob
+    for path in sorted(glob.glob(os.path.join(ROOT, "profiles", "ncu_traffic_r*.json")), reverse=True):
+        try:
+            with open(path) as f:
+                table = json.load(f)
+            if table.get("source_sha1") != kernel_source_hash():
+                continue
+            return sum(table[k] for k in kernels) / len(kernels), os.path.basename(path)
+        except Exception:
+            continue
+    return None, "no ncu capture on file for these kernel sources"
+
+
 class ClockSampler:
     """nvidia-smi clocks / throttle reasons sampled DURING the timed region."""
     Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
@@ -126,15 +153,23 @@ def run_reference_arm(args):
     for _ in range(args.steps):
         _, ms, desc = cpu_reference_run(n, SWEEPS, 1)
         total_ms += ms
-    wall = time.perf_counter() - t0
     val = n * n * args.steps / (total_ms * 1e-3) / 1e9
     desc["value"] = val
     desc["unit"] = UNIT
+    try:   # the serial solver (SerialNavierStokes<float>::solve(), one core) on the same sample, once
+        sv, _, sdesc = cpu_reference_run(n, SWEEPS, 1, kind="serial")
+        sdesc.update({"value": sv, "unit": UNIT})
+        desc["serial"] = sdesc
+    except Exception as ex:
+        desc["serial"] = {"value": None, "sample": repr(ex)}
+    wall = time.perf_counter() - t0
     print(json.dumps({
         "impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": total_ms / args.steps,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": f"cavity {GRID}x{GRID} fp32, {SWEEPS} Poisson sweeps/step",
+        "config": {"workload": f"cavity {GRID}x{GRID} fp32, {SWEEPS} Poisson sweeps/step -- timed on a {n}x{n} sample of it "
+                               f"(same spacing, dt and sweeps; per-cell throughput; the {GRID}^2 grid itself needs "
+                               f"{GRID * GRID * 92 / 1e9:.0f} GB of the reference's 92-byte cells and ~450 s per step)",
                    "sample": desc["sample"], "wall_s": round(wall, 2)},
         "cpu_baseline": desc,
         "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
@@ -213,30 +248,61 @@ def run_single(args):
     kernel = f"jacobi_fast_kernel<float,4,{KMAX}>"   # + the edge and wall kernels of the same split launch
     # ncu dram bytes per launch for exactly these kernels and this grid, when captures are on file: the mean over
     # the launches of one step (same rule as step_poisson: launch i takes ceil(left / launches left) sweeps)
-    traffic = None
-    try:
-        with open(os.path.join(ROOT, "profiles", "ncu_traffic_r1.json")) as f:
-            table = json.load(f)
-        left, per_launch = SWEEPS, []
-        for i in range(n_launch):
-            k = -(-left // (n_launch - i))
-            left -= k
-            per_launch.append(table[f"jacobi_fast_kernel<float,4,{k}>@{X}x{Y}"])
-        traffic = sum(per_launch) / len(per_launch)
-    except Exception:
-        pass
-    roofline = {"bound": "hbm", "kernel": kernel, "achieved": achieved, "peak": peak,
-                "unit": "GB/s", "frac": achieved / peak, "traffic": traffic,
-                "dram_GBps": traffic / (jac_launch_ms * 1e-3) / 1e9 if traffic else None,
-                "dram_frac": traffic / (jac_launch_ms * 1e-3) / 1e9 / peak if traffic else None,
+    left, per_launch = SWEEPS, []
+    for i in range(n_launch):
+        k = -(-left // (n_launch - i))
+        left -= k
+        per_launch.append(f"jacobi_fast_kernel<float,4,{k}>@{X}x{Y}")
+    traffic, traffic_src = ncu_traffic(per_launch)
+    # A launch of k blocked sweeps must move each cell's p (read + write) and rhs (read) once: 12 B/cell per LAUNCH is the
+    # compulsory DRAM traffic, and `frac` is that over the launch time over the measured copy peak -- a physical fraction
+    # (<= 1). The algorithmic figure (12 B/cell per SWEEP, section 8(d) of SURVEY.md) is k times larger and is kept beside it.
+    compulsory = 12.0 * cells
+    dram_ach = compulsory / (jac_launch_ms * 1e-3) / 1e9
+    roofline = {"bound": "hbm", "kernel": kernel, "achieved": dram_ach, "peak": peak, "unit": "GB/s", "frac": dram_ach / peak,
+                "traffic": traffic, "traffic_source": traffic_src,
+                "traffic_GBps": traffic / (jac_launch_ms * 1e-3) / 1e9 if traffic else None,
+                "traffic_frac": traffic / (jac_launch_ms * 1e-3) / 1e9 / peak if traffic else None,
+                "compulsory_bytes_per_launch": compulsory,
+                "algorithmic": {"bytes_per_launch": alg_bytes, "achieved": achieved, "frac": achieved / peak,
+                                "note": "12 B/cell/sweep x sweeps per launch / launch time: what a sweep-at-a-time kernel "
+                                        "would have to move; exceeds the peak by the blocking depth, by design"},
                 "peak_source": peak_src, "sweeps_per_launch": KMAX, "launches_per_step": n_launch, "mean_depth": mean_depth,
-                "launch_ms": jac_launch_ms, "algorithmic_bytes_per_launch": alg_bytes,
+                "launch_ms": jac_launch_ms,
                 "gcell_sweeps_per_s": cells * SWEEPS * args.steps / (jac_ms * 1e-3) / 1e9,
                 "share_of_step": jac_ms / total_ms,
                 "other_kernels": {"predictor_ms": pred_ms, "predictor_GBps": 20.0 * cells / (pred_ms * 1e-3) / 1e9,
-                                  "corrector_ms": corr_ms, "corrector_GBps": 20.0 * cells / (corr_ms * 1e-3) / 1e9},
-                "note": "achieved = algorithmic bytes (12 B/cell/sweep x sweeps_per_launch) / launch time; with temporal "
-                        "blocking the DRAM traffic per launch is ~12 B/cell, so frac > 1 is expected; see profiles/"}
+                                  "predictor_frac": 20.0 * cells / (pred_ms * 1e-3) / 1e9 / peak,
+                                  "corrector_ms": corr_ms, "corrector_GBps": 20.0 * cells / (corr_ms * 1e-3) / 1e9,
+                                  "corrector_frac": 20.0 * cells / (corr_ms * 1e-3) / 1e9 / peak},
+                "whole_step": {"bytes": (40.0 + 12.0 * n_launch) * cells, "GBps": (40.0 + 12.0 * n_launch) * cells / (total_ms / args.steps * 1e-3) / 1e9,
+                               "frac": (40.0 + 12.0 * n_launch) * cells / (total_ms / args.steps * 1e-3) / 1e9 / peak,
+                               "note": "compulsory DRAM bytes of a step (20 + 12 per Jacobi launch + 20 B/cell) over the step time"}}
+
+    # ---- the same step with a spacing that is NOT a power of two (the reference's own h = 1/(n-1) is not): the general
+    # division-free arithmetic with its flagged exact fallback, and the rhs scaling inside the sweeps
+    general = None
+    if not os.environ.get("FLUIDB200_SKIP_GENERAL"):
+        saved = os.environ.get("FLUIDB200_DIVMODE")
+        os.environ["FLUIDB200_DIVMODE"] = "1"
+        try:
+            step(); torch.cuda.synchronize()
+            g0, g1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            gsteps = max(2, min(args.steps, 4))
+            g0.record(stream)
+            for _ in range(gsteps):
+                step()
+            g1.record(stream)
+            torch.cuda.synchronize()
+            gms = g0.elapsed_time(g1) / gsteps
+            general = {"ms_per_step": gms, "value": cells / (gms * 1e-3) / 1e9, "unit": UNIT, "steps": gsteps,
+                       "what": "FLUIDB200_DIVMODE=1: division-free arithmetic for any spacing (flagged exact fallback) in "
+                               "predictor and corrector; the Jacobi sweeps are the same kernels"}
+        finally:
+            if saved is None:
+                os.environ.pop("FLUIDB200_DIVMODE", None)
+            else:
+                os.environ["FLUIDB200_DIVMODE"] = saved
 
     # ---- e2e: host buffers in, host buffers out, every step ---------------------------------
     e2e_steps = max(1, min(args.steps, int(os.environ.get("FLUIDB200_E2E_STEPS", 3))))
@@ -309,35 +375,71 @@ def run_single(args):
         s2.close()
     s.close()
 
-    # ---- BASELINE.json configs[1], for the record: 1000 x 1000, 1000 timesteps, 50 sweeps each (the shape the
-    # reference publishes 1.23 min for on an RTX 2080 Super), launch-bound, so replayed as CUDA graphs. A stable
-    # dt is used (the reference's dt = 0.001 diverges to NaN at this resolution).
-    small = None
-    if not os.environ.get("FLUIDB200_SKIP_SMALL"):
-        n = 1000
-        sm = ParallelNavierStokes(n, n, 1.0, 1.0, dtype=np.float32)   # on its own stream: the legacy
-        sm.time_step = float(np.float32(0.125) * np.float32(1.0 / (n - 1)) ** 2 / np.float32(0.1))  # stream cannot be captured
-        sm.num_poisson_iterations, sm.num_iterations = 50, 1000
-        small = {"grid": f"{n}x{n}", "timesteps": 1000, "sweeps_per_step": 50, "dt": sm.time_step,
-                 "timing": "host clock around solve() + synchronize()"}
-        for graph in (False, True):
+    # ---- BASELINE.json configs[0] and [1]: 41 x 41 and 1000 x 1000, 1000 timesteps x 50 sweeps (the shapes of the reference's
+    # own test and of its published numbers). The default path (resident solver: one cooperative launch per solve()), and
+    # the streaming kernels with and without CUDA-graph replay beside it. 1000^2 uses a stable dt (the reference's dt = 0.001
+    # diverges to NaN at that resolution); 41^2 the reference's defaults.
+    def small_grid(n, dt, reference_cuda_steps):
+        rec = {"grid": f"{n}x{n}", "timesteps": 1000, "sweeps_per_step": 50, "dt": dt,
+               "timing": "host clock around solve() + synchronize(), as fluid_cpp/cuda_main.cu:96-99"}
+        sm = ParallelNavierStokes(n, n, 1.0, 1.0, dtype=np.float32)   # (on its own stream: the legacy stream cannot be captured)
+        sm.time_step, sm.num_poisson_iterations = dt, 50
+        for name, resident, graph in (("resident", True, False), ("streaming_graph", False, True), ("streaming_plain", False, False)):
+            sm.set_resident(resident)
             sm.set_use_graph(graph)
             sm.upload_cavity(LID)
             sm.num_iterations = 10
             sm.solve(); sm.synchronize()      # warm-up (and graph capture)
+            sm.upload_cavity(LID)
             sm.num_iterations = 1000
+            k0 = sm.launch_count()
             t0 = time.perf_counter()
             sm.solve()
             sm.synchronize()
             ms = (time.perf_counter() - t0) * 1e3
-            small["ms_total_graph" if graph else "ms_total_plain"] = ms
-            small["gcell_updates_per_s_graph" if graph else "gcell_updates_per_s_plain"] = n * n * 1000 / (ms * 1e-3) / 1e9
+            rec[name] = {"ms_total": ms, "us_per_step": ms, "gcell_updates_per_s": n * n * 1000 / (ms * 1e-3) / 1e9,
+                         "kernel_launches": sm.launch_count() - k0}
+            if name == "resident":
+                rec["took_resident_path"] = sm.resident_launch_count() == 2
+                rec["_v"] = sm.device_field("v")
         sm.close()
+        rec["ms_total"] = rec["resident"]["ms_total"]
+        rec["gcell_updates_per_s"] = rec["resident"]["gcell_updates_per_s"]
+        # the reference's own code on this box: CPU (serial = 1 core; threaded = its fixed 8 threads) and its CUDA solver
+        try:
+            import oracle
+            cpu_steps = 1000 if n <= 64 else 2
+            for kind in ("serial", "threaded"):
+                out, ms = oracle.ref_solve(kind, n, n, dt=dt, K=50, S=cpu_steps, want=("v",) if cpu_steps == 1000 else ())
+                rec["reference_cpu_" + kind] = {"ms_total": ms * 1000 / cpu_steps, "steps_run": cpu_steps,
+                                                "cores": 1 if kind == "serial" else 8, "extrapolated": cpu_steps != 1000}
+                if kind == "serial" and cpu_steps == 1000:
+                    rec["v_bit_equal_to_reference_serial"] = bool(np.array_equal(out["v"].view(np.uint32), rec["_v"].view(np.uint32)))
+            if oracle.have_ref_cuda():
+                ms, _ = oracle.ref_cuda_cavity(n, n, dt=dt, K=50, S=reference_cuda_steps, warmup_steps=2)
+                rec["reference_cuda_sm100a"] = {
+                    "ms_total": ms * 1000 / reference_cuda_steps, "steps_run": reference_cuda_steps,
+                    "extrapolated": reference_cuda_steps != 1000,
+                    "what": "the reference's ParallelNavierStokes<float> (fluid_cpp/cuda/ParallelNavierStokes.cu) compiled unmodified "
+                            "with nvcc -gencode arch=compute_100a,code=sm_100a; solve() + cudaDeviceSynchronize() after migrateHostToDevice()"}
+        except Exception as ex:
+            rec["reference_error"] = repr(ex)
+        rec.pop("_v", None)
+        return rec
+
+    small = small0 = None
+    if not os.environ.get("FLUIDB200_SKIP_SMALL"):
+        small0 = small_grid(41, 0.001, 1000)
+        small = small_grid(1000, float(np.float32(0.125) * np.float32(1.0 / 999) ** 2 / np.float32(0.1)), 5)
 
     # ---- cpu baseline: bounded sample of the same workload on the host cores ---------------
     try:
-        cv, _, cdesc = cpu_reference_run(int(os.environ.get("FLUIDB200_CPU_GRID", 1536)), SWEEPS, 2)
+        ngrid = int(os.environ.get("FLUIDB200_CPU_GRID", 1536))
+        cv, _, cdesc = cpu_reference_run(ngrid, SWEEPS, 2)
         cdesc.update({"value": cv, "unit": UNIT})
+        sv, _, sdesc = cpu_reference_run(ngrid // 2, SWEEPS, 1, kind="serial")
+        sdesc.update({"value": sv, "unit": UNIT})
+        cdesc["serial"] = sdesc
     except Exception as ex:  # the checker is optional for the measurement itself
         cdesc = {"value": None, "unit": UNIT, "cores": 0, "kind": "unavailable", "sample": repr(ex)}
 
@@ -350,9 +452,9 @@ def run_single(args):
                    "division_mode": os.environ.get("FLUIDB200_DIVMODE", "2 (power-of-two spacing: exact scalings; "
                                                    "FLUIDB200_DIVMODE=1 forces the general division-free mode)"),
                    "l2": "fields are 1.07 GB each, >> 126 MB L2, no flush needed",
-                   "effective_GBps_step": (40 + 12 * SWEEPS) * cells * args.steps / (total_ms * 1e-3) / 1e9},
+                   "algorithmic_GBps_step": (40 + 12 * SWEEPS) * cells * args.steps / (total_ms * 1e-3) / 1e9},
         "roofline": roofline, "cpu_baseline": cdesc, "e2e": e2e, "gpu_launches": int(launches), "clocks": clk,
-        "config1_1000x1000": small,
+        "headline_general_spacing": general, "config0_41x41": small0, "config1_1000x1000": small,
     }
 
 

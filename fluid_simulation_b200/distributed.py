@@ -355,6 +355,7 @@ def bench_distributed(args, grid, sweeps, kmax, prm, metric, unit):
     total_ms = float(ms.item())
     launches = torch.tensor([s.launches - l0], device=s.device)
     dist.all_reduce(launches)
+    launches_total = int(launches.item())
     cells = X * Y
 
     # e2e: every step each rank uploads its owned u, v, p from pinned host memory and reads them back
@@ -384,6 +385,60 @@ def bench_distributed(args, grid, sweeps, kmax, prm, metric, unit):
     dist.all_reduce(finite, op=dist.ReduceOp.MIN)
     assert int(finite.item()) == 1, "non-finite field after the e2e steps"
     halo_per_step = (s.halo_bytes - hb0) / max(1, args.steps + e2e_steps + 1)
+    weak_rows = s.x1 - s.x0
+    weak_desc = f"cavity {X}x{Y} fp32 ({weak_rows} rows per GPU, x-slabs), {sweeps} Poisson sweeps/step"
+
+    # ---- strong scaling beside it (BASELINE.json configs[3]): a FIXED 32768^2 grid cut over the same ranks, and the same
+    # grid on one GPU (rank 0 alone, the others wait), so that one invocation yields the speed-up
+    strong_rec = None
+    if not strong and not os.environ.get("FLUIDB200_SKIP_STRONG"):
+        del s, host
+        torch.cuda.empty_cache()
+        SX = SY = int(os.environ.get("FLUIDB200_STRONG_GRID", 32768))
+        ssteps = max(2, min(args.steps, 5))
+
+        def timed(solver, n):
+            for _ in range(2):
+                solver.step()
+            torch.cuda.synchronize()
+            a0, a1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a0.record(solver.main)
+            for _ in range(n):
+                solver.step()
+            a1.record(solver.main)
+            torch.cuda.synchronize()
+            return a0.elapsed_time(a1) / n
+
+        ss = SlabSolver(SX, SY, float(SX - 1), float(SY - 1), np.float32, rank=rank, world=world, device=f"cuda:{local}", kmax=kmax)
+        ss.time_step, ss.kinematic_viscosity, ss.density = prm["dt"], prm["nu"], prm["rho"]
+        ss.num_poisson_iterations = sweeps
+        ss.init_cavity(prm["lid"])
+        dist.barrier()
+        t = torch.tensor([timed(ss, ssteps)], device=ss.device)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        strong_ms = float(t.item())
+        srows = ss.x1 - ss.x0
+        del ss
+        torch.cuda.empty_cache()
+        one_ms = None
+        if rank == 0:
+            try:
+                s1 = SlabSolver(SX, SY, float(SX - 1), float(SY - 1), np.float32, rank=0, world=1, device=f"cuda:{local}", kmax=kmax)
+                s1.time_step, s1.kinematic_viscosity, s1.density = prm["dt"], prm["nu"], prm["rho"]
+                s1.num_poisson_iterations = sweeps
+                s1.init_cavity(prm["lid"])
+                one_ms = timed(s1, max(2, ssteps // 2))
+                del s1
+                torch.cuda.empty_cache()
+            except Exception as ex:   # (e.g. another tenant's memory on the device)
+                one_ms = None
+                print(f"strong scaling: single-GPU {SX}^2 run failed: {ex!r}", file=__import__("sys").stderr)
+        dist.barrier()
+        strong_rec = {"grid": f"{SX}x{SY}", "rows_per_gpu": srows, "steps": ssteps, "ms_per_step": strong_ms,
+                      "gcell_updates_per_s": SX * SY / (strong_ms * 1e-3) / 1e9,
+                      "one_gpu_ms_per_step": one_ms, "speedup_vs_one_gpu": (one_ms / strong_ms) if one_ms else None,
+                      "efficiency": (one_ms / strong_ms / world) if one_ms else None,
+                      "timing": "CUDA events on each rank's launching stream, max over ranks; one-GPU figure: rank 0 alone, same build"}
     dist.destroy_process_group()
     if rank != 0:
         return None
@@ -391,15 +446,15 @@ def bench_distributed(args, grid, sweeps, kmax, prm, metric, unit):
         "metric": metric, "value": cells * args.steps / (total_ms * 1e-3) / 1e9, "unit": unit, "n_gpus": world,
         "steps": args.steps, "warmup": warm, "ms_per_step": total_ms / args.steps, "higher_is_better": True,
         "scaling": "strong" if strong else "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": f"cavity {X}x{Y} fp32 ({s.x1 - s.x0} rows per GPU, x-slabs), {sweeps} Poisson sweeps/step",
+        "config": {"workload": weak_desc, "strong": strong_rec,
                    "dt": prm["dt"], "nu": prm["nu"], "rho": prm["rho"], "hx": 1.0, "hy": 1.0, "sweeps_per_launch": kmax,
                    "host_issue_ms_per_step": t_issue / args.steps * 1e3,
                    "parallelism": f"x-slabs x{world}, halo depth {kmax + 1}, NCCL send/recv overlapped with interior sweeps",
                    "halo_bytes_per_rank_per_step": halo_per_step,
-                   "l2": f"fields are {(s.x1 - s.x0) * Y * 4 / 1e9:.2f} GB per GPU, >> 126 MB L2, no flush needed"},
+                   "l2": f"fields are {weak_rows * Y * 4 / 1e9:.2f} GB per GPU, >> 126 MB L2, no flush needed"},
         "roofline": None, "cpu_baseline": None,
         "e2e": {"value": cells * e2e_steps / e2e_s / 1e9, "unit": unit, "h2d_bytes_per_step": 3 * cells * 4,
                 "d2h_bytes_per_step": 3 * cells * 4, "steps": e2e_steps, "ms_per_step": e2e_s / e2e_steps * 1e3,
                 "api": "per rank: copy owned u,v,p from pinned host + SlabSolver.step() + copy back"},
-        "gpu_launches": int(launches.item()), "clocks": None,
+        "gpu_launches": int(launches_total), "clocks": None,
     }

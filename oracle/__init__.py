@@ -26,6 +26,7 @@ import numpy as np
 HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_ORACLE = os.path.join(HERE, "liboracle.so")
 LIB_REF = os.path.join(HERE, "_ref", "libref_fluid.so")
+LIB_REF_CUDA = os.path.join(HERE, "_ref", "libref_cuda.so")
 REFERENCE_ROOT = "/root/reference/fluid_cpp"
 
 
@@ -34,6 +35,8 @@ def build(ref: bool = True) -> None:
     subprocess.check_call(["make", "-s", "-C", HERE, "oracle"])
     if ref and os.path.isdir(os.path.join(REFERENCE_ROOT, "cpp")):
         subprocess.check_call(["make", "-s", "-C", HERE, "ref"])
+        if os.path.exists(os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")):
+            subprocess.check_call(["make", "-s", "-C", HERE, "ref_cuda"], stderr=subprocess.DEVNULL)
 
 
 def have_ref() -> bool:
@@ -209,3 +212,29 @@ def ref_solve(kind, X, Y, *, wx=1.0, wy=1.0, dt=0.001, nu=0.1, rho=1.0, K=50, S=
     if rc != 0:
         raise RuntimeError(f"ref_solve returned {rc}")
     return out, ms.value
+
+
+# ------------------------------------------------------------------------------------------
+def have_ref_cuda() -> bool:
+    return os.path.exists(LIB_REF_CUDA)
+
+
+_ref_cuda = None
+
+
+def ref_cuda_cavity(X, Y, *, wx=1.0, wy=1.0, dt=0.001, nu=0.1, rho=1.0, K=50, S=1000, warmup_steps=2, want_v=False):
+    """The reference's own CUDA solver, ``ParallelNavierStokes<float>`` compiled unmodified for sm_100a
+    (``oracle/_ref/libref_cuda.so``), on a lid-driven cavity: returns ``(elapsed_ms, v or None)``; elapsed
+    covers ``solve(); cudaDeviceSynchronize()`` like ``fluid_cpp/cuda_main.cu:96-99``, after
+    ``migrateHostToDevice()``. A same-box comparison for bench.py, never an oracle."""
+    global _ref_cuda
+    if _ref_cuda is None:
+        _ref_cuda = C.CDLL(LIB_REF_CUDA)
+        _ref_cuda.ref_cuda_cavity.restype = C.c_int
+        _ref_cuda.ref_cuda_cavity.argtypes = [C.c_int, C.c_int] + [C.c_double] * 5 + [C.c_int] * 3 + [C.c_void_p, C.POINTER(C.c_double)]
+    v = np.zeros((X, Y), np.float32) if want_v else None
+    ms = C.c_double(0.0)
+    rc = _ref_cuda.ref_cuda_cavity(X, Y, wx, wy, dt, nu, rho, K, S, warmup_steps, v.ctypes.data if want_v else None, C.byref(ms))
+    if rc != 0:
+        raise RuntimeError(f"ref_cuda_cavity: CUDA error {rc}")
+    return ms.value, v
