@@ -312,13 +312,18 @@ def run_single(args):
     for i in range(3):
         fields[i] = host[i].data_ptr()
 
-    def e2e_step():
+    io = (C.c_void_p * 3)(*[host[i].data_ptr() for i in range(3)])
+
+    def e2e_step():       # the reference-facing call: migrateSolve on host arrays (one timestep, in place)
+        _lib.check(lib, lib.fluidb200_migrate_solve(h, io, io))
+
+    def e2e_step_serial():   # the same work as three separate calls: upload, solve, download x 3 (no overlap)
         _lib.check(lib, lib.fluidb200_upload(h, fields, None, None))
         _lib.check(lib, lib.fluidb200_solve(h))
         for i in range(3):
             _lib.check(lib, lib.fluidb200_download(h, i, host[i].data_ptr()))
 
-    e2e_step()  # warm-up
+    e2e_step()  # warm-up (allocates the pipeline's buffers)
     torch.cuda.synchronize()
     t0 = time.perf_counter()
     for _ in range(e2e_steps):
@@ -327,8 +332,19 @@ def run_single(args):
     e2e_s = time.perf_counter() - t0
     e2e = {"value": cells * e2e_steps / e2e_s / 1e9, "unit": UNIT, "h2d_bytes_per_step": 3 * cells * 4,
            "d2h_bytes_per_step": 3 * cells * 4, "steps": e2e_steps, "ms_per_step": e2e_s / e2e_steps * 1e3,
-           "api": "fluidb200_upload(u,v,p pinned host) + fluidb200_solve(1 step) + fluidb200_download(u,v,p)"}
+           "link_GBps_each_way": 3 * cells * 4 / (e2e_s / e2e_steps) / 1e9,
+           "api": "fluidb200_migrate_solve(u,v,p pinned host -> u,v,p pinned host), one timestep per call: upload, compute and "
+                  "download pipelined over row chunks with K+2 recomputed halo rows (csrc/api.cpp)"}
     assert bool(torch.isfinite(host[0]).all()), "non-finite field after the e2e steps"
+    e2e_step_serial()
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    for _ in range(e2e_steps):
+        e2e_step_serial()
+    torch.cuda.synchronize()
+    ser_s = time.perf_counter() - t0
+    e2e["separate_calls"] = {"value": cells * e2e_steps / ser_s / 1e9, "unit": UNIT, "ms_per_step": ser_s / e2e_steps * 1e3,
+                             "api": "fluidb200_upload + fluidb200_solve + 3 x fluidb200_download, nothing overlapped (round 1's e2e)"}
 
     # The same calls from TWO host threads, each with its own solver handle, stream and pinned buffers (two
     # independent simulations in flight): the upload of one overlaps the download of the other on the full-duplex
@@ -350,11 +366,9 @@ def run_single(args):
         _lib.check(lib, lib.fluidb200_set_stream(h, own.cuda_stream))
 
         def worker(handle, flds, hst, n):
+            ptrs = (C.c_void_p * 3)(*[hst[i].data_ptr() for i in range(3)])
             for _ in range(n):
-                _lib.check(lib, lib.fluidb200_upload(handle, flds, None, None))
-                _lib.check(lib, lib.fluidb200_solve(handle))
-                for i in range(3):
-                    _lib.check(lib, lib.fluidb200_download(handle, i, hst[i].data_ptr()))
+                _lib.check(lib, lib.fluidb200_migrate_solve(handle, ptrs, ptrs))
 
         worker(s2._h, fields2, host2, 1)  # warm-up of the second handle
         torch.cuda.synchronize()
@@ -370,7 +384,7 @@ def run_single(args):
         pair_s = time.perf_counter() - t0
         e2e["two_instances"] = {"value": cells * 2 * per / pair_s / 1e9, "unit": UNIT, "steps": 2 * per,
                                 "ms_per_step": pair_s / (2 * per) * 1e3,
-                                "api": "the same three calls from two host threads, one solver handle each"}
+                                "api": "the same call from two host threads, one solver handle each"}
         assert bool(torch.isfinite(host2[0]).all())
         s2.close()
     s.close()

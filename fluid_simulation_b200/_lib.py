@@ -65,6 +65,7 @@ _SIGS = {
     "fluidb200_step_corrector": (C.c_int, [C.c_void_p]),
     "fluidb200_synchronize": (C.c_int, [C.c_void_p]),
     "fluidb200_download": (C.c_int, [C.c_void_p, C.c_int, C.c_void_p]),
+    "fluidb200_migrate_solve": (C.c_int, [C.c_void_p, C.POINTER(C.c_void_p), C.POINTER(C.c_void_p)]),
     "fluidb200_get_slab": (C.c_int, [C.c_void_p, C.POINTER(Slab)]),
     "fluidb200_field_ptr": (C.c_void_p, [C.c_void_p, C.c_int]),
     "fluidb200_set_stream": (C.c_int, [C.c_void_p, C.c_void_p]),

@@ -433,6 +433,13 @@ struct fluidb200_solver {
     bool res_planned = false, res_ok = false;
     fb::ResidentPlan res_plan = {};
     void* res_scratch = nullptr;      // device: tile counters + 4 values for the corner rule
+    // chunk pipeline of fluidb200_migrate_solve: copy streams, events, output arrays, a chunk's pressure ping-pong pair
+    void* pipe_up = nullptr;
+    void* pipe_down = nullptr;
+    void* pipe_out[2] = {nullptr, nullptr};   // new u, v (whole grid): the inputs must stay intact for the next chunk's halo
+    void* pipe_p[2] = {nullptr, nullptr};
+    size_t pipe_p_rows = 0;
+    std::vector<void*> pipe_ev;
     int64_t resident_launches = 0;
 };
 
@@ -795,6 +802,11 @@ extern "C" int fluidb200_destroy(fluidb200_solver* s) {
     for (int i = 0; i < FLUIDB200_NUM_FIELDS; ++i)
         if (s->f[i]) fbk::be_free(s->f[i]);
     if (s->res_scratch) fbk::be_free(s->res_scratch);
+    for (void* p : {s->pipe_out[0], s->pipe_out[1], s->pipe_p[0], s->pipe_p[1]})
+        if (p) fbk::be_free(p);
+    for (void* e : s->pipe_ev) fbk::be_event_destroy(e);
+    if (s->pipe_up) fbk::be_stream_destroy(s->pipe_up);
+    if (s->pipe_down) fbk::be_stream_destroy(s->pipe_down);
     if (s->own_stream && s->stream) fbk::be_stream_destroy(s->stream);
     delete s;
     return 0;
@@ -958,6 +970,159 @@ extern "C" int fluidb200_download(fluidb200_solver* s, int field, void* out) {
     const size_t row = (size_t)s->Y * s->esize;
     BE_CHECK(fbk::be_memcpy2d_async(out, row, s->f[src], (size_t)s->pitch * s->esize, row, s->X, fbk::D2H, s->stream),
              "download");
+    BE_CHECK(fbk::be_stream_sync(s->stream), "download");
+    return 0;
+}
+
+// ---- migrateSolve with host buffers: upload, timesteps, download -----------------------------------
+namespace {
+
+// One timestep of a LARGE grid, pipelined over row chunks so that the three legs -- host -> device,
+// compute, device -> host -- of different chunks run at the same time and the link works in both
+// directions at once. Rows [a, b) after one timestep depend on rows [a - H, b + H) before it with
+// H = K + 2 (K sweeps reach K rows, the corrector one more, the predictor's u_next another), so a chunk
+// is computed on its rows plus H halo rows from launches whose valid range shrinks sweep by sweep; the
+// halo is recomputed (2H / chunk rows of extra arithmetic, hidden behind the transfers), never sent twice:
+// every input row crosses the link once, into the solver's own u, v, p, which stay intact as inputs;
+// results go to other arrays (new u, v: two extra arrays; new p: p_next) and the roles are swapped at the end.
+int migrate_solve_pipelined(fluidb200_solver* s, const void* const host_in[3], void* const host_out[3], int chunk_rows) {
+    const int X = s->X, Y = s->Y, K = s->K, H = K + 2;
+    const size_t es = s->esize, pitchB = (size_t)s->pitch * es, rowB = (size_t)Y * es;
+    const int nchunks = (X + chunk_rows - 1) / chunk_rows;
+    // resources (kept with the solver)
+    if (!s->pipe_up && (fbk::be_stream_create(&s->pipe_up) || fbk::be_stream_create(&s->pipe_down))) return fail_backend("pipeline streams");
+    for (int i = 0; i < 2; ++i)
+        if (!s->pipe_out[i]) {
+            BE_CHECK(fbk::be_malloc(&s->pipe_out[i], field_bytes(s)), "pipeline output arrays");
+            BE_CHECK(fbk::be_memset_async(s->pipe_out[i], 0, field_bytes(s), s->stream), "pipeline output arrays");
+        }
+    const size_t prow = (size_t)chunk_rows + 2 * H;
+    if (s->pipe_p_rows < prow) {
+        for (int i = 0; i < 2; ++i) {
+            if (s->pipe_p[i]) fbk::be_free(s->pipe_p[i]);
+            s->pipe_p[i] = nullptr;
+            BE_CHECK(fbk::be_malloc(&s->pipe_p[i], prow * pitchB), "pipeline pressure buffers");
+        }
+        s->pipe_p_rows = prow;
+    }
+    while ((int)s->pipe_ev.size() < 2 * nchunks + 2) {
+        void* e = nullptr;
+        BE_CHECK(fbk::be_event_create(&e), "pipeline events");
+        s->pipe_ev.push_back(e);
+    }
+    void* const up = s->pipe_up;
+    void* const down = s->pipe_down;
+    void* const comp = s->stream;
+    // the copy streams start after whatever the solver's stream was doing (and the output arrays' clearing)
+    void* ev0 = s->pipe_ev[2 * nchunks];
+    BE_CHECK(fbk::be_event_record(ev0, comp), "pipeline");
+    BE_CHECK(fbk::be_stream_wait_event(up, ev0), "pipeline");
+    BE_CHECK(fbk::be_stream_wait_event(down, ev0), "pipeline");
+
+    char* const fU = (char*)s->f[FLUIDB200_FIELD_U];
+    char* const fV = (char*)s->f[FLUIDB200_FIELD_V];
+    char* const fP = (char*)s->f[FLUIDB200_FIELD_P];
+    char* const fUS = (char*)s->f[FLUIDB200_FIELD_U_NEXT];
+    char* const fVS = (char*)s->f[FLUIDB200_FIELD_V_NEXT];
+    char* const fR = (char*)s->f[FLUIDB200_FIELD_RHS];
+    char* const oP = (char*)s->f[FLUIDB200_FIELD_P_NEXT];
+    char* const oU = (char*)s->pipe_out[0];
+    char* const oV = (char*)s->pipe_out[1];
+    char* const dev_in[3] = {fU, fV, fP};
+    char* const dev_out[3] = {oU, oV, oP};
+    const int kmax = poisson_kmax(s);
+    const int nlaunch = (K + kmax - 1) / kmax;
+    const long long k0 = fbk::be_kernel_count();
+    int uploaded = 0;   // rows [0, uploaded) are on their way to the device
+    for (int c = 0; c < nchunks; ++c) {
+        const int a = c * chunk_rows, b = std::min(X, a + chunk_rows);
+        const int lo = std::max(0, a - H), hi = std::min(X, b + H);
+        // 1. host -> device: the rows this chunk needs and no earlier chunk brought
+        if (hi > uploaded) {
+            for (int f = 0; f < 3; ++f)
+                BE_CHECK(fbk::be_memcpy2d_async(dev_in[f] + (size_t)uploaded * pitchB, pitchB, (const char*)host_in[f] + (size_t)uploaded * rowB,
+                                                rowB, rowB, (size_t)(hi - uploaded), fbk::H2D, up), "pipeline upload");
+            uploaded = hi;
+        }
+        BE_CHECK(fbk::be_event_record(s->pipe_ev[2 * c], up), "pipeline");
+        BE_CHECK(fbk::be_stream_wait_event(comp, s->pipe_ev[2 * c]), "pipeline");
+        // 2. one timestep on rows [a, b), computed on the slab [lo, hi)
+        fluidb200_slab g;
+        fill_slab(s, &g);
+        g.row0 = lo;
+        g.rows = hi - lo;
+        const size_t off = (size_t)lo * pitchB;
+        const int star_lo = lo == 0 ? 0 : lo + 1, star_hi = hi == X ? X : hi - 1;
+        const int rhs_lo = lo == 0 ? 0 : lo + 2, rhs_hi = hi == X ? X : hi - 2;
+        int rc = fluidb200_predictor(&g, fU + off, fV + off, fUS + off, fVS + off, fR + off, s->dt, s->nu, s->rho, star_lo, star_hi,
+                                     rhs_lo, rhs_hi, comp);
+        if (rc) return rc;
+        const char* src = fP + off;   // the first launch reads the pristine p; then the chunk's own pair
+        int done = 0, left = K, which = 0;
+        for (int i = 0; i < nlaunch; ++i) {
+            const int k = (left + (nlaunch - i) - 1) / (nlaunch - i);
+            done += k;
+            left -= k;
+            const int out_lo = lo == 0 ? 0 : lo + 1 + done, out_hi = hi == X ? X : hi - 1 - done;
+            rc = fluidb200_poisson_sweeps(&g, src, s->pipe_p[which], fR + off, &s->edges[2], nullptr, k, out_lo, out_hi, comp);
+            if (rc) return rc;
+            src = (const char*)s->pipe_p[which];
+            which ^= 1;
+        }
+        rc = fluidb200_corrector(&g, src, fUS + off, fVS + off, oU + off, oV + off, &s->edges[0], &s->edges[1], nullptr, nullptr, s->dt, s->rho,
+                                 a, b, comp);
+        if (rc) return rc;
+        // the chunk's final p joins the whole-grid array (rows [a, b); device to device)
+        BE_CHECK(fbk::be_memcpy_async(oP + (size_t)a * pitchB, src + (size_t)(a - lo) * pitchB, (size_t)(b - a) * pitchB, fbk::D2D, comp),
+                 "pipeline p");
+        BE_CHECK(fbk::be_event_record(s->pipe_ev[2 * c + 1], comp), "pipeline");
+        // 3. device -> host
+        BE_CHECK(fbk::be_stream_wait_event(down, s->pipe_ev[2 * c + 1]), "pipeline");
+        for (int f = 0; f < 3; ++f)
+            if (host_out[f])
+                BE_CHECK(fbk::be_memcpy2d_async((char*)host_out[f] + (size_t)a * rowB, rowB, dev_out[f] + (size_t)a * pitchB, pitchB, rowB,
+                                                (size_t)(b - a), fbk::D2H, down), "pipeline download");
+    }
+    s->launches += fbk::be_kernel_count() - k0;
+    // the new state takes the place of the old one
+    std::swap(s->f[FLUIDB200_FIELD_U], s->pipe_out[0]);
+    std::swap(s->f[FLUIDB200_FIELD_V], s->pipe_out[1]);
+    std::swap(s->f[FLUIDB200_FIELD_P], s->f[FLUIDB200_FIELD_P_NEXT]);
+    s->p_next_is_p = true;
+    drop_graphs(s);   // (captured graphs hold the old pointers)
+    void* evd = s->pipe_ev[2 * nchunks + 1];
+    BE_CHECK(fbk::be_event_record(evd, down), "pipeline");
+    BE_CHECK(fbk::be_stream_wait_event(comp, evd), "pipeline");   // later work on the solver's stream comes after the downloads
+    BE_CHECK(fbk::be_stream_sync(down), "pipeline download");
+    BE_CHECK(fbk::be_stream_sync(comp), "pipeline");
+    return 0;
+}
+
+}  // namespace
+
+extern "C" int fluidb200_migrate_solve(fluidb200_solver* s, const void* const host_in[3], void* const host_out[3]) {
+    if (!s) return fail(FLUIDB200_EINVAL, "solver is NULL");
+    if (!host_in || !host_out) return fail(FLUIDB200_EINVAL, "host_in / host_out is NULL");
+    for (int f = 0; f < 3; ++f)
+        if (!host_in[f]) return fail(FLUIDB200_EINVAL, "host_in[%d] is NULL (u, v and p are all needed)", f);
+    if (!(s->dt != 0) || !(s->rho != 0)) return fail(FLUIDB200_EINVAL, "time_step and density must be non-zero");
+    // chunk pipeline: one timestep, no interior flags, a grid tall enough that the halo is a fraction of a chunk
+    const int H = s->K + 2;
+    int chunk = env_int("FLUIDB200_E2E_CHUNK", std::max(4 * H, s->X / 32));
+    chunk = std::max(chunk, 2);
+    const bool masks = s->mask[0].set || s->mask[1].set || s->mask[2].set;
+    if (s->S == 1 && s->K >= 1 && !masks && chunk + 2 * H <= s->X / 2 && env_int("FLUIDB200_E2E_PIPELINE", 1))
+        return migrate_solve_pipelined(s, host_in, host_out, chunk);
+    // otherwise: the plain sequence, with the three downloads queued together
+    const void* fields[FLUIDB200_NUM_FIELDS] = {host_in[0], host_in[1], host_in[2], nullptr, nullptr, nullptr, nullptr};
+    int rc = fluidb200_upload(s, fields, nullptr, nullptr);
+    if (rc) return rc;
+    if ((rc = fluidb200_solve(s))) return rc;
+    const size_t row = (size_t)s->Y * s->esize;
+    for (int f = 0; f < 3; ++f)
+        if (host_out[f])
+            BE_CHECK(fbk::be_memcpy2d_async(host_out[f], row, s->f[f], (size_t)s->pitch * s->esize, row, s->X, fbk::D2H, s->stream),
+                     "download");
     BE_CHECK(fbk::be_stream_sync(s->stream), "download");
     return 0;
 }

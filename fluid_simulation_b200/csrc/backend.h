@@ -26,6 +26,11 @@ int be_stream_destroy(void* stream);
 int be_stream_sync(void* stream);
 // Drop the helper stream a split Jacobi launch forked from `stream` (if any); be_stream_destroy does it too.
 void be_side_stream_release(void* stream);
+// events, for ordering work across streams (copy / compute pipelines)
+int be_event_create(void** ev);
+int be_event_destroy(void* ev);
+int be_event_record(void* ev, void* stream);
+int be_stream_wait_event(void* stream, void* ev);
 const char* be_last_error_string();
 // Kernels launched (or recorded into a graph capture) by the calling host thread so far: a split
 // Jacobi launch counts its three kernels. The solver handle keeps its launch count with it.

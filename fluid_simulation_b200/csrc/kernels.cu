@@ -298,6 +298,16 @@ int be_stream_sync(void* stream) { return rc_of(cudaStreamSynchronize((cudaStrea
 // A failed capture call leaves its (non-sticky) error in the runtime's per-thread slot, where the
 // next launch's cudaGetLastError() would find it: the caller falls back to plain launches, so the
 // slot is cleared here.
+int be_event_create(void** ev) {
+    cudaEvent_t e;
+    const int rc = rc_of(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+    *ev = rc ? nullptr : (void*)e;
+    return rc;
+}
+int be_event_destroy(void* ev) { return rc_of(cudaEventDestroy((cudaEvent_t)ev)); }
+int be_event_record(void* ev, void* stream) { return rc_of(cudaEventRecord((cudaEvent_t)ev, (cudaStream_t)stream)); }
+int be_stream_wait_event(void* stream, void* ev) { return rc_of(cudaStreamWaitEvent((cudaStream_t)stream, (cudaEvent_t)ev, 0)); }
+
 int be_graph_begin(void* stream) {
     const int rc = rc_of(cudaStreamBeginCapture((cudaStream_t)stream, cudaStreamCaptureModeThreadLocal));
     if (rc) (void)cudaGetLastError();

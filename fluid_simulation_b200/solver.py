@@ -176,6 +176,20 @@ class ParallelNavierStokes:
         self.solve()
         self.migrateDeviceToHost()
 
+    def migrate_solve_uvp(self, u, v, p, out=None):
+        """``migrateSolve`` on caller-owned host arrays of shape (X, Y): upload u, v, p, run ``solve()``, return
+        the new (u, v, p) -- written into ``out`` (three arrays) when given. Boundary description and the other
+        device fields stay as they are. One timestep of a tall grid is pipelined over row chunks (upload,
+        compute and download of different chunks overlap); pass pinned memory (e.g. ``torch`` pinned tensors
+        viewed as NumPy) to get that overlap."""
+        self._push_params()
+        ins = [np.ascontiguousarray(a, dtype=self.dtype) for a in (u, v, p)]
+        outs = list(out) if out is not None else [np.empty(self.shape, self.dtype) for _ in range(3)]
+        pi = (C.c_void_p * 3)(*[a.ctypes.data for a in ins])
+        po = (C.c_void_p * 3)(*[a.ctypes.data for a in outs])
+        _lib.check(self._lib, self._lib.fluidb200_migrate_solve(self._h, pi, po))
+        return tuple(outs)
+
     # phase-level access (the reference's protected wrappers, ParallelNavierStokes.cu:297-334)
     def unifiedApproximateTimeStepAndRightHand(self):
         self._push_params()

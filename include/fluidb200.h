@@ -259,6 +259,16 @@ int fluidb200_synchronize(fluidb200_solver* s);
  * NavierStokesSolver.cpp:87-145): dense host array, i = x*Y + y. Blocks until done. */
 int fluidb200_download(fluidb200_solver* s, int field, void* out);
 
+/* migrateSolve (fluid_cpp/cuda/ParallelNavierStokes.cu:290-295) on caller-owned HOST arrays: upload u, v, p
+ * (host_in[0..2], dense X*Y, i = x*Y + y), run solve(), write the new u, v, p to host_out[0..2] (any may be NULL).
+ * The other fields and the boundary description stay as they are on the device. Blocks until host_out is complete.
+ * With num_iterations == 1 on a tall grid without interior flags the three legs are PIPELINED over row chunks
+ * (upload of chunk c+1, the timestep on chunk c, download of chunk c-1 on three streams, each chunk computed with
+ * K+2 recomputed halo rows), so the link is busy in both directions at once; pinned host memory is needed for
+ * that overlap to happen (pageable memory works, serially). Results are bit-identical to
+ * fluidb200_upload + fluidb200_solve + fluidb200_download. */
+int fluidb200_migrate_solve(fluidb200_solver* s, const void* const host_in[3], void* const host_out[3]);
+
 /* Introspection for tools and benchmarks. */
 int fluidb200_get_slab(const fluidb200_solver* s, fluidb200_slab* out);
 void* fluidb200_field_ptr(fluidb200_solver* s, int field);        /* device pointer            */

@@ -119,6 +119,10 @@ int be_stream_create(void** s) { *s = nullptr; return 0; }
 int be_stream_destroy(void*) { return 0; }
 int be_stream_sync(void*) { return 0; }
 void be_side_stream_release(void*) {}
+int be_event_create(void** ev) { *ev = (void*)1; return 0; }   // (the emulation runs everything in order)
+int be_event_destroy(void*) { return 0; }
+int be_event_record(void*, void*) { return 0; }
+int be_stream_wait_event(void*, void*) { return 0; }
 int be_graph_begin(void*) { return -1; }
 int be_graph_end(void*, void**) { return -1; }
 int be_graph_launch(void*, void*) { return -1; }

@@ -181,3 +181,37 @@ def test_solve_on_a_stream_that_cannot_be_captured(Solver, golden):
     s.migrateSolve()
     H.compare_with(s, H.load_fields(golden["cavity41_S10_K50"]), tag="legacy-stream")
     s.close()
+
+
+def test_migrate_solve_pipeline_at_size(Solver):
+    """The chunk-pipelined fluidb200_migrate_solve on a grid where chunks, halos and the split Jacobi launches are
+    all in play (4096 x 2048, K = 30, pinned host memory, in place): host results equal upload + solve + download."""
+    import torch
+    X, Y, K = 4096, 2048, 30
+    rng = np.random.default_rng(5)
+    st = [(0.01 * rng.standard_normal((X, Y))).astype(np.float32) for _ in range(3)]
+    a = Solver(X, Y, float(X - 1), float(Y - 1)).set_cavity(1.0)
+    a.num_iterations, a.num_poisson_iterations = 1, K
+    a.upload_cavity(1.0)
+    pinned = [torch.from_numpy(x.copy()).pin_memory() for x in st]
+    views = [t.numpy() for t in pinned]
+    k0 = a.launch_count()
+    got = a.migrate_solve_uvp(*views, out=views)          # in place
+    assert a.launch_count() - k0 > 3 * (2 + 4), "the chunk pipeline was not taken"
+    b = Solver(X, Y, float(X - 1), float(Y - 1)).set_cavity(1.0)
+    b.num_iterations, b.num_poisson_iterations = 1, K
+    b.upload_cavity(1.0)
+    for n, x in zip(("u", "v", "p"), st):
+        b._hostf(n)[:] = x
+    import ctypes as C
+    from fluid_simulation_b200 import _lib
+    fields = (C.c_void_p * _lib.NUM_FIELDS)()
+    for i, n in enumerate(("u", "v", "p")):
+        fields[i] = b._hostf(n).ctypes.data
+    _lib.check(b._lib, b._lib.fluidb200_upload(b._h, fields, None, None))
+    b.solve()
+    for n, g in zip(("u", "v", "p"), got):
+        H.assert_bit_equal(g, b.device_field(n), f"pipeline/{n}")
+    for n in ("u_next", "v_next", "rhs", "p_next"):
+        H.assert_bit_equal(a.device_field(n), b.device_field(n), f"pipeline-device/{n}")
+    a.close(); b.close()
