@@ -75,6 +75,15 @@ _SIGS = {
     "fluidb200_set_resident": (C.c_int, [C.c_void_p, C.c_int]),
     "fluidb200_resident_launch_count": (C.c_int64, [C.c_void_p]),
     "fluidb200_resident_profile": (C.c_int, [C.c_void_p, C.POINTER(C.c_uint64)]),
+    "fluidb200_device_alloc": (C.c_int, [C.POINTER(C.c_void_p), C.c_size_t]),
+    "fluidb200_device_free": (C.c_int, [C.c_void_p]),
+    "fluidb200_ipc_export": (C.c_int, [C.c_void_p, C.c_char_p]),
+    "fluidb200_ipc_open": (C.c_int, [C.c_char_p, C.POINTER(C.c_void_p)]),
+    "fluidb200_ipc_close": (C.c_int, [C.c_void_p]),
+    "fluidb200_peer_enable": (C.c_int, [C.c_int]),
+    "fluidb200_halo_push": (C.c_int, [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p, C.c_uint32, C.c_void_p]),
+    "fluidb200_halo_copy": (C.c_int, [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p]),
+    "fluidb200_halo_wait": (C.c_int, [C.c_void_p, C.c_uint32, C.c_void_p]),
     "fluidb200_set_device": (C.c_int, [C.c_int]),
     "fluidb200_last_error": (C.c_char_p, []),
     "fluidb200_report_error": (C.c_int, [C.c_int, C.c_char_p]),

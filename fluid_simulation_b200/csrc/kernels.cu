@@ -6,6 +6,8 @@
 //        next to the *_rn intrinsics, see the arithmetic contract in warp_kernels.cuh)
 #include <cuda_runtime.h>
 #include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
 
 #include <map>
 #include <mutex>
@@ -543,5 +545,112 @@ extern "C" int fluidb200_poisson_solve_noalloc(const fluidb200_slab* g, void* p,
             return fluidb200_report_error(FLUIDB200_ECUDA, g_noalloc_err);
         }
     }
+    return 0;
+}
+
+// =========================================================================================
+// Halo exchange between GPUs without a collective: one-sided pushes over NVLink
+// (see include/fluidb200.h, "x-slab halo links"). Plain peer copies and a flag word; no TMA.
+// =========================================================================================
+#include <cuda.h>
+
+namespace {
+
+__global__ void halo_flag_kernel(volatile unsigned* flag, unsigned seq) {
+    *flag = seq;
+    __threadfence_system();
+}
+__global__ void halo_spin_kernel(const volatile unsigned* flag, unsigned seq) {
+    while ((int)(*flag - seq) < 0) {}
+}
+typedef CUresult (*wait_value32_fn)(CUstream, CUdeviceptr, cuuint32_t, unsigned int);
+wait_value32_fn get_wait_value32() {
+    static const wait_value32_fn fn = [] {
+        void* p = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (getenv("FLUIDB200_HALO_SPIN")) return (wait_value32_fn) nullptr;   // (measurement knob: wait in a kernel)
+        if (cudaGetDriverEntryPoint("cuStreamWaitValue32", &p, cudaEnableDefault, &q) != cudaSuccess || q != cudaDriverEntryPointSuccess) {
+            (void)cudaGetLastError();
+            return (wait_value32_fn) nullptr;
+        }
+        return (wait_value32_fn)p;
+    }();
+    return fn;
+}
+int halo_fail(const char* what) {
+    static thread_local char msg[256];
+    snprintf(msg, sizeof(msg), "%s: %s", what, cudaGetErrorString(g_last));
+    return fluidb200_report_error(FLUIDB200_ECUDA, msg);
+}
+
+}  // namespace
+
+extern "C" int fluidb200_device_alloc(void** ptr, size_t bytes) {
+    if (!ptr || bytes == 0) return fluidb200_report_error(FLUIDB200_EINVAL, "device_alloc: bad argument");
+    if (rc_of(cudaMalloc(ptr, bytes))) return halo_fail("device_alloc");
+    if (rc_of(cudaMemset(*ptr, 0, bytes))) return halo_fail("device_alloc: clear");
+    return 0;
+}
+extern "C" int fluidb200_device_free(void* ptr) {
+    if (ptr && rc_of(cudaFree(ptr))) return halo_fail("device_free");
+    return 0;
+}
+extern "C" int fluidb200_ipc_export(const void* ptr, unsigned char handle[64]) {
+    static_assert(sizeof(cudaIpcMemHandle_t) == 64, "cudaIpcMemHandle_t is 64 bytes");
+    if (!ptr || !handle) return fluidb200_report_error(FLUIDB200_EINVAL, "ipc_export: NULL argument");
+    cudaIpcMemHandle_t h;
+    if (rc_of(cudaIpcGetMemHandle(&h, const_cast<void*>(ptr)))) return halo_fail("ipc_export");
+    memcpy(handle, &h, 64);
+    return 0;
+}
+extern "C" int fluidb200_ipc_open(const unsigned char handle[64], void** ptr) {
+    if (!ptr || !handle) return fluidb200_report_error(FLUIDB200_EINVAL, "ipc_open: NULL argument");
+    cudaIpcMemHandle_t h;
+    memcpy(&h, handle, 64);
+    if (rc_of(cudaIpcOpenMemHandle(ptr, h, cudaIpcMemLazyEnablePeerAccess))) return halo_fail("ipc_open");
+    return 0;
+}
+extern "C" int fluidb200_ipc_close(void* ptr) {
+    if (ptr && rc_of(cudaIpcCloseMemHandle(ptr))) return halo_fail("ipc_close");
+    return 0;
+}
+extern "C" int fluidb200_peer_enable(int peer_device) {
+    int dev = 0, can = 0;
+    if (rc_of(cudaGetDevice(&dev))) return halo_fail("peer_enable");
+    if (dev == peer_device) return 0;
+    if (rc_of(cudaDeviceCanAccessPeer(&can, dev, peer_device))) return halo_fail("peer_enable");
+    if (!can) return fluidb200_report_error(FLUIDB200_ESTATE, "peer_enable: the two devices cannot reach each other's memory");
+    const cudaError_t e = cudaDeviceEnablePeerAccess(peer_device, 0);
+    if (e != cudaSuccess && e != cudaErrorPeerAccessAlreadyEnabled) {
+        g_last = e;
+        return halo_fail("peer_enable");
+    }
+    (void)cudaGetLastError();
+    return 0;
+}
+extern "C" int fluidb200_halo_push(void* dst, const void* src, size_t bytes, void* flag, uint32_t seq, void* stream) {
+    if ((bytes && (!dst || !src)) || !flag) return fluidb200_report_error(FLUIDB200_EINVAL, "halo_push: NULL argument");
+    cudaStream_t st = (cudaStream_t)stream;
+    if (bytes && rc_of(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDefault, st))) return halo_fail("halo_push: copy");
+    halo_flag_kernel<<<1, 1, 0, st>>>((volatile unsigned*)flag, seq);
+    ++g_kernels;
+    if (rc_of(cudaGetLastError())) return halo_fail("halo_push: flag");
+    return 0;
+}
+extern "C" int fluidb200_halo_copy(void* dst, const void* src, size_t bytes, void* stream) {
+    if (!dst || !src) return fluidb200_report_error(FLUIDB200_EINVAL, "halo_copy: NULL argument");
+    if (rc_of(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDefault, (cudaStream_t)stream))) return halo_fail("halo_copy");
+    return 0;
+}
+extern "C" int fluidb200_halo_wait(void* flag, uint32_t seq, void* stream) {
+    if (!flag) return fluidb200_report_error(FLUIDB200_EINVAL, "halo_wait: NULL argument");
+    if (wait_value32_fn fn = get_wait_value32()) {
+        // (flag - seq) as a signed number >= 0: sequence numbers stay far below 2^31 apart
+        const CUresult r = fn((CUstream)stream, (CUdeviceptr)flag, seq, CU_STREAM_WAIT_VALUE_GEQ);
+        if (r == CUDA_SUCCESS) return 0;
+    }
+    halo_spin_kernel<<<1, 1, 0, (cudaStream_t)stream>>>((const volatile unsigned*)flag, seq);
+    ++g_kernels;
+    if (rc_of(cudaGetLastError())) return halo_fail("halo_wait");
     return 0;
 }

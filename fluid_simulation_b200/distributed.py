@@ -41,6 +41,14 @@ def slab_bounds(X, world, rank):
     return (rank * X) // world, ((rank + 1) * X) // world
 
 
+class _DeviceBlock:
+    """A cudaMalloc'ed range (fluidb200_device_alloc) exposed to torch through __cuda_array_interface__."""
+
+    def __init__(self, ptr, shape, typestr):
+        self.__cuda_array_interface__ = {"shape": tuple(shape), "typestr": typestr, "data": (int(ptr), False),
+                                         "version": 2, "strides": None}
+
+
 class SlabSolver:
     """One rank's slab of a lid-driven cavity (boundary set-up of fluid_cpp/main.cpp:43-55)."""
 
@@ -71,7 +79,20 @@ class SlabSolver:
         hx = self.lib.fluidb200_element_length(dt, float(domain_x), self.X)
         hy = self.lib.fluidb200_element_length(dt, float(domain_y), self.Y)
         self.slab = _lib.Slab(dt, self.X, self.Y, self.pitch, self.lo, self.rows, hx, hy)
-        self.f = {n: torch.zeros((self.rows, self.pitch), dtype=self.tdt, device=self.device) for n in _FIELDS}
+        # Halo transport on GPUs: "push" (default) = every rank copies the rows its neighbour needs straight into
+        # the neighbour's slab over NVLink (CUDA IPC mapping) and raises a flag there, all stream-ordered;
+        # "nccl" = isend / irecv pairs through torch.distributed (also what the CPU tests use, over gloo).
+        self.halo = "nccl"
+        if self.on_gpu and world > 1 and os.environ.get("FLUIDB200_HALO", "push") == "push":
+            self.halo = "push"
+        self._block = None
+        if self.halo == "push":
+            self._setup_push_links()
+        else:
+            self.f = {n: torch.zeros((self.rows, self.pitch), dtype=self.tdt, device=self.device) for n in _FIELDS}
+        self.phys = {n: i for i, n in enumerate(_FIELDS)}   # which physical array a name refers to (p / p_next swap)
+        self.seq = 0
+        self._fresh = True
         self.edges = {}
         self.time_step, self.kinematic_viscosity, self.density = 0.001, 0.1, 1.0
         self.num_poisson_iterations, self.num_iterations = 50, 1
@@ -88,6 +109,66 @@ class SlabSolver:
         else:
             self.main = self.comm = self.edge = self.edge2 = None
         self._set_edges(1.0)
+
+    # -- one-sided halo links ----------------------------------------------------------------------
+    def _setup_push_links(self):
+        torch, lib = self.torch, self.lib
+        item = self.npdt.itemsize
+        self._field_bytes = self.rows * self.pitch * item
+        total = len(_FIELDS) * self._field_bytes + 256           # + two flag words, 128 bytes apart
+        base = C.c_void_p()
+        _lib.check(lib, lib.fluidb200_device_alloc(C.byref(base), total))
+        self._block = base.value
+        typestr = "<f4" if item == 4 else "<f8"
+        self._holders = [_DeviceBlock(self._block + i * self._field_bytes, (self.rows, self.pitch), typestr) for i in range(len(_FIELDS))]
+        self.f = {n: torch.as_tensor(h, device=self.device) for n, h in zip(_FIELDS, self._holders)}
+        self._flag = {"lo": self._block + len(_FIELDS) * self._field_bytes, "hi": self._block + len(_FIELDS) * self._field_bytes + 128}
+        handle = C.create_string_buffer(64)
+        _lib.check(lib, lib.fluidb200_ipc_export(C.c_void_p(self._block), handle))
+        mine = (bytes(handle.raw), self.lo, self.rows)
+        every = [None] * self.world
+        self.dist.all_gather_object(every, mine, group=self.group)
+        self._peer = {}
+        for side, r in (("lo", self.rank - 1), ("hi", self.rank + 1)):
+            if 0 <= r < self.world:
+                h, plo, prows = every[r]
+                ptr = C.c_void_p()
+                _lib.check(lib, lib.fluidb200_ipc_open(h, C.byref(ptr)))
+                fb = prows * self.pitch * item
+                # I am the `hi` neighbour of the rank below me, and the `lo` neighbour of the rank above
+                flag = ptr.value + len(_FIELDS) * fb + (128 if side == "lo" else 0)
+                self._peer[side] = {"base": ptr.value, "lo": plo, "field_bytes": fb, "flag": flag}
+
+    def _peer_rows_ptr(self, side, name, g0):
+        """Address, in the neighbour's slab, of global row g0 of the physical array `name` currently refers to."""
+        p = self._peer[side]
+        return p["base"] + self.phys[name] * p["field_bytes"] + (g0 - p["lo"]) * self.pitch * self.npdt.itemsize
+
+    def _push(self, names, depth, seq, streams=None):
+        """Queue the copies of my `depth` outermost owned rows of each field into both neighbours' halo rows, each
+        side followed by its flag. streams: {"lo": stream, "hi": stream} (default: the main stream)."""
+        lib, item = self.lib, self.npdt.itemsize
+        nbytes = depth * self.pitch * item
+        for side, g0 in (("lo", self.x0), ("hi", self.x1 - depth)):
+            if side not in self._peer:
+                continue
+            st = (streams or {}).get(side) or self.main
+            stp = C.c_void_p(st.cuda_stream)
+            for i, n in enumerate(names):
+                src = C.c_void_p(self._rows(n, g0, g0 + depth).data_ptr())
+                dst = C.c_void_p(self._peer_rows_ptr(side, n, g0))
+                if i < len(names) - 1:
+                    _lib.check(lib, lib.fluidb200_halo_copy(dst, src, nbytes, stp))
+                else:
+                    _lib.check(lib, lib.fluidb200_halo_push(dst, src, nbytes, C.c_void_p(self._peer[side]["flag"]), seq, stp))
+                self.halo_bytes += nbytes
+            self.launches += 1   # (the flag kernel)
+
+    def _wait_pushed(self, seq, stream=None):
+        st = C.c_void_p((stream or self.main).cuda_stream)
+        for side in ("lo", "hi"):
+            if side in self._peer:
+                _lib.check(self.lib, self.lib.fluidb200_halo_wait(C.c_void_p(self._flag[side]), seq, st))
 
     # ------------------------------------------------------------------------------------------
     def _set_edges(self, lid):
@@ -109,6 +190,7 @@ class SlabSolver:
         _lib.check(self.lib, self.lib.fluidb200_init_cavity(
             C.byref(self.slab), *[self._ptr(n) for n in _FIELDS], float(lid_velocity), self._stream()))
         self.launches += 1
+        self._fresh = True
 
     # -- halo exchange ---------------------------------------------------------------------------
     def _rows(self, name, g0, g1):
@@ -139,6 +221,11 @@ class SlabSolver:
             w.wait()
 
     def exchange(self, names, depth):
+        if self.halo == "push":
+            self.seq += 1
+            self._push(names, depth, self.seq)
+            self._wait_pushed(self.seq)
+            return
         self._wait(self._post_exchange(names, depth))
 
     # -- phases ----------------------------------------------------------------------------------
@@ -168,6 +255,7 @@ class SlabSolver:
 
     def _swap_p(self):
         self.f["p"], self.f["p_next"] = self.f["p_next"], self.f["p"]   # ping-pong instead of p = p_next
+        self.phys["p"], self.phys["p_next"] = self.phys["p_next"], self.phys["p"]
 
     def poisson(self, sweeps):
         """`sweeps` Jacobi sweeps, at most kmax per launch, one halo exchange after every launch.
@@ -205,6 +293,18 @@ class SlabSolver:
                     ev = torch.cuda.Event()
                     ev.record(stream)
                     ready.append(ev)
+            if self.halo == "push":
+                # each strip goes to its neighbour from the stream that computed it, the flag right behind it; the
+                # interior sweeps meanwhile; the next launch starts when both strips are done here and both
+                # neighbours' strips have landed
+                self.seq += 1
+                self._push(["p_next"], d, self.seq, {"lo": self.edge, "hi": self.edge2})
+                self._sweeps(k, lo_strip[1] if lo_strip else x0, hi_strip[0] if hi_strip else x1)
+                for ev in ready:
+                    self.main.wait_event(ev)
+                self._wait_pushed(self.seq)
+                self._swap_p()
+                continue
             # 2. the interior of the owned range, concurrently, on the main stream
             self._sweeps(k, lo_strip[1] if lo_strip else x0, hi_strip[0] if hi_strip else x1)
             # 3. ship the strips on the communication stream while the interior runs
@@ -230,7 +330,16 @@ class SlabSolver:
     def step(self):
         """One projection timestep (phase order of SerialNavierStokes.cpp:49-67)."""
         mark = self._phase_marks()
+        if self.world > 1 and self.halo == "push" and self._fresh:
+            # a neighbour's pushes may only arrive once this rank's set-up (init kernels, uploads) is done
+            self.synchronize()
+            self.dist.barrier(group=self.group)
+            self._fresh = False
         if self.world > 1:
+            if self.halo == "push" and int(self.num_poisson_iterations) == 0:
+                # (with no sweep launches between them nothing orders one step's pushes behind the neighbour's reads)
+                self.synchronize()
+                self.dist.barrier(group=self.group)
             self.exchange(["u", "v"], self.H)
         mark("exchange_uv")
         self.predictor()
@@ -292,6 +401,7 @@ class SlabSolver:
 
     def upload_owned(self, name, host_tensor):
         """Host (pinned) tensor of this rank's owned rows, shape (x1-x0, Y) -> device slab."""
+        self._fresh = True
         self._rows(name, self.x0, self.x1)[:, : self.Y].copy_(host_tensor, non_blocking=True)
 
     def download_owned(self, name, host_tensor):
@@ -386,6 +496,7 @@ def bench_distributed(args, grid, sweeps, kmax, prm, metric, unit):
     assert int(finite.item()) == 1, "non-finite field after the e2e steps"
     halo_per_step = (s.halo_bytes - hb0) / max(1, args.steps + e2e_steps + 1)
     weak_rows = s.x1 - s.x0
+    halo_mode = s.halo
     weak_desc = f"cavity {X}x{Y} fp32 ({weak_rows} rows per GPU, x-slabs), {sweeps} Poisson sweeps/step"
 
     # ---- strong scaling beside it (BASELINE.json configs[3]): a FIXED 32768^2 grid cut over the same ranks, and the same
@@ -449,12 +560,16 @@ def bench_distributed(args, grid, sweeps, kmax, prm, metric, unit):
         "config": {"workload": weak_desc, "strong": strong_rec,
                    "dt": prm["dt"], "nu": prm["nu"], "rho": prm["rho"], "hx": 1.0, "hy": 1.0, "sweeps_per_launch": kmax,
                    "host_issue_ms_per_step": t_issue / args.steps * 1e3,
-                   "parallelism": f"x-slabs x{world}, halo depth {kmax + 1}, NCCL send/recv overlapped with interior sweeps",
+                   "parallelism": f"x-slabs x{world}, halo depth {kmax + 1}, " + (
+                       "edge strips pushed into the neighbour's slab over NVLink (IPC-mapped peer memory + flag, stream-ordered)"
+                       if halo_mode == "push" else "NCCL send/recv") + " overlapped with the interior sweeps; NCCL for bootstrap",
                    "halo_bytes_per_rank_per_step": halo_per_step,
                    "l2": f"fields are {weak_rows * Y * 4 / 1e9:.2f} GB per GPU, >> 126 MB L2, no flush needed"},
         "roofline": None, "cpu_baseline": None,
         "e2e": {"value": cells * e2e_steps / e2e_s / 1e9, "unit": unit, "h2d_bytes_per_step": 3 * cells * 4,
                 "d2h_bytes_per_step": 3 * cells * 4, "steps": e2e_steps, "ms_per_step": e2e_s / e2e_steps * 1e3,
-                "api": "per rank: copy owned u,v,p from pinned host + SlabSolver.step() + copy back"},
+                "host_link_GBps_aggregate": 2 * 3 * cells * 4 / (e2e_s / e2e_steps) / 1e9,
+                "api": "per rank: copy owned u,v,p from pinned host + SlabSolver.step() + copy back (all ranks share the "
+                       "host's memory and PCIe complex: host_link_GBps_aggregate is what they moved through it together)"},
         "gpu_launches": int(launches_total), "clocks": None,
     }

@@ -289,6 +289,29 @@ int fluidb200_resident_profile(fluidb200_solver* s, unsigned long long out[8]);
 int64_t fluidb200_launch_count(const fluidb200_solver* s);         /* kernels launched so far (a split Jacobi launch = 3) */
 
 /* ====================================================================================
+ * x-slab halo links between GPUs (no counterpart in the reference, which knows one device): the
+ * plumbing the multi-GPU driver (fluid_simulation_b200/distributed.py) uses instead of a send/recv
+ * pair per sweep launch. A rank PUSHES the rows its neighbour needs straight into the neighbour's
+ * slab over NVLink (a plain copy into peer memory mapped through CUDA IPC, or reached by peer access
+ * inside one process) and then sets a 32-bit flag in the neighbour's memory to a sequence number; the
+ * neighbour's stream waits for that number. Everything is stream-ordered: no host thread waits.
+ * ==================================================================================*/
+/* Device memory another process can map: a plain cudaMalloc, zero-filled (pool allocators hand out
+ * sub-ranges that CUDA IPC cannot export). */
+int fluidb200_device_alloc(void** ptr, size_t bytes);
+int fluidb200_device_free(void* ptr);
+int fluidb200_ipc_export(const void* ptr, unsigned char handle[64]);   /* cudaIpcGetMemHandle             */
+int fluidb200_ipc_open(const unsigned char handle[64], void** ptr);    /* cudaIpcOpenMemHandle, in the peer */
+int fluidb200_ipc_close(void* ptr);
+int fluidb200_peer_enable(int peer_device);                            /* same process, other device       */
+/* On `stream`: copy `bytes` from src (this GPU) to dst (the peer's memory), then *flag = seq (flag in the
+ * peer's memory). A push of several arrays: fluidb200_halo_copy for all but the last. */
+int fluidb200_halo_push(void* dst, const void* src, size_t bytes, void* flag, uint32_t seq, void* stream);
+int fluidb200_halo_copy(void* dst, const void* src, size_t bytes, void* stream);
+/* On `stream`: wait until (int32)(*flag - seq) >= 0 (flag in THIS GPU's memory); cuStreamWaitValue32, no SM used. */
+int fluidb200_halo_wait(void* flag, uint32_t seq, void* stream);
+
+/* ====================================================================================
  * Library-level
  * ==================================================================================*/
 /* Select the CUDA device the calling thread's later fluidb200_* calls use (cudaSetDevice inside

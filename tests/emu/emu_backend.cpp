@@ -241,6 +241,18 @@ extern "C" int fluidb200_poisson_solve_noalloc(const fluidb200_slab*, void*, con
     return fluidb200_report_error(FLUIDB200_ESTATE, "poisson_solve_noalloc is not available in the host emulation");
 }
 
+// GPU-to-GPU halo links do not exist in the host emulation (its multi-rank tests exchange through gloo).
+#define EMU_NO_LINK(name, ...) extern "C" int name(__VA_ARGS__) { return fluidb200_report_error(FLUIDB200_ESTATE, #name " is not available in the host emulation"); }
+EMU_NO_LINK(fluidb200_device_alloc, void**, size_t)
+EMU_NO_LINK(fluidb200_device_free, void*)
+EMU_NO_LINK(fluidb200_ipc_export, const void*, unsigned char*)
+EMU_NO_LINK(fluidb200_ipc_open, const unsigned char*, void**)
+EMU_NO_LINK(fluidb200_ipc_close, void*)
+EMU_NO_LINK(fluidb200_peer_enable, int)
+EMU_NO_LINK(fluidb200_halo_push, void*, const void*, size_t, void*, uint32_t, void*)
+EMU_NO_LINK(fluidb200_halo_copy, void*, const void*, size_t, void*)
+EMU_NO_LINK(fluidb200_halo_wait, void*, uint32_t, void*)
+
 // Test hooks: the product's exact-rounding arithmetic (Ar<float>), element-wise, so that its
 // division-free modes can be hammered against the reference formulas in NumPy. A flagged
 // element is recomputed in DIV_EXACT, like the kernels do per row.
