@@ -6,6 +6,6 @@ with the boundary rows fused in, fused velocity correction. The product is the C
 ``libfluidb200.so`` (``include/fluidb200.h``); this package is its thin Python face.
 """
 from ._lib import FluidB200Error, load  # noqa: F401
-from .solver import ParallelNavierStokes, TiledNavierStokes, solve_navier_stokes  # noqa: F401
+from .solver import MultiGpuNavierStokes, ParallelNavierStokes, TiledNavierStokes, solve_navier_stokes  # noqa: F401
 
-__all__ = ["ParallelNavierStokes", "TiledNavierStokes", "solve_navier_stokes", "FluidB200Error", "load"]
+__all__ = ["ParallelNavierStokes", "TiledNavierStokes", "MultiGpuNavierStokes", "solve_navier_stokes", "FluidB200Error", "load"]

@@ -84,6 +84,16 @@ _SIGS = {
     "fluidb200_halo_push": (C.c_int, [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p, C.c_uint32, C.c_void_p]),
     "fluidb200_halo_copy": (C.c_int, [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p]),
     "fluidb200_halo_wait": (C.c_int, [C.c_void_p, C.c_uint32, C.c_void_p]),
+    "fluidb200_multi_create": (C.c_int, [C.POINTER(C.c_void_p), C.c_int, C.c_int, C.c_int, C.c_double, C.c_double, C.c_int, C.POINTER(C.c_int)]),
+    "fluidb200_multi_destroy": (C.c_int, [C.c_void_p]),
+    "fluidb200_multi_set_params": (C.c_int, [C.c_void_p, C.c_double, C.c_double, C.c_double, C.c_int, C.c_int]),
+    "fluidb200_multi_upload_cavity": (C.c_int, [C.c_void_p, C.c_double]),
+    "fluidb200_multi_upload": (C.c_int, [C.c_void_p, C.POINTER(C.c_void_p)]),
+    "fluidb200_multi_solve": (C.c_int, [C.c_void_p]),
+    "fluidb200_multi_synchronize": (C.c_int, [C.c_void_p]),
+    "fluidb200_multi_download": (C.c_int, [C.c_void_p, C.c_int, C.c_void_p]),
+    "fluidb200_multi_launch_count": (C.c_int64, [C.c_void_p]),
+    "fluidb200_multi_num_slabs": (C.c_int, [C.c_void_p]),
     "fluidb200_set_device": (C.c_int, [C.c_int]),
     "fluidb200_last_error": (C.c_char_p, []),
     "fluidb200_report_error": (C.c_int, [C.c_int, C.c_char_p]),

@@ -219,6 +219,26 @@ class ParallelNavierStokes:
     def launch_count(self):
         return int(self._lib.fluidb200_launch_count(self._h))
 
+    def device_array(self, name):
+        """Zero-copy view of one DEVICE field: an object with ``__cuda_array_interface__`` (shape (X, Y), row
+        stride = the device pitch), accepted by ``torch.as_tensor(..., device="cuda")``, CuPy and Numba without
+        a copy. The view follows the solver's memory: it is valid until the next call that swaps or frees the
+        field's buffer (``solve()`` swaps p and p_next; ``close()`` frees everything), so take it again after those."""
+        slab = _lib.Slab()
+        _lib.check(self._lib, self._lib.fluidb200_get_slab(self._h, C.byref(slab)))
+        ptr = self._lib.fluidb200_field_ptr(self._h, _FIELD_NAMES.index(name))
+        if not ptr:
+            raise ValueError(f"no such field: {name}")
+        item = self.dtype.itemsize
+
+        class _View:
+            pass
+        v = _View()
+        v.pitch = int(slab.pitch)
+        v.__cuda_array_interface__ = {"shape": self.shape, "typestr": "<f4" if item == 4 else "<f8", "data": (int(ptr), False),
+                                      "version": 2, "strides": (int(slab.pitch) * item, item)}
+        return v
+
     def device_field(self, name):
         """Download one field straight from the device (shape (X, Y))."""
         out = np.empty(self.shape, self.dtype)
@@ -275,6 +295,72 @@ class ParallelNavierStokes:
         return np.fromfile(path, dtype=np.dtype(dtype).newbyteorder("<")).reshape(num_x_bins, num_y_bins)
 
 
+class MultiGpuNavierStokes:
+    """The x-slab multi-GPU solver of the C ABI (``fluidb200_multi_*``): one process, one slab per entry of
+    ``devices`` (an entry may repeat). Cavity boundaries; same public fields and call sequence as
+    ``ParallelNavierStokes``; results are bit-identical to it."""
+
+    def __init__(self, box_dim_x, box_dim_y, domain_size_x=1.0, domain_size_y=1.0, dtype=np.float32, devices=(0,), _libpath=None):
+        self.dtype = np.dtype(dtype)
+        self._lib = _lib.load(_libpath)
+        self.box_dimension_x, self.box_dimension_y = int(box_dim_x), int(box_dim_y)
+        self.time_step, self.kinematic_viscosity, self.density = 0.001, 0.1, 1.0
+        self.num_poisson_iterations, self.num_iterations = 50, 1000
+        T = self.dtype.type
+        devs = (C.c_int * len(devices))(*[int(d) for d in devices])
+        self._h = C.c_void_p()
+        _lib.check(self._lib, self._lib.fluidb200_multi_create(
+            C.byref(self._h), int(self.dtype == np.float64), self.box_dimension_x, self.box_dimension_y,
+            float(T(domain_size_x)), float(T(domain_size_y)), len(devices), devs))
+
+    @property
+    def shape(self):
+        return (self.box_dimension_x, self.box_dimension_y)
+
+    def upload_cavity(self, lid_velocity=1.0):
+        _lib.check(self._lib, self._lib.fluidb200_multi_upload_cavity(self._h, float(lid_velocity)))
+
+    def upload(self, **fields):
+        """Dense (X, Y) host arrays by field name (u, v, p, u_next, v_next, p_next, rhs)."""
+        ptrs = (C.c_void_p * _lib.NUM_FIELDS)()
+        keep = []
+        for i, n in enumerate(_FIELD_NAMES):
+            if n in fields:
+                a = np.ascontiguousarray(fields[n], dtype=self.dtype)
+                keep.append(a)
+                ptrs[i] = a.ctypes.data
+        _lib.check(self._lib, self._lib.fluidb200_multi_upload(self._h, ptrs))
+
+    def solve(self):
+        T = self.dtype.type
+        _lib.check(self._lib, self._lib.fluidb200_multi_set_params(
+            self._h, float(T(self.time_step)), float(T(self.kinematic_viscosity)), float(T(self.density)),
+            int(self.num_poisson_iterations), int(self.num_iterations)))
+        _lib.check(self._lib, self._lib.fluidb200_multi_solve(self._h))
+
+    def synchronize(self):
+        _lib.check(self._lib, self._lib.fluidb200_multi_synchronize(self._h))
+
+    def device_field(self, name):
+        out = np.empty(self.shape, self.dtype)
+        _lib.check(self._lib, self._lib.fluidb200_multi_download(self._h, _FIELD_NAMES.index(name), out.ctypes.data))
+        return out
+
+    def launch_count(self):
+        return int(self._lib.fluidb200_multi_launch_count(self._h))
+
+    def close(self):
+        if getattr(self, "_h", None) is not None and self._h.value:
+            self._lib.fluidb200_multi_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
 class TiledNavierStokes(ParallelNavierStokes):
     """Drop-in for ``TiledNavierStokes<T>`` (``fluid_cpp/cuda/TiledNavierStokes.cuh:10-23``).
 
@@ -289,7 +375,7 @@ class TiledNavierStokes(ParallelNavierStokes):
 
 def solve_navier_stokes(num_elements=41, domain_size=1.0, num_iterations=1000, time_step=0.001,
                         kinematic_viscosity=0.1, density=1., top_velocity=1., num_poisson_iterations=50,
-                        stability_safety_factor=0.5, dtype=np.float64):
+                        stability_safety_factor=0.5, dtype=np.float64, _libpath=None):
     """Signature of the reference's only Python entry point (``python/navier_stokes.py:24-26``),
     returning ``(X, Y, u, v, p)`` with ``[y, x]`` arrays like it does (``:99``), computed by the
     CUDA solver with the C++ solver's semantics. Differences from the NumPy script that follow
@@ -297,7 +383,7 @@ def solve_navier_stokes(num_elements=41, domain_size=1.0, num_iterations=1000, t
     ``num_iterations = S`` here corresponds to ``S + 1`` there, and the four corner cells differ.
     """
     n = int(num_elements)
-    s = ParallelNavierStokes(n, n, domain_size, domain_size, dtype=dtype)
+    s = ParallelNavierStokes(n, n, domain_size, domain_size, dtype=dtype, _libpath=_libpath)
     s.time_step, s.kinematic_viscosity, s.density = time_step, kinematic_viscosity, density
     s.num_iterations, s.num_poisson_iterations = int(num_iterations), int(num_poisson_iterations)
     s.stability_safety_factor = stability_safety_factor

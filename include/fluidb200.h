@@ -312,6 +312,30 @@ int fluidb200_halo_copy(void* dst, const void* src, size_t bytes, void* stream);
 int fluidb200_halo_wait(void* flag, uint32_t seq, void* stream);
 
 /* ====================================================================================
+ * Multi-GPU solver handle: ONE process, several devices, the grid cut into x-slabs (one per entry of
+ * `devices`; NULL = devices 0 .. ndev-1; an entry may repeat, which puts several slabs on one GPU --
+ * useful for tests). The reference has no multi-device path (no cudaSetDevice anywhere in its tree); the
+ * calls mirror the single-device handle above one to one, so ParallelNavierStokes<T>'s methods map onto
+ * them the same way. Cavity-style boundaries (fluidb200_multi_upload_cavity).
+ * Results are bit-identical to the single-device handle: Jacobi is order-free and the kernels are the same.
+ * Halos travel by fluidb200_halo_push over NVLink peer access; every call is made from one host thread,
+ * solve() itself issues the devices' work from one short-lived thread per slab and returns without waiting.
+ * ==================================================================================*/
+typedef struct fluidb200_multi fluidb200_multi;
+int fluidb200_multi_create(fluidb200_multi** out, int dtype, int X, int Y, double domain_x, double domain_y,
+                           int ndev, const int* devices);
+int fluidb200_multi_destroy(fluidb200_multi* m);
+int fluidb200_multi_set_params(fluidb200_multi* m, double time_step, double kinematic_viscosity, double density,
+                               int num_poisson_iterations, int num_iterations);
+int fluidb200_multi_upload_cavity(fluidb200_multi* m, double lid_velocity);                 /* fluid_cpp/main.cpp:43-55 */
+int fluidb200_multi_upload(fluidb200_multi* m, const void* const fields[FLUIDB200_NUM_FIELDS]); /* migrateHostToDevice: dense X*Y arrays or NULL */
+int fluidb200_multi_solve(fluidb200_multi* m);                                              /* solve(), asynchronous */
+int fluidb200_multi_synchronize(fluidb200_multi* m);
+int fluidb200_multi_download(fluidb200_multi* m, int field, void* out);                     /* migrateDeviceToHost + getter, blocking */
+int64_t fluidb200_multi_launch_count(const fluidb200_multi* m);
+int fluidb200_multi_num_slabs(const fluidb200_multi* m);
+
+/* ====================================================================================
  * Library-level
  * ==================================================================================*/
 /* Select the CUDA device the calling thread's later fluidb200_* calls use (cudaSetDevice inside

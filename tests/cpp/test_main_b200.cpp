@@ -17,6 +17,7 @@
 
 #include "cuda/ParallelNavierStokes.cuh"
 #include "cuda/TiledNavierStokes.cuh"
+#include "cuda/MultiGpuNavierStokes.cuh"
 
 struct OracleStateF32 {  // mirrors oracle_state_f32 in oracle/fluid_oracle_impl.inc
     int X, Y;
@@ -151,5 +152,25 @@ int main(int argc, char** argv) {
     int errors = compare("ParallelNavierStokes<float>", tested_solver, unit_solver, num_x_bins, num_y_bins, true);
     errors += compare("TiledNavierStokes<float>", tiled_solver, unit_solver, num_x_bins, num_y_bins, true);
     errors += compare("ParallelNavierStokes<float> after setBoxDimenension", resized_solver, unit_solver, num_x_bins, num_y_bins, true);
+    {   // the multi-GPU class on the devices named in FLUIDB200_TEST_DEVICES (default: device 0 alone)
+        std::vector<int> devices;
+        if (const char* e = getenv("FLUIDB200_TEST_DEVICES"))
+            for (const char* c = e; *c; ++c)
+                if (*c >= '0' && *c <= '9') devices.push_back(*c - '0');
+        MultiGpuNavierStokes<float> multi_solver(num_x_bins, num_y_bins, width, height, devices);
+        multi_solver.density = tested_solver.density;
+        multi_solver.kinematic_viscosity = tested_solver.kinematic_viscosity;
+        multi_solver.num_iterations = tested_solver.num_iterations;
+        multi_solver.num_poisson_iterations = tested_solver.num_poisson_iterations;
+        multi_solver.time_step = tested_solver.time_step;
+        multi_solver.uploadCavity(1.0f);
+        multi_solver.solve();
+        multi_solver.migrateDeviceToHost();
+        if (multi_solver.lastError()) {
+            std::cerr << "fluidb200 multi error: " << multi_solver.lastErrorMessage() << std::endl;
+            return 3;
+        }
+        errors += compare("MultiGpuNavierStokes<float>", multi_solver, unit_solver, num_x_bins, num_y_bins, true);
+    }
     return errors == 0 ? 0 : 1;
 }

@@ -38,7 +38,7 @@ def test_cpp_parity_program():
     r = subprocess.run([exe, os.path.join(ROOT, "oracle", "liboracle.so")], capture_output=True, text=True, cwd=ROOT,
                        timeout=300, env=_default_env())
     assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
-    assert r.stdout.count("Passed 100% cells") == 9, r.stdout
+    assert r.stdout.count("Passed 100% cells") == 12, r.stdout
 
 
 @pytest.mark.gpu

@@ -16,10 +16,11 @@ import torch
 from fluid_simulation_b200 import ParallelNavierStokes, _lib
 
 N = int(os.environ.get("N", 16384))
+NX, NY = int(os.environ.get("NX", N)), int(os.environ.get("NY", N))   # (a slab-shaped grid: NX rows of NY columns)
 DT = np.float64 if os.environ.get("DTYPE", "f32") == "f64" else np.float32
 ks = [int(a) for a in sys.argv[1:]] or [4, 5, 6, 7, 8]
 lib = _lib.load()
-s = ParallelNavierStokes(N, N, float(N - 1), float(N - 1), dtype=DT)
+s = ParallelNavierStokes(NX, NY, float(NX - 1), float(NY - 1), dtype=DT)
 s.num_poisson_iterations, s.num_iterations = 100, 1
 st = torch.cuda.current_stream()
 _lib.check(lib, lib.fluidb200_set_stream(s._h, st.cuda_stream))
@@ -39,6 +40,6 @@ for k in ks:
     e1.record(st)
     torch.cuda.synchronize()
     us = e0.elapsed_time(e1) * 1e3 / (reps * launches)
-    out[k] = {"us_per_launch": round(us, 1), "gcell_sweeps_per_s": round(N * N * k / us / 1e3, 1)}
+    out[k] = {"us_per_launch": round(us, 1), "gcell_sweeps_per_s": round(NX * NY * k / us / 1e3, 1)}
 s.close()
 print(json.dumps(out))
