@@ -111,7 +111,7 @@ def load(path: str | None = None):
     global _lib
     if _lib is not None and path is None:
         return _lib
-    p = path or LIB_PATH
+    p = path or os.environ.get("FLUIDB200_LIB") or LIB_PATH   # (FLUIDB200_LIB: another build of the same library, for measurements)
     if not os.path.exists(p):
         raise ImportError(
             f"{p} not found: the CUDA library must be built first "

@@ -244,7 +244,11 @@ int poisson_t(const fluidb200_slab* g, const void* p_in, void* p_out, const void
     int rpc, nchunks;
     // resident CTAs per SM of the kernel that does the bulk of the work (the lean FAST kernel)
     const int ctas_per_sm = sweeps <= 2 ? 5 : sweeps <= 6 ? 4 : 3;
-    const int tasks = sweeps >= 7 ? kJacobiTasksDeep : kJacobiTasks;
+    // Waves of tasks: few on a short range (every chunk recomputes 2K halo rows, so short chunks cost more than a
+    // ragged last wave does), the measured optimum of the tall grid from about 13000 rows up. Depth 8 at 32768 columns,
+    // us per launch with 2 / 3 / 5 / 7 waves: 4096 rows 315 / 315 / 331 / 340; 16384 rows (16384 columns) - / 590 / 584 / 591.
+    const int nrows = out_hi - out_lo;
+    const int tasks = sweeps >= 7 ? 148 * 16 * std::max(2, std::min(5, nrows / 2700)) : 148 * 16 * std::max(3, std::min(9, nrows / 1800));
     // First try: the chunks at an x wall as short as the pipeline allows (the next chunk must start
     // at row >= 2K+2, the previous one end at row <= X-K-2), because only the register-heavy general
     // kernel can run them; the rows between are chunked uniformly and go to the lean kernels.

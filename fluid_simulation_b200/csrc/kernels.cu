@@ -97,8 +97,11 @@ __global__ void __launch_bounds__(kThreads, FLUIDB200_JACOBI_EDGE_MIN_BLOCKS(K))
     fb::jacobi_edge_task<T, V, K>(A, strip, chunk, threadIdx.x & 31, threadIdx.x, kThreads);
 }
 
+#ifndef FLUIDB200_PRED_MIN_BLOCKS
+#define FLUIDB200_PRED_MIN_BLOCKS 4
+#endif
 template <typename T, int V, int MODE>
-__global__ void __launch_bounds__(kThreads) predictor_kernel(const __grid_constant__ fb::PredictorArgs<T> A) {
+__global__ void __launch_bounds__(kThreads, FLUIDB200_PRED_MIN_BLOCKS) predictor_kernel(const __grid_constant__ fb::PredictorArgs<T> A) {
     pdl_prologue();
     const int strip = blockIdx.x * fb::kWarpsPerCta + (threadIdx.x >> 5);
     if (strip >= A.g.nstrips) return;

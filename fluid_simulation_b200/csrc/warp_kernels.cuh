@@ -382,12 +382,13 @@ template <typename T, int V, int D> struct LaneRing {
 };
 // ring depth used by the Jacobi fast path for blocking depth K (U = steps per unrolled iteration)
 // Unroll factor U of the fast loop. U = K (rounded up to even) lets the row windows and the
-// right-hand-side shift register rotate by register renaming alone, but at K >= 7 the unrolled body
-// (8 steps x 8 levels, 27 KB of code) no longer sits in the instruction caches: 4 steps per iteration
-// plus a few moves is 10 % faster there (measured, profiles/README_r1.md). Build-time knobs
-// (0 = the default rule), kept for such measurements:
+// right-hand-side shift register rotate by register renaming alone. Round 1 ran K >= 7 with 4 steps per
+// iteration because the 8-step body (27 KB then) fell out of the instruction caches; after that round's
+// instruction diet the 8-step body is 22 KB (1405 instructions, 34 moves instead of 180 per 8 steps) and is
+// the faster one again: 7.36 -> 7.18 ms for the 100 sweeps of a 16384^2 step (profiles/README_r2.md).
+// Build-time knobs (0 = the default rule), kept for such measurements:
 #ifndef FLUIDB200_U_DEEP
-#define FLUIDB200_U_DEEP 4   // K = 7, 8
+#define FLUIDB200_U_DEEP 8   // K = 7, 8
 #endif
 #ifndef FLUIDB200_U_MID
 #define FLUIDB200_U_MID 0    // K = 5, 6
