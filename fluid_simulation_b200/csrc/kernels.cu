@@ -202,7 +202,10 @@ SideStream* side_stream(cudaStream_t caller) {
 template <typename T, int K> int launch_jacobi_k(const fb::JacobiArgs<T>& a, bool mask, int nchunks, cudaStream_t st) {
     constexpr int V = fb::VecWidth<T>::V;
     // dynamic shared memory: the per-lane cp.async prefetch ring (D slots x 2 arrays x 16 B per thread)
-    const size_t smem = (size_t)fb::JacobiRing<K>::D * 2 * 16 * kThreads;
+    size_t smem = (size_t)fb::JacobiRing<K>::D * 2 * 16 * kThreads;
+#ifdef FLUIDB200_TMA_RING
+    smem += (size_t)fb::JacobiRing<K>::D * 8 * fb::kWarpsPerCta;   // one mbarrier per (warp, slot)
+#endif
     SideStream* side = a.part != 0 ? side_stream(st) : nullptr;
     if (!side) {  // one kernel does every task
         fb::JacobiArgs<T> all = a;

@@ -806,6 +806,133 @@ FB_DEV void jacobi_fast_body(const JacobiArgs<T>& A, int strip, int chunk, int l
     ring.template wait<0>();  // nothing may still be landing in shared memory when the CTA retires
 }
 
+#if defined(FLUIDB200_TMA_RING) && !defined(FLUIDB200_HOST_EMU)
+// EXPERIMENT (build with -DFLUIDB200_TMA_RING; not the default): the lean pipeline
+// fed by 1-D bulk copies (cp.async.bulk, the TMA engine's linear mode) instead of the per-lane cp.async ring.
+// One elected lane asks for the warp's 512 contiguous bytes of p and of rhs; an mbarrier per (warp, slot)
+// counts the bytes in; every lane then reads its own 16 bytes. This GPU's memory only, no multicast.
+FB_DEV void mbar_init(unsigned bar, unsigned count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
+}
+FB_DEV void mbar_expect_tx(unsigned bar, unsigned bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+FB_DEV void mbar_wait(unsigned bar, unsigned phase) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "WAIT_%=:\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+        "@p bra DONE_%=;\n\t"
+        "bra WAIT_%=;\n\t"
+        "DONE_%=:\n\t}" ::"r"(bar), "r"(phase) : "memory");
+}
+FB_DEV void bulk_g2s(unsigned dst, const void* src, unsigned bytes, unsigned bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst), "l"(src), "r"(bytes),
+                 "r"(bar)
+                 : "memory");
+}
+template <typename T, int V, int K, bool SCALE_B>
+FB_DEV void jacobi_fast_body_bulk(const JacobiArgs<T>& A, int strip, int chunk, int lane, int tid, int nthreads) {
+    constexpr int H = (K + 3) & ~3;
+    constexpr int U = JacobiRing<K>::U, D = JacobiRing<K>::D;
+    static_assert(D == U, "the bulk-copy experiment keeps one ring slot per unrolled step");
+    using A_ = Ar<T>;
+    using VT = Vec<T, V>;
+    constexpr unsigned ROW = 32 * 16;   // bytes of a warp's row piece
+    const Geom& g = A.g;
+    Strip<V, H> st;
+    st.init(g, strip, lane);
+    int c0, c1;
+    jacobi_chunk_rows(A, chunk, &c0, &c1);
+    if (c0 >= c1) return;
+    const int r_begin = c0 - K;
+    const int load_hi = min(c1 + K, g.row0 + g.rows);
+    const int r_end = c1 - 1 + K;
+    const int pmax = load_hi - 1, bmax = min(load_hi - 1, g.X - 2);
+    // lane 0's addresses: the start of the warp's 512 bytes
+    const long long base0 = (long long)(st.col0 - lane * V) + (long long)(r_begin - g.row0) * g.pitch;
+    const T* pbase = A.p_in + base0;
+    const T* bbase = A.rhs + base0;
+    T* optr = A.p_out + (long long)st.col0 + (long long)(r_begin - K - g.row0) * g.pitch;
+    const unsigned pitch32 = (unsigned)g.pitch;
+    const unsigned pmax_off = (unsigned)(pmax - r_begin) * pitch32;
+    const unsigned bmax_off = (unsigned)(bmax - r_begin) * pitch32;
+
+    extern __shared__ __align__(16) unsigned char fb_ring_smem[];
+    const int warp = tid >> 5, nwarps = nthreads >> 5;
+    // [warp][slot][p, rhs][512 B], then the mbarriers [warp][slot]
+    const unsigned smem0 = (unsigned)__cvta_generic_to_shared(fb_ring_smem);
+    const unsigned wbase = smem0 + (unsigned)warp * D * 2 * ROW;
+    const unsigned bar0 = smem0 + (unsigned)nwarps * D * 2 * ROW + (unsigned)warp * D * 8;
+    if (lane == 0) {
+#pragma unroll
+        for (int j = 0; j < D; ++j) mbar_init(bar0 + j * 8, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncwarp();
+
+    VT w[K][2];
+    VT bw[K];
+#pragma unroll
+    for (int t = 0; t < K; ++t) {
+        w[t][0] = vzero<T, V>();
+        w[t][1] = vzero<T, V>();
+        bw[t] = vzero<T, V>();
+    }
+    if (lane == 0) {
+#pragma unroll
+        for (int j = 0; j < D; ++j) {
+            mbar_expect_tx(bar0 + j * 8, 2 * ROW);
+            bulk_g2s(wbase + j * 2 * ROW, pbase + min((unsigned)j * pitch32, pmax_off), ROW, bar0 + j * 8);
+            bulk_g2s(wbase + j * 2 * ROW + ROW, bbase + min((unsigned)(j > 0 ? j - 1 : 0) * pitch32, bmax_off), ROW, bar0 + j * 8);
+        }
+    }
+    unsigned poff = min((unsigned)D * pitch32, pmax_off);
+    unsigned boff = min((unsigned)(D - 1) * pitch32, bmax_off);
+    unsigned phase = 0;
+    const unsigned char* mine = fb_ring_smem + (size_t)warp * D * 2 * ROW + lane * 16;
+#pragma unroll 1
+    for (int r = r_begin; r <= r_end; r += U) {
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            mbar_wait(bar0 + u * 8, phase);
+            VT cur = *reinterpret_cast<const VT*>(mine + u * 2 * ROW);
+            VT bnew = *reinterpret_cast<const VT*>(mine + u * 2 * ROW + ROW);
+            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // my reads come before the next bulk write of this slot
+            __syncwarp();
+            if (lane == 0) {
+                mbar_expect_tx(bar0 + u * 8, 2 * ROW);
+                bulk_g2s(wbase + u * 2 * ROW, pbase + poff, ROW, bar0 + u * 8);
+                bulk_g2s(wbase + u * 2 * ROW + ROW, bbase + boff, ROW, bar0 + u * 8);
+            }
+            poff = min(poff + pitch32, pmax_off);
+            boff = min(boff + pitch32, bmax_off);
+            if (SCALE_B) {
+#pragma unroll
+                for (int e = 0; e < V; ++e) bnew.a[e] = A_::mul(A_::mul(bnew.a[e], A.hx), A.hy);
+            }
+#pragma unroll
+            for (int t = K - 1; t > 0; --t) bw[t] = bw[t - 1];
+            bw[0] = bnew;
+#pragma unroll
+            for (int t = 1; t <= K; ++t) {
+                VT out = jacobi_row<T, V>(w[t - 1][0], w[t - 1][1], cur, bw[t - 1]);
+                w[t - 1][0] = w[t - 1][1];
+                w[t - 1][1] = cur;
+                cur = out;
+            }
+            const int row = r + u - K;
+            if (st.st_ok && row >= c0 && row < c1) st_vec<T, V>(optr, cur);
+            optr += pitch32;
+        }
+        phase ^= 1u;
+    }
+    // every copy that was asked for has to land before the CTA may retire
+#pragma unroll
+    for (int u = 0; u < D; ++u) mbar_wait(bar0 + u * 8, phase);
+}
+#endif
+
 // Masked split launch: does the footprint of task (strip, chunk) -- every row and column its pipeline
 // loads -- hold a flagged interior cell? Tile granularity (JacobiArgs::mtiles); all lanes read the
 // same few bytes.
@@ -831,6 +958,13 @@ FB_DEV bool jacobi_task_flagged(const JacobiArgs<T>& A, int strip, int chunk) {
 template <typename T, int V, int K>
 FB_DEV void jacobi_fast_task(const JacobiArgs<T>& A, int strip, int chunk, int lane, int tid, int nthreads) {
     if (A.mtiles && jacobi_task_flagged<T, V, K>(A, strip, chunk)) return;  // the general kernel runs it
+#if defined(FLUIDB200_TMA_RING) && !defined(FLUIDB200_HOST_EMU)
+    if constexpr (JacobiRing<K>::D == JacobiRing<K>::U) {
+        if (A.hx == T(1) && A.hy == T(1)) jacobi_fast_body_bulk<T, V, K, false>(A, strip, chunk, lane, tid, nthreads);
+        else jacobi_fast_body_bulk<T, V, K, true>(A, strip, chunk, lane, tid, nthreads);
+        return;
+    }
+#endif
     if (A.hx == T(1) && A.hy == T(1)) jacobi_fast_body<T, V, K, false, false>(A, strip, chunk, lane, tid, nthreads);
     else jacobi_fast_body<T, V, K, true, false>(A, strip, chunk, lane, tid, nthreads);
 }
