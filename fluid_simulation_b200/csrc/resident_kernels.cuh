@@ -254,10 +254,31 @@ FB_DEV void resident_body(const ResidentArgs<T>& A) {
             lf[r] = T(0);
             rt[r] = T(0);
         }
-        if (o_up_k == 1) up = *reinterpret_cast<const VT*>(su + o_up_s + par * o_rowpar);
-        else if (o_up_k == 2) get_packets(band + o_up_g + par * o_bandpar, reinterpret_cast<unsigned*>(&up), ModeTag<ROWW>{}, seq);
-        if (o_dn_k == 1) dn = *reinterpret_cast<const VT*>(su + o_dn_s + par * o_rowpar);
-        else if (o_dn_k == 2) get_packets(band + o_dn_g + par * o_bandpar, reinterpret_cast<unsigned*>(&dn), ModeTag<ROWW>{}, seq);
+        if (o_up_k == 2 && o_dn_k == 2) {
+            // both rows come from other tiles: ask for both at once and spin on both (one trip through L2, not two)
+            const unsigned long long* sa = band + o_up_g + par * o_bandpar;
+            const unsigned long long* sb = band + o_dn_g + par * o_bandpar;
+            unsigned* wa = reinterpret_cast<unsigned*>(&up);
+            unsigned* wb = reinterpret_cast<unsigned*>(&dn);
+            bool ok;
+            do {
+                ok = true;
+#pragma unroll
+                for (int k = 0; k < ROWW; k += 2) {
+                    unsigned long long a, c, d, e;
+                    asm volatile("ld.volatile.global.v2.u64 {%0, %1}, [%2];" : "=l"(a), "=l"(c) : "l"(sa + k) : "memory");
+                    asm volatile("ld.volatile.global.v2.u64 {%0, %1}, [%2];" : "=l"(d), "=l"(e) : "l"(sb + k) : "memory");
+                    wa[k] = (unsigned)a; wa[k + 1] = (unsigned)c;
+                    wb[k] = (unsigned)d; wb[k + 1] = (unsigned)e;
+                    ok = ok && (unsigned)(a >> 32) == seq && (unsigned)(c >> 32) == seq && (unsigned)(d >> 32) == seq && (unsigned)(e >> 32) == seq;
+                }
+            } while (!ok);
+        } else {
+            if (o_up_k == 1) up = *reinterpret_cast<const VT*>(su + o_up_s + par * o_rowpar);
+            else if (o_up_k == 2) get_packets(band + o_up_g + par * o_bandpar, reinterpret_cast<unsigned*>(&up), ModeTag<ROWW>{}, seq);
+            if (o_dn_k == 1) dn = *reinterpret_cast<const VT*>(su + o_dn_s + par * o_rowpar);
+            else if (o_dn_k == 2) get_packets(band + o_dn_g + par * o_bandpar, reinterpret_cast<unsigned*>(&dn), ModeTag<ROWW>{}, seq);
+        }
         // (every lane reads the same run: one broadcast access; only lane 0 / 31 use it)
         if (o_lf_k == 1) load_run<T, R, false>(su + o_lf_s + par * o_colpar, lf);
         else if (o_lf_k == 2) get_packets(band + o_lf_g + par * o_bandpar, reinterpret_cast<unsigned*>(lf), ModeTag<COLW>{}, seq);
