@@ -9,11 +9,18 @@ the 16384 x 16384 fp32 lid-driven cavity per GPU (BASELINE.json configs[2]; weak
 16384*N x 16384 over N x-slabs). Prints ONE JSON line (rank 0).
 
   value     Gcell-updates/s, device-resident state, CUDA events on the launching stream
-  roofline  the Jacobi kernel: algorithmic bytes (12 B x cells x sweeps-per-launch) / mean launch
-            time measured with events inside the same timed steps, vs MEASURED_PEAKS.json
-  e2e       same metric through the C ABI with HOST buffers: every step uploads u,v,p from pinned
-            host memory, runs one timestep, downloads u,v,p
-  cpu_baseline  the reference's threaded C++ solver (oracle/_ref) on a bounded sample, host cores
+  roofline  the Jacobi launch (k blocked sweeps): achieved = compulsory DRAM bytes of a launch (12 B x cells) / mean launch
+            time measured with events inside the same timed steps; frac = that / MEASURED_PEAKS.json; .algorithmic = the
+            12 B/cell/sweep figure (k times larger); .traffic = ncu DRAM bytes per launch (profiles/, dropped when the
+            kernel sources changed since the capture); .other_kernels, .whole_step
+  e2e       same metric through the C ABI with HOST buffers: fluidb200_migrate_solve on pinned arrays, every step
+            (upload, compute, download pipelined over row chunks); .separate_calls = upload / solve / download unpipelined
+  cpu_baseline  the reference's threaded C++ solver (oracle/_ref, its fixed 8 threads) and, under .serial, its serial
+            solver (1 core), each on a bounded sample, on this box's host cores
+  headline_general_spacing   the same step with a spacing that is not a power of two (general division-free arithmetic)
+  config0_41x41, config1_1000x1000   BASELINE.json configs[0], [1] (1000 steps x 50 sweeps): resident solver, streaming
+            kernels, the reference's CPU solvers and the reference's CUDA solver compiled for sm_100a, same box
+  N > 1: value = weak scaling (16384 rows per GPU); config.strong = 32768^2 over the same ranks + on one GPU
 --impl reference times the reference's own CPU implementation on this box's host cores.
 """
 from __future__ import annotations

@@ -14,7 +14,6 @@
 #include <string.h>
 
 #include <algorithm>
-#include <atomic>
 #include <new>
 #include <string>
 #include <thread>
@@ -57,9 +56,6 @@ struct fluidb200_multi {
     fluidb200_edges edges[3];
     unsigned seq = 0;
     bool fresh = true;          // state was (re)written from the host: settle before the first pushes
-    bool same_device = false;   // several slabs share a device (tests): waits must not occupy an SM
-    int64_t launches = 0;
-    std::string error;
 };
 
 namespace {
@@ -230,8 +226,6 @@ extern "C" int fluidb200_multi_create(fluidb200_multi** out, int dtype, int X, i
     for (int d = 0; d < ndev && rc == 0; ++d) {
         Slab& s = m->slabs[d];
         s.device = devices ? devices[d] : d;
-        for (int e = 0; e < d; ++e)
-            if (m->slabs[e].device == s.device) m->same_device = true;
         s.x0 = (int)((long long)d * X / ndev);
         s.x1 = (int)((long long)(d + 1) * X / ndev);
         s.lo = std::max(0, s.x0 - m->H);

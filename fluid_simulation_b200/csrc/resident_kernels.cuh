@@ -61,7 +61,6 @@ FB_DEV void resident_grid_barrier(unsigned* bar, unsigned& epoch, unsigned nctas
 }
 
 template <int M> struct ModeTag { static constexpr int value = M; };
-template <bool B> struct BoolTag { static constexpr bool value = B; };
 
 // N consecutive elements (N * sizeof(T) is 8 or a multiple of 16 bytes, the address aligned likewise) from
 // shared memory, or -- CG -- from L2 past this SM's L1.

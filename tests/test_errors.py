@@ -93,3 +93,48 @@ def test_predictor_and_corrector_argument_checks(lib):
     assert lib.fluidb200_corrector(C.byref(g), p, us, vs, u, v, C.byref(eu), C.byref(ev), None, None, 1e-3, 0.0, 0, 40, None) == EINVAL
     assert lib.fluidb200_corrector(C.byref(g), p, us, vs, u, v, None, C.byref(ev), None, None, 1e-3, 1.0, 0, 40, None) == EINVAL
     assert lib.fluidb200_cavity_edges(b"x", 1.0, C.byref(eu)) == EINVAL
+
+
+def test_migrate_solve_argument_checks_and_plain_sequence(lib):
+    """NULL arguments are refused; with interior flags or several timesteps the call is the plain
+    upload + solve + download (same bits as those three calls)."""
+    from oracle import Oracle
+    h = C.c_void_p()
+    assert lib.fluidb200_create(C.byref(h), 0, 30, 20, 1.0, 1.0) == 0
+    bad = (C.c_void_p * 3)()
+    assert lib.fluidb200_migrate_solve(h, None, bad) == EINVAL
+    assert lib.fluidb200_migrate_solve(h, bad, bad) == EINVAL and "host_in[0]" in _msg(lib)
+    assert lib.fluidb200_migrate_solve(None, bad, bad) == EINVAL
+    rng = np.random.default_rng(0)
+    st = [(0.01 * rng.standard_normal((30, 20))).astype(np.float32) for _ in range(3)]
+    out = [np.empty((30, 20), np.float32) for _ in range(3)]
+    assert lib.fluidb200_upload_cavity(h, 1.0) == 0
+    assert lib.fluidb200_set_params(h, 1e-4, 0.1, 1.0, 5, 2) == 0      # two timesteps: no chunk pipeline
+    pi = (C.c_void_p * 3)(*[a.ctypes.data for a in st])
+    po = (C.c_void_p * 3)(*[a.ctypes.data for a in out])
+    assert lib.fluidb200_migrate_solve(h, pi, po) == 0
+    o = Oracle(30, 20).set_cavity(1.0)
+    for n, a in zip(("u", "v", "p"), st):
+        getattr(o, n)[:] = a
+    o.p_next[:] = o.p
+    o.time_step, o.num_iterations, o.num_poisson_iterations = 1e-4, 2, 5
+    o.solve()
+    for n, a in zip(("u", "v", "p"), out):
+        H.assert_bit_equal(a, getattr(o, n), f"migrate_solve/plain:{n}")
+    assert lib.fluidb200_destroy(h) == 0
+
+
+def test_multi_handle_argument_checks(lib):
+    m = C.c_void_p()
+    assert lib.fluidb200_multi_create(C.byref(m), 7, 40, 40, 1.0, 1.0, 1, None) == EINVAL
+    assert lib.fluidb200_multi_create(C.byref(m), 0, 2, 40, 1.0, 1.0, 1, None) == EINVAL
+    assert lib.fluidb200_multi_create(C.byref(m), 0, 40, 40, 1.0, 1.0, 0, None) == EINVAL
+    assert lib.fluidb200_multi_create(C.byref(m), 0, 40, 40, 1.0, 1.0, 8, None) == EINVAL and "too thin" in _msg(lib)
+    assert lib.fluidb200_multi_create(None, 0, 40, 40, 1.0, 1.0, 1, None) == EINVAL
+    assert lib.fluidb200_multi_create(C.byref(m), 0, 40, 40, 1.0, 1.0, 1, None) == 0
+    assert lib.fluidb200_multi_num_slabs(m) == 1
+    assert lib.fluidb200_multi_set_params(m, 0.001, 0.1, 1.0, -1, 1) == EINVAL
+    assert lib.fluidb200_multi_set_params(m, 0.0, 0.1, 1.0, 5, 1) == 0 and lib.fluidb200_multi_solve(m) == EINVAL
+    assert lib.fluidb200_multi_download(m, 9, C.c_void_p(1)) == EINVAL
+    assert lib.fluidb200_multi_solve(None) == EINVAL and lib.fluidb200_multi_destroy(None) == 0
+    assert lib.fluidb200_multi_destroy(m) == 0
