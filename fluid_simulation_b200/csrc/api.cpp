@@ -218,7 +218,12 @@ void split_jacobi(fb::JacobiArgs<T>* a, const fluidb200_slab* g, int K, int nchu
     // a launch that cannot fill the GPU a few times over is latency bound: the extra kernels and the
     // fork/join events cost more than the extra occupancy brings (measured, us per depth-3 launch,
     // split vs single kernel: 1000^2 18.0 vs 14.8, 1536^2 19.1 vs 19.3, 2048^2 21.7 vs 27.3)
-    if ((long long)(sf_hi - sf_lo) * (cf_hi - cf_lo) < (long long)env_int("FLUIDB200_SPLIT_MIN_TASKS", 2048)) return;
+    // Exception: a range inside a SLAB of a wide grid (the halo strips of the multi-GPU drivers, swept beside the
+    // slab's big interior launch). There the general kernel's 218 registers are the cost: one of its CTAs on an SM
+    // pushes two of the interior launch's lean CTAs (3 x 162 registers fill the file) off it, whereas lean CTAs of the
+    // same kind pack with them. Measured on a 4096 x 32768 slab: 313 us per launch with ~40 us of that displacement.
+    const bool slab_strip = nstrips >= 32 && (g->row0 > 0 || g->row0 + g->rows < g->X);
+    if ((long long)(sf_hi - sf_lo) * (cf_hi - cf_lo) < (long long)env_int("FLUIDB200_SPLIT_MIN_TASKS", 2048) && !slab_strip) return;
     a->part = 1;
     a->sf_lo = sf_lo; a->sf_hi = sf_hi; a->cf_lo = cf_lo; a->cf_hi = cf_hi;
     // the lean EDGE kernel knows constant and copy boundary cells; per-cell arrays stay with the general kernel
