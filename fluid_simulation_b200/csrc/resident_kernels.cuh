@@ -401,7 +401,7 @@ FB_DEV void resident_body(const ResidentArgs<T>& A) {
         UV<T> r = tentative_cell<T, MODE>(A.pa, su[c], sv[c], su[c - FP], su[c + FP], su[c - 1], su[c + 1], sv[c - FP],
                                           sv[c + FP], sv[c - 1], sv[c + 1], fl);
         if (MODE != DIV_EXACT && fl.raised(A.pa.m.pow2_lo_m1))
-            r = tentative_cell_exact<T>(A.pa, su[c], sv[c], su[c - FP], su[c + FP], su[c - 1], su[c + 1], sv[c - FP],
+            r = tentative_cell_exact<T, MODE>(A.pa, su[c], sv[c], su[c - FP], su[c + FP], su[c - 1], su[c + 1], sv[c - FP],
                                         sv[c + FP], sv[c - 1], sv[c + 1]);
         sus[c] = r.u;
         svs[c] = r.v;
@@ -449,7 +449,7 @@ FB_DEV void resident_body(const ResidentArgs<T>& A) {
                     Flags fl;
                     T v = rhs_cell<T, MODE>(A.pa, sus[c + e - FP], sus[c + e + FP], svs[c + e - 1], svs[c + e + 1], fl);
                     if (MODE != DIV_EXACT && fl.raised(A.pa.m.pow2_lo_m1))
-                        v = rhs_cell_exact<T>(A.pa, sus[c + e - FP], sus[c + e + FP], svs[c + e - 1], svs[c + e + 1]);
+                        v = rhs_cell_exact<T, MODE>(A.pa, sus[c + e - FP], sus[c + e + FP], svs[c + e - 1], svs[c + e + 1]);
                     q.a[e] = v;
                 }
                 b[r].a[e] = A_::mul(A_::mul(q.a[e], A.hx), A.hy);   // (rhs * hx) * hy, :144, once per step
@@ -487,7 +487,7 @@ FB_DEV void resident_body(const ResidentArgs<T>& A) {
                             Flags fl;
                             UV<T> q = correct_cell<T, MODE>(A.ca, pm.a[e], pp.a[e], pym.a[e], pyp.a[e], sus[c + e], svs[c + e], fl);
                             if (MODE != DIV_EXACT && fl.raised(A.ca.m.pow2_lo_m1))
-                                q = correct_cell_exact<T>(A.ca, pm.a[e], pp.a[e], pym.a[e], pyp.a[e], sus[c + e], svs[c + e]);
+                                q = correct_cell_exact<T, MODE>(A.ca, pm.a[e], pp.a[e], pym.a[e], pyp.a[e], sus[c + e], svs[c + e]);
                             un.a[e] = q.u;
                             vn.a[e] = q.v;
                         } else if (col == 0) {          // the y edges own their cells for ALL x (:236-264) ...
@@ -713,7 +713,7 @@ FB_DEV void resident_cell_body(const ResidentArgs<T>& A) {
             UV<T> r = tentative_cell<T, MODE>(A.pa, su[c], sv[c], su[c - Y], su[c + Y], su[c - 1], su[c + 1], sv[c - Y],
                                               sv[c + Y], sv[c - 1], sv[c + 1], fl);
             if (MODE != DIV_EXACT && fl.raised(A.pa.m.pow2_lo_m1))
-                r = tentative_cell_exact<T>(A.pa, su[c], sv[c], su[c - Y], su[c + Y], su[c - 1], su[c + 1], sv[c - Y], sv[c + Y],
+                r = tentative_cell_exact<T, MODE>(A.pa, su[c], sv[c], su[c - Y], su[c + Y], su[c - 1], su[c + 1], sv[c - Y], sv[c + Y],
                                             sv[c - 1], sv[c + 1]);
             sus[c] = r.u;
             svs[c] = r.v;
@@ -727,7 +727,7 @@ FB_DEV void resident_cell_body(const ResidentArgs<T>& A) {
             const int c = cell[k];
             Flags fl;
             T q = rhs_cell<T, MODE>(A.pa, sus[c - Y], sus[c + Y], svs[c - 1], svs[c + 1], fl);
-            if (MODE != DIV_EXACT && fl.raised(A.pa.m.pow2_lo_m1)) q = rhs_cell_exact<T>(A.pa, sus[c - Y], sus[c + Y], svs[c - 1], svs[c + 1]);
+            if (MODE != DIV_EXACT && fl.raised(A.pa.m.pow2_lo_m1)) q = rhs_cell_exact<T, MODE>(A.pa, sus[c - Y], sus[c + Y], svs[c - 1], svs[c + 1]);
             b[k] = A_::mul(A_::mul(q, A.hx), A.hy);   // (rhs * hx) * hy, :144, once per step
             if (last_step) {
                 const int x = c / Y;
@@ -749,7 +749,7 @@ FB_DEV void resident_cell_body(const ResidentArgs<T>& A) {
                 const T pym = src[redirected ? aym[k] : c - 1], pyp = src[redirected ? ayp[k] : c + 1];
                 Flags fl;
                 UV<T> q = correct_cell<T, MODE>(A.ca, pxm, pxp, pym, pyp, sus[c], svs[c], fl);
-                if (MODE != DIV_EXACT && fl.raised(A.ca.m.pow2_lo_m1)) q = correct_cell_exact<T>(A.ca, pxm, pxp, pym, pyp, sus[c], svs[c]);
+                if (MODE != DIV_EXACT && fl.raised(A.ca.m.pow2_lo_m1)) q = correct_cell_exact<T, MODE>(A.ca, pxm, pxp, pym, pyp, sus[c], svs[c]);
                 un = q.u;
                 vn = q.v;
             } else {   // the y edges own their cells for all x (:236-264), the x walls the cells between (:266-294)

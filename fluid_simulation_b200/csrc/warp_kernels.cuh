@@ -55,7 +55,22 @@ template <typename T> struct Ar;
 //              branched on, so the ~40 independent chains of a row can overlap;
 //   DIV_POW2   hx and hy are powers of two (unit spacing, 2^k+1 points on a unit box, ...): every
 //              division is an exact scaling, i.e. one correctly rounded multiplication.
-enum { DIV_EXACT = 0, DIV_FAST = 1, DIV_POW2 = 2 };
+enum { DIV_EXACT = 0, DIV_FAST = 1, DIV_POW2 = 2, DIV_POW2_WIDE = 3, DIV_FAST_CHECKED = 4 };
+// What the cells a mode flags are recomputed in (each of these costs the same for every input, unlike an
+// IEEE division, whose slow path the subnormal values at the front of an impulsively started flow take):
+//   DIV_POW2 -> DIV_POW2_WIDE. With power-of-two spacings every division of the reference is an exact
+//     scaling, so the flagged cells (results in the subnormal range, where the float product would round
+//     twice) need no division either: the Laplacian numerator is formed in double, scaled and rounded
+//     once, which is the reference's evaluation to the letter.
+//   DIV_FAST -> DIV_FAST_CHECKED -> DIV_EXACT. The same products as DIV_FAST, each one verified by
+//     rounding the two ends of an interval that holds the reference's double (Ar<float>::rounds_alike);
+//     only a cell that fails this (a tie, or nearly one) takes the divisions.
+template <typename T, int MODE> struct FallbackMode {
+    static constexpr int value = sizeof(T) != 4 ? DIV_EXACT : MODE == DIV_POW2 ? DIV_POW2_WIDE : MODE == DIV_FAST ? DIV_FAST_CHECKED : DIV_EXACT;
+};
+#ifndef FLUIDB200_EXACT_WIDE
+#define FLUIDB200_EXACT_WIDE 1   // fp32 DIV_EXACT central differences go through one double division (0: __fdiv_rn)
+#endif
 
 // What the division-free modes collect over the cells of one row strip. The row is recomputed with
 // DIV_EXACT when raised() says so; nothing branches per cell.
@@ -85,14 +100,32 @@ template <> struct Ar<float> {
     // DIV_POW2: d * (1/h2) is the same real number as d / h2 and is rounded once, like the division.
     template <int MODE>
     static FB_DEV float cdiff(float a, float b, float h, float h2, double inv_h2, float inv_h2f, Flags& fl) {
-        (void)h;
+        (void)h; (void)h2;
         const float d = __fsub_rn(a, b);
+#if FLUIDB200_EXACT_WIDE
+        // the reference's own evaluation, literally: d / 2. (exact) and one double division, rounded to float.
+        // Every float, subnormals included, is a NORMAL double, so the cost does not depend on the data.
+        if (MODE == DIV_EXACT) return __double2float_rn(__ddiv_rn(__dmul_rn((double)d, 0.5), (double)h));
+#else
         if (MODE == DIV_EXACT) return __fdiv_rn(d, h2);
-        if (MODE == DIV_POW2) return __fmul_rn(d, inv_h2f);
+#endif
+        if (MODE == DIV_POW2 || MODE == DIV_POW2_WIDE) return __fmul_rn(d, inv_h2f);
         // (float -> double is exact for every input, subnormals included; inf/nan propagate like the division)
-        const float r = __double2float_rn(__dmul_rn((double)d, inv_h2));
-        fl.bad |= (d != 0.0f) && (fabsf(r) < 7.52316385e-37f /* 2^-120 */);
+        const double q = __dmul_rn((double)d, inv_h2);
+        const float r = __double2float_rn(q);
+        if (MODE == DIV_FAST_CHECKED) fl.bad |= !rounds_alike(q);
+        else fl.bad |= (d != 0.0f) && (fabsf(r) < 7.52316385e-37f /* 2^-120 */);
         return r;
+    }
+    // q~ and the reference's double T are both within 2^-52 (relative) of the exact quotient, so T lies
+    // inside q~ (1 +- 2^-50) even after the two products below are rounded. Rounding to float is monotone:
+    // when both ends of that interval round to the same float, so do q~ and T. (DIV_FAST_CHECKED: the
+    // second evaluation of a cell DIV_FAST flagged, typically for a result in the subnormal range, whose
+    // coarse, absolute float grid allows ties -- if very rarely.)
+    static FB_DEV bool rounds_alike(double q) {
+        const float lo = __double2float_rn(__dmul_rn(q, 1.0 - 0x1p-50));
+        const float hi = __double2float_rn(__dmul_rn(q, 1.0 + 0x1p-50));
+        return lo == hi;
     }
     // (s - 4.*c) / hx / hy with s already rounded to float: the one place the fp32 path is
     // observably mixed precision (SerialNavierStokes.cpp:308-311). 4.*c is exact in double, so
@@ -126,9 +159,11 @@ template <> struct Ar<float> {
         const double d = __fma_rn(-4.0, (double)c, (double)s);
         const double q = __dmul_rn(d, inv_hxhy);
         const float r = __double2float_rn(q);
+        if (MODE == DIV_POW2_WIDE) return r;   // q == T: the two divisions are exact scalings
         // distance of the 29 sub-float bits of q from the midpoint pattern, as one unsigned compare
         const unsigned low = (unsigned)__double2loint(q) & 0x1fffffffu;
-        fl.bad |= (low - 0x0ffffff0u) <= 32u || (fabsf(r) < 7.52316385e-37f && d != 0.0);
+        if (MODE == DIV_FAST_CHECKED) fl.bad |= !rounds_alike(q);   // (|T - q~| <= 2^-51 |q~| here too)
+        else fl.bad |= (low - 0x0ffffff0u) <= 32u || (fabsf(r) < 7.52316385e-37f && d != 0.0);
         return r;
     }
     // t *= -0.25 : the double multiply is exact, so this is one float rounding (subnormals).
@@ -1024,11 +1059,14 @@ FB_DEV UV<T> tentative_cell(const PredictorArgs<T>& A, T uc, T vc, T uxm, T uxp,
     r.v = A_::add(vc, A_::mul(A.dt, dv_dt));
     return r;
 }
-template <typename T>
+template <typename T, int MODE>
 FB_DEV_NOINLINE UV<T> tentative_cell_exact(const PredictorArgs<T>& A, T uc, T vc, T uxm, T uxp, T uym, T uyp, T vxm,
                                            T vxp, T vym, T vyp) {
+    constexpr int FB = FallbackMode<T, MODE>::value;
     Flags fl;
-    return tentative_cell<T, DIV_EXACT>(A, uc, vc, uxm, uxp, uym, uyp, vxm, vxp, vym, vyp, fl);
+    UV<T> r = tentative_cell<T, FB>(A, uc, vc, uxm, uxp, uym, uyp, vxm, vxp, vym, vyp, fl);
+    if (FB == DIV_FAST_CHECKED && fl.bad) r = tentative_cell<T, DIV_EXACT>(A, uc, vc, uxm, uxp, uym, uyp, vxm, vxp, vym, vyp, fl);
+    return r;
 }
 
 // u_next, v_next of one interior row strip from rows x-1 (um,vm), x (u0,v0), x+1 (up,vp) of u, v.
@@ -1052,7 +1090,7 @@ FB_DEV void tentative_row(const PredictorArgs<T>& A, const Vec<T, V>& um, const 
     if (MODE != DIV_EXACT && fl.raised(A.m.pow2_lo_m1)) {
 #pragma unroll
         for (int e = 0; e < V; ++e) {
-            const UV<T> r = tentative_cell_exact<T>(A, u0.a[e], v0.a[e], um.a[e], up_.a[e], uym.a[e], uyp.a[e],
+            const UV<T> r = tentative_cell_exact<T, MODE>(A, u0.a[e], v0.a[e], um.a[e], up_.a[e], uym.a[e], uyp.a[e],
                                                     vm.a[e], vp_.a[e], vym.a[e], vyp.a[e]);
             us.a[e] = r.u;
             vs.a[e] = r.v;
@@ -1069,10 +1107,13 @@ FB_DEV T rhs_cell(const PredictorArgs<T>& A, T us_m, T us_p, T vs_ym, T vs_yp, F
     const T dv_next_dy = A_::template cdiff<MODE>(vs_yp, vs_ym, A.m.hy, A.m.hy2, A.m.inv_hy2, A.m.inv_hy2f, fl);
     return A_::mul(A.rho_over_dt, A_::add(du_next_dx, dv_next_dy));
 }
-template <typename T>
+template <typename T, int MODE>
 FB_DEV_NOINLINE T rhs_cell_exact(const PredictorArgs<T>& A, T us_m, T us_p, T vs_ym, T vs_yp) {
+    constexpr int FB = FallbackMode<T, MODE>::value;
     Flags fl;
-    return rhs_cell<T, DIV_EXACT>(A, us_m, us_p, vs_ym, vs_yp, fl);
+    T r = rhs_cell<T, FB>(A, us_m, us_p, vs_ym, vs_yp, fl);
+    if (FB == DIV_FAST_CHECKED && fl.bad) r = rhs_cell<T, DIV_EXACT>(A, us_m, us_p, vs_ym, vs_yp, fl);
+    return r;
 }
 template <typename T, int V, int MODE>
 FB_DEV Vec<T, V> rhs_row(const PredictorArgs<T>& A, const Vec<T, V>& us_m, const Vec<T, V>& us_p, const Vec<T, V>& vs0) {
@@ -1083,7 +1124,7 @@ FB_DEV Vec<T, V> rhs_row(const PredictorArgs<T>& A, const Vec<T, V>& us_m, const
     for (int e = 0; e < V; ++e) q.a[e] = rhs_cell<T, MODE>(A, us_m.a[e], us_p.a[e], vym.a[e], vyp.a[e], fl);
     if (MODE != DIV_EXACT && fl.raised(A.m.pow2_lo_m1)) {
 #pragma unroll
-        for (int e = 0; e < V; ++e) q.a[e] = rhs_cell_exact<T>(A, us_m.a[e], us_p.a[e], vym.a[e], vyp.a[e]);
+        for (int e = 0; e < V; ++e) q.a[e] = rhs_cell_exact<T, MODE>(A, us_m.a[e], us_p.a[e], vym.a[e], vyp.a[e]);
     }
     return q;
 }
@@ -1301,10 +1342,13 @@ FB_DEV UV<T> correct_cell(const CorrectorArgs<T>& A, T pxm, T pxp, T pym, T pyp,
     r.v = A_::sub(vs, A_::mul(A.dt_over_rho, dp_dy));
     return r;
 }
-template <typename T>
+template <typename T, int MODE>
 FB_DEV_NOINLINE UV<T> correct_cell_exact(const CorrectorArgs<T>& A, T pxm, T pxp, T pym, T pyp, T us, T vs) {
+    constexpr int FB = FallbackMode<T, MODE>::value;
     Flags fl;
-    return correct_cell<T, DIV_EXACT>(A, pxm, pxp, pym, pyp, us, vs, fl);
+    UV<T> r = correct_cell<T, FB>(A, pxm, pxp, pym, pyp, us, vs, fl);
+    if (FB == DIV_FAST_CHECKED && fl.bad) r = correct_cell<T, DIV_EXACT>(A, pxm, pxp, pym, pyp, us, vs, fl);
+    return r;
 }
 template <typename T, int V, int MODE>
 FB_DEV void correct_row(const CorrectorArgs<T>& A, const Vec<T, V>& pm, const Vec<T, V>& p0, const Vec<T, V>& pp_,
@@ -1321,7 +1365,7 @@ FB_DEV void correct_row(const CorrectorArgs<T>& A, const Vec<T, V>& pm, const Ve
     if (MODE != DIV_EXACT && fl.raised(A.m.pow2_lo_m1)) {
 #pragma unroll
         for (int e = 0; e < V; ++e) {
-            const UV<T> r = correct_cell_exact<T>(A, pm.a[e], pp_.a[e], pym.a[e], pyp.a[e], us.a[e], vs.a[e]);
+            const UV<T> r = correct_cell_exact<T, MODE>(A, pm.a[e], pp_.a[e], pym.a[e], pyp.a[e], us.a[e], vs.a[e]);
             un.a[e] = r.u;
             vn.a[e] = r.v;
         }

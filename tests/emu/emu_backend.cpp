@@ -255,13 +255,20 @@ EMU_NO_LINK(fluidb200_halo_wait, void*, uint32_t, void*)
 
 // Test hooks: the product's exact-rounding arithmetic (Ar<float>), element-wise, so that its
 // division-free modes can be hammered against the reference formulas in NumPy. A flagged
-// element is recomputed in DIV_EXACT, like the kernels do per row.
+// element is recomputed in the mode's fallback, like the kernels do per row.
+static long long g_second_fallbacks = 0;   // elements that failed the checked products and took the divisions
+extern "C" long long emu_second_fallbacks(void) { const long long n = g_second_fallbacks; g_second_fallbacks = 0; return n; }
 template <int MODE> static void cdiff_hook(const float* a, const float* b, float h, long long n, float* out) {
     const fb::Metric<float> m = fb::make_metric<float>(h, h);
     for (long long i = 0; i < n; ++i) {
         fb::Flags fl;
         out[i] = fb::Ar<float>::cdiff<MODE>(a[i], b[i], m.hx, m.hx2, m.inv_hx2, m.inv_hx2f, fl);
-        if (fl.raised(m.pow2_lo_m1)) out[i] = fb::Ar<float>::cdiff<fb::DIV_EXACT>(a[i], b[i], m.hx, m.hx2, m.inv_hx2, m.inv_hx2f, fl);
+        if (fl.raised(m.pow2_lo_m1)) {
+            constexpr int FB = fb::FallbackMode<float, MODE>::value;
+            fb::Flags f2;
+            out[i] = fb::Ar<float>::cdiff<FB>(a[i], b[i], m.hx, m.hx2, m.inv_hx2, m.inv_hx2f, f2);
+            if (FB == fb::DIV_FAST_CHECKED && f2.bad) { out[i] = fb::Ar<float>::cdiff<fb::DIV_EXACT>(a[i], b[i], m.hx, m.hx2, m.inv_hx2, m.inv_hx2f, f2); ++g_second_fallbacks; }
+        }
     }
 }
 template <int MODE> static void lap_hook(const float* s, const float* c, float hx, float hy, long long n, float* out) {
@@ -269,7 +276,12 @@ template <int MODE> static void lap_hook(const float* s, const float* c, float h
     for (long long i = 0; i < n; ++i) {
         fb::Flags fl;
         out[i] = fb::Ar<float>::lap_tail<MODE>(s[i], c[i], m.hx, m.hy, m.inv_hxhy, m.inv_hxhyf, fl);
-        if (fl.raised(m.pow2_lo_m1)) out[i] = fb::Ar<float>::lap_tail<fb::DIV_EXACT>(s[i], c[i], m.hx, m.hy, m.inv_hxhy, m.inv_hxhyf, fl);
+        if (fl.raised(m.pow2_lo_m1)) {
+            constexpr int FB = fb::FallbackMode<float, MODE>::value;
+            fb::Flags f2;
+            out[i] = fb::Ar<float>::lap_tail<FB>(s[i], c[i], m.hx, m.hy, m.inv_hxhy, m.inv_hxhyf, f2);
+            if (FB == fb::DIV_FAST_CHECKED && f2.bad) { out[i] = fb::Ar<float>::lap_tail<fb::DIV_EXACT>(s[i], c[i], m.hx, m.hy, m.inv_hxhy, m.inv_hxhyf, f2); ++g_second_fallbacks; }
+        }
     }
 }
 extern "C" int emu_metric_mode_f32(float hx, float hy) { return fb::make_metric<float>(hx, hy).mode; }
