@@ -1174,12 +1174,14 @@ extern "C" int fluidb200_set_resident(fluidb200_solver* s, int enable) {
     return 0;
 }
 // (measurement aid) cycles per phase of the last resident launch made with FLUIDB200_RESIDENT_PROF=1:
-// out[0..7] = ring load + grid barrier, tentative velocity, right-hand side, sweeps, corrector, write-back, -, -
-extern "C" int fluidb200_resident_profile(fluidb200_solver* s, unsigned long long out[8]) {
+// out[0..5] = ring load + grid barrier, tentative velocity, right-hand side, sweeps (the rest after the split below), corrector, write-back;
+// out[8..12] = inside the sweeps: waiting for the borders, first + last row and their publication, rows between, fix-ups + columns, CTA barrier;
+// out[13] = polling rounds
+extern "C" int fluidb200_resident_profile(fluidb200_solver* s, unsigned long long out[24]) {
     if (!s || !out || !s->res_scratch) return fail(FLUIDB200_ESTATE, "no resident launch to report on");
     BE_CHECK(fbk::be_stream_sync(s->stream), "resident profile");
     const size_t words = fb::resident_sync_words(s->res_plan.tiles_x * s->res_plan.tiles_y);
-    BE_CHECK(fbk::be_memcpy_async(out, (char*)s->res_scratch + words * sizeof(unsigned) + 64, 64, fbk::D2H, s->stream), "resident profile");
+    BE_CHECK(fbk::be_memcpy_async(out, (char*)s->res_scratch + words * sizeof(unsigned) + 64, 192, fbk::D2H, s->stream), "resident profile");
     BE_CHECK(fbk::be_stream_sync(s->stream), "resident profile");
     return 0;
 }

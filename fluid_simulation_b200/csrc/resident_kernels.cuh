@@ -198,6 +198,27 @@ FB_DEV void resident_body(const ResidentArgs<T>& A) {
         b[r] = vzero<T, V>();
     }
 
+    // FLUIDB200_RESIDENT_PROF=1 at run time: cycles per phase of a timestep. The split of a SWEEP (five more ticks per
+    // sweep, ~4 % of a 1000^2 step even when switched off) is compiled in only with -DFLUIDB200_RESIDENT_SUBPROF=1.
+#ifndef FLUIDB200_RESIDENT_SUBPROF
+#define FLUIDB200_RESIDENT_SUBPROF 0
+#endif
+    long long t_prev = 0;
+    const bool profiled = A.prof && tid == 0 && tile == ntiles / 2;
+    __shared__ unsigned long long prof_s[16];   // (added up in shared memory with fire-and-forget reductions: a tick must not stall the warp)
+    if (profiled) {
+        for (int k = 0; k < 16; ++k) prof_s[k] = 0;
+    }
+    auto tick = [&](int k) {   // (only when asked for: one thread of a middle tile adds up its cycles per phase)
+        if (k >= 8 && !FLUIDB200_RESIDENT_SUBPROF) return;
+        if (profiled) {
+            const long long t = clock64();
+            atomicAdd(&prof_s[k], (unsigned long long)(t - t_prev));
+            t_prev = t;
+        }
+    };
+    unsigned polls = 0;
+
     // ---- exchange of patch borders ----------------------------------------------------------
     // NW 32-bit words -> NW packets carrying sequence number `seq`, stored 16 bytes (two packets) at a time
     auto put_packets = [&](unsigned long long* dst, const unsigned* w, auto nw_tag, unsigned seq) {
@@ -215,6 +236,7 @@ FB_DEV void resident_body(const ResidentArgs<T>& A) {
         bool ok;
         do {
             ok = true;
+            if (FLUIDB200_RESIDENT_SUBPROF) ++polls;
 #pragma unroll
             for (int k = 0; k < NW; k += 2) {
                 unsigned long long a, c;
@@ -253,7 +275,8 @@ FB_DEV void resident_body(const ResidentArgs<T>& A) {
             lf[r] = T(0);
             rt[r] = T(0);
         }
-        if (o_up_k == 2 && o_dn_k == 2) {
+        const bool need_up = o_up_k == 2, need_dn = o_dn_k == 2;
+        if (need_up && need_dn) {
             // both rows come from other tiles: ask for both at once and spin on both (one trip through L2, not two)
             const unsigned long long* sa = band + o_up_g + par * o_bandpar;
             const unsigned long long* sb = band + o_dn_g + par * o_bandpar;
@@ -262,6 +285,7 @@ FB_DEV void resident_body(const ResidentArgs<T>& A) {
             bool ok;
             do {
                 ok = true;
+                if (FLUIDB200_RESIDENT_SUBPROF) ++polls;
 #pragma unroll
                 for (int k = 0; k < ROWW; k += 2) {
                     unsigned long long a, c, d, e;
@@ -274,9 +298,9 @@ FB_DEV void resident_body(const ResidentArgs<T>& A) {
             } while (!ok);
         } else {
             if (o_up_k == 1) up = *reinterpret_cast<const VT*>(su + o_up_s + par * o_rowpar);
-            else if (o_up_k == 2) get_packets(band + o_up_g + par * o_bandpar, reinterpret_cast<unsigned*>(&up), ModeTag<ROWW>{}, seq);
+            else if (need_up) get_packets(band + o_up_g + par * o_bandpar, reinterpret_cast<unsigned*>(&up), ModeTag<ROWW>{}, seq);
             if (o_dn_k == 1) dn = *reinterpret_cast<const VT*>(su + o_dn_s + par * o_rowpar);
-            else if (o_dn_k == 2) get_packets(band + o_dn_g + par * o_bandpar, reinterpret_cast<unsigned*>(&dn), ModeTag<ROWW>{}, seq);
+            else if (need_dn) get_packets(band + o_dn_g + par * o_bandpar, reinterpret_cast<unsigned*>(&dn), ModeTag<ROWW>{}, seq);
         }
         // (every lane reads the same run: one broadcast access; only lane 0 / 31 use it)
         if (o_lf_k == 1) load_run<T, R, false>(su + o_lf_s + par * o_colpar, lf);
@@ -352,11 +376,13 @@ FB_DEV void resident_body(const ResidentArgs<T>& A) {
         VT up, dn;
         T lf[R], rt[R];
         fetch((g + 1) & 1, (unsigned)(g + 1), up, dn, lf, rt);
+        tick(8);
         if (o_general) fix_neighbours(g > 0, dn, rt);
         const VT old0 = p[0], oldL = p[R - 1];
         const VT new0 = one_row(up, old0, p[1], lf[0], rt[0], b[0]);
         const VT newL = one_row(p[R - 2], oldL, dn, lf[R - 1], rt[R - 1], b[R - 1]);
         publish_rows(g & 1, (unsigned)(g + 2), new0, newL);
+        tick(9);
         VT prev = old0;
 #pragma unroll
         for (int r = 1; r < R - 1; ++r) {
@@ -367,8 +393,10 @@ FB_DEV void resident_body(const ResidentArgs<T>& A) {
         }
         p[0] = new0;
         p[R - 1] = newL;
+        tick(10);
         if (o_general) fix_boundary_cells();
         publish_cols(g & 1, (unsigned)(g + 2));
+        tick(11);
     };
 
     // ---- predictor: u_next, v_next on the tile + 1 ring, rhs on the patch (SerialNavierStokes.cpp:298-335) ----
@@ -545,14 +573,7 @@ FB_DEV void resident_body(const ResidentArgs<T>& A) {
     publish_cols(1, 1u);
     __syncthreads();
     unsigned epoch = 0;
-    long long t_prev = clock64();
-    auto tick = [&](int k) {   // (only when asked for: one thread of a middle tile adds up its cycles per phase)
-        if (A.prof && tid == 0 && tile == ntiles / 2) {
-            const long long t = clock64();
-            A.prof[k] += (unsigned long long)(t - t_prev);
-            t_prev = t;
-        }
-    };
+    t_prev = clock64();
     const int G = A.S * A.K;
     int g = 0;
     for (int step = 0; step < A.S; ++step) {
@@ -582,6 +603,7 @@ FB_DEV void resident_body(const ResidentArgs<T>& A) {
             }
             sweep(g);
             __syncthreads();
+            tick(12);
         }
         // a tile may overwrite u, v only when no other tile still reads them for ITS predictor: three
         // sweeps of neighbour hand-shakes order that even for the diagonal tiles; fewer do not
@@ -633,6 +655,10 @@ FB_DEV void resident_body(const ResidentArgs<T>& A) {
         P[(long long)(X - 1) * pitch + Y - 1] = top_use ? top_v : c11;
     }
     tick(5);
+    if (profiled) {
+        for (int k = 0; k < 13; ++k) A.prof[k] += prof_s[k];
+        A.prof[13] += polls;
+    }
 }
 
 

@@ -284,7 +284,7 @@ int fluidb200_set_resident(fluidb200_solver* s, int enable);
 int64_t fluidb200_resident_launch_count(const fluidb200_solver* s); /* solve() calls that took that path */
 /* Measurement aid: SM cycles one tile spent per phase of the last such launch when FLUIDB200_RESIDENT_PROF=1
  * (halo load + barrier, tentative velocity, right-hand side, sweeps, corrector, write-back, -, -). */
-int fluidb200_resident_profile(fluidb200_solver* s, unsigned long long out[8]);
+int fluidb200_resident_profile(fluidb200_solver* s, unsigned long long out[24]);
 /* Kernels launched by this solver since creation (for bench.py's gpu_launches). */
 int64_t fluidb200_launch_count(const fluidb200_solver* s);         /* kernels launched so far (a split Jacobi launch = 3) */
 

@@ -61,6 +61,67 @@ def test_central_difference_matches_reference_formula(emu, h):
         assert ok.all(), f"h={h} mode {mode}: {np.count_nonzero(~ok)} mismatches, first {a[~ok][:3]}, {b[~ok][:3]}"
 
 
+def test_central_difference_over_many_spacings(emu):
+    """The division-free central difference over 400 spacings drawn at random -- among them spacings one ulp
+    away from a power of two and significands that are nearly all ones -- with numerators chosen so that the
+    quotient lands on, or next to, the midpoint of two floats (d = RN32(m * 2h), m a midpoint): the cases a
+    wrong last-bit correction would get wrong."""
+    rng = np.random.default_rng(11)
+    n = 60_000
+    hs = list(np.exp2(rng.uniform(-20, 6, 380)).astype(np.float32))
+    for e in (-7, 0, 3):
+        one = np.float32(2.0 ** e)
+        hs += [np.nextafter(one, np.float32(0)), np.nextafter(one, np.float32(4 * one)),
+               np.nextafter(np.nextafter(one, np.float32(0)), np.float32(0))]
+    hs += [np.float32(1.0 / 999), np.float32(1.0 / 40), np.float32(1.0 / 16383), np.float32(1.9999998), np.float32(1.9999996),
+           np.float32(0.99999994 / 2), np.float32(3.0), np.float32(5.0), np.float32(0.3), np.float32(1.0 / 3), np.float32(1e-3)]
+    bad = []
+    for h32 in hs:
+        h32 = np.float32(h32)
+        if emu.emu_metric_mode_f32(h32, h32) != 1:
+            continue
+        a, b = _inputs(n, 100), np.zeros(n, np.float32)
+        m = rng.uniform(1.0, 2.0, n // 2).astype(np.float32).astype(np.float64) + 2.0 ** -24      # midpoints of floats in [1, 2)
+        scale = np.exp2(rng.integers(-30, 30, n // 2).astype(np.float64))
+        a[: n // 2] = (m * scale * 2.0 * np.float64(h32)).astype(np.float32)
+        a[n // 2: n // 2 + n // 4] *= np.float32(1e-20)                                            # small, still normal
+        with np.errstate(all="ignore"):
+            d = (a - b).astype(np.float32)
+            want = (d.astype(np.float64) / 2.0 / np.float64(h32)).astype(np.float32)
+        out = np.empty(n, np.float32)
+        emu.emu_cdiff_f32(1, a.ctypes.data, b.ctypes.data, h32, n, out.ctypes.data)
+        ok = (out.view(np.uint32) == want.view(np.uint32)) | (np.isnan(out) & np.isnan(want))
+        if not ok.all():
+            bad.append((float(h32), int(np.count_nonzero(~ok)), a[~ok][:2].tolist()))
+    assert not bad, bad[:5]
+
+
+def test_second_fallback_is_rare_and_ties_take_it(emu):
+    """Flagged elements are first re-evaluated with checked products (DIV_FAST_CHECKED); only a quotient on or
+    next to a rounding boundary goes on to the divisions. Random subnormal quotients never do; exact ties
+    in the subnormal range (h = 3: k * 2^-149 / 6) always do."""
+    rng = np.random.default_rng(12)
+    n = 200_000
+    h32 = np.float32(1.0 / 999)
+    a = (rng.uniform(1, 2, n) * np.exp2(rng.integers(-149, -100, n).astype(np.float64))).astype(np.float32)
+    b = np.zeros(n, np.float32)
+    out = np.empty(n, np.float32)
+    emu.emu_second_fallbacks.restype = C.c_longlong
+    emu.emu_second_fallbacks()
+    emu.emu_cdiff_f32(1, a.ctypes.data, b.ctypes.data, h32, n, out.ctypes.data)
+    assert emu.emu_second_fallbacks() <= 2
+    want = (a.astype(np.float64) / 2.0 / np.float64(h32)).astype(np.float32)
+    assert np.array_equal(out.view(np.uint32), want.view(np.uint32))
+    k = np.arange(3, 6000, 6, dtype=np.float64)                      # k / 6 = integer + 1/2
+    a = (k * 2.0 ** -149).astype(np.float32)
+    b = np.zeros(a.size, np.float32)
+    out = np.empty(a.size, np.float32)
+    emu.emu_cdiff_f32(1, a.ctypes.data, b.ctypes.data, np.float32(3.0), a.size, out.ctypes.data)
+    assert emu.emu_second_fallbacks() == a.size
+    want = (a.astype(np.float64) / 2.0 / 3.0).astype(np.float32)
+    assert np.array_equal(out.view(np.uint32), want.view(np.uint32))
+
+
 @pytest.mark.parametrize("hx,hy", [(1.0, 1.0), (1.0 / 99, 1.0 / 99), (1.0 / 16383, 1.0 / 16383), (0.1, 3.0),
                                    (1.0 / 128, 1.0 / 40), (7.0 / 3, 1e-3), (1.0 / 128, 1.0 / 256), (4.0, 0.25),
                                    (2.0 ** -30, 2.0 ** -30), (2.0 ** 20, 2.0 ** 20)])

@@ -24,7 +24,7 @@ for n in sizes:
             out["took_resident_path"] = s.resident_launch_count() == 2
             if os.environ.get("FLUIDB200_RESIDENT_PROF"):
                 import ctypes as C
-                buf = (C.c_uint64 * 8)()
+                buf = (C.c_uint64 * 24)()
                 s._lib.fluidb200_resident_profile(s._h, buf)
                 out["cycles_per_step"] = {k: round(buf[i] / S) for i, k in enumerate(("halo+barrier", "tentative", "rhs", "sweeps", "corrector", "writeback"))}
         s.close()
