@@ -283,7 +283,9 @@ int fluidb200_set_use_graph(fluidb200_solver* s, int enable);      /* replay ste
 int fluidb200_set_resident(fluidb200_solver* s, int enable);
 int64_t fluidb200_resident_launch_count(const fluidb200_solver* s); /* solve() calls that took that path */
 /* Measurement aid: SM cycles one tile spent per phase of the last such launch when FLUIDB200_RESIDENT_PROF=1
- * (halo load + barrier, tentative velocity, right-hand side, sweeps, corrector, write-back, -, -). */
+ * (out[0..5]: halo load + barrier, tentative velocity, right-hand side, sweeps, corrector, write-back; a library built
+ * with -DFLUIDB200_RESIDENT_SUBPROF=1 also splits the sweeps into out[8..12]: waiting for the neighbours' rows, first + last
+ * row and their publication, rows between, fix-ups + columns, CTA barrier, and counts polling rounds in out[13]). */
 int fluidb200_resident_profile(fluidb200_solver* s, unsigned long long out[24]);
 /* Kernels launched by this solver since creation (for bench.py's gpu_launches). */
 int64_t fluidb200_launch_count(const fluidb200_solver* s);         /* kernels launched so far (a split Jacobi launch = 3) */
