@@ -363,10 +363,10 @@ template <typename T> int launch_predictor(const fb::PredictorArgs<T>& a, int nc
     constexpr int V = fb::VecWidth<T>::V;
     const dim3 grid = grid_for(a.g.nstrips, nchunks);
     cudaStream_t st = (cudaStream_t)stream;
-    // the arithmetic mode is a compile-time property of the kernel (see Metric::mode); fp64 has modes 0 and 2
+    // the arithmetic mode is a compile-time property of the kernel (see Metric::mode)
     const size_t smem = (size_t)FLUIDB200_PRED_D * 2 * 16 * kThreads;  // per-lane cp.async ring: D slots x {u, v} x 16 B
     if (a.m.mode == 2) launch_k(predictor_kernel<T, V, 2>, grid, smem, st, a);
-    else if (sizeof(T) == 4 && a.m.mode == 1) launch_k(predictor_kernel<T, V, (sizeof(T) == 4 ? 1 : 0)>, grid, smem, st, a);
+    else if (a.m.mode == 1) launch_k(predictor_kernel<T, V, 1>, grid, smem, st, a);
     else launch_k(predictor_kernel<T, V, 0>, grid, smem, st, a);
     ++g_kernels;
     return rc_of(cudaGetLastError());
@@ -376,12 +376,12 @@ template <typename T> int launch_corrector(const fb::CorrectorArgs<T>& a, bool m
     constexpr int V = fb::VecWidth<T>::V;
     const dim3 grid = grid_for(a.g.nstrips, nchunks);
     cudaStream_t st = (cudaStream_t)stream;
-    const int mode = a.m.mode;  // (fp64 never reports mode 1)
+    const int mode = a.m.mode;
     if (mask) {  // the general-BC path is not specialised further
-        if (mode != 0) launch_k(corrector_kernel<T, V, true, (sizeof(T) == 4 ? 1 : 0)>, grid, 0, st, a);
+        if (mode != 0) launch_k(corrector_kernel<T, V, true, 1>, grid, 0, st, a);
         else launch_k(corrector_kernel<T, V, true, 0>, grid, 0, st, a);
     } else if (mode == 2) launch_k(corrector_kernel<T, V, false, 2>, grid, 0, st, a);
-    else if (mode == 1) launch_k(corrector_kernel<T, V, false, (sizeof(T) == 4 ? 1 : 0)>, grid, 0, st, a);
+    else if (mode == 1) launch_k(corrector_kernel<T, V, false, 1>, grid, 0, st, a);
     else launch_k(corrector_kernel<T, V, false, 0>, grid, 0, st, a);
     ++g_kernels;
     return rc_of(cudaGetLastError());

@@ -545,7 +545,7 @@ FB_DEV void resident_body(const ResidentArgs<T>& A) {
         }
     };
     using M0 = ModeTag<DIV_EXACT>;
-    using M1 = ModeTag<(sizeof(T) == 4) ? DIV_FAST : DIV_EXACT>;
+    using M1 = ModeTag<DIV_FAST>;
     using M2 = ModeTag<DIV_POW2>;
     const int mode = A.pa.m.mode;   // (grid-uniform)
 
@@ -788,7 +788,7 @@ FB_DEV void resident_cell_body(const ResidentArgs<T>& A) {
         }
     };
     using M0 = ModeTag<DIV_EXACT>;
-    using M1 = ModeTag<(sizeof(T) == 4) ? DIV_FAST : DIV_EXACT>;
+    using M1 = ModeTag<DIV_FAST>;
     using M2 = ModeTag<DIV_POW2>;
 
     T* src = pbuf0;

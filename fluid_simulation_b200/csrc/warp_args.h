@@ -70,8 +70,16 @@ template <typename T> inline Metric<T> make_metric(T hx, T hy, int forced_mode =
         const double lo = 9.094947017729282e-13 /* 2^-40 */, hi = 1099511627776.0 /* 2^40 */;
         const bool sane = (double)hx >= lo && (double)hx <= hi && (double)hy >= lo && (double)hy <= hi;
         const bool pow2 = metric_is_pow2((double)hx) && metric_is_pow2((double)hy);
-        if (sane) m.mode = pow2 ? 2 : (sizeof(T) == 4 ? 1 : 0);  // fp64: exact reciprocals or IEEE divisions
-        if (forced_mode >= 0 && forced_mode < m.mode) m.mode = sizeof(T) == 4 ? forced_mode : 0;  // only ever towards "more exact"
+        if (sane) m.mode = pow2 ? 2 : 1;
+        if (forced_mode >= 0 && forced_mode < m.mode) m.mode = forced_mode;  // only ever towards "more exact"
+        if (m.mode == 1 && sizeof(T) == 8) {
+            // fp64 mode 1 corrects quotients by the constants 2hx, 2hy, hx, hy with fused multiply-adds; a divisor whose
+            // significand is all ones is the one case that correction is not proven for: IEEE divisions there
+            union { double d; unsigned long long u; } a, b;
+            a.d = (double)hx; b.d = (double)hy;
+            const unsigned long long ones = 0x000fffffffffffffULL;
+            if ((a.u & ones) == ones || (b.u & ones) == ones) m.mode = 0;
+        }
     }
     return m;
 }

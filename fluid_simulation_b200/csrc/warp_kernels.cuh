@@ -140,7 +140,9 @@ template <> struct Ar<float> {
     // RN32(D * 2^k) = RN32(D) * 2^k = fmaf(-4, c, s) * 2^k (double rounding of a float sum is
     // innocuous); values at the edge of the subnormal range are flagged.
     template <int MODE>
-    static FB_DEV float lap_tail(float s, float c, float hx, float hy, double inv_hxhy, float inv_hxhyf, Flags& fl) {
+    static FB_DEV float lap_tail(float s, float c, const Metric<float>& m, Flags& fl) {
+        const float hx = m.hx, hy = m.hy, inv_hxhyf = m.inv_hxhyf;
+        const double inv_hxhy = m.inv_hxhy;
         if (MODE == DIV_EXACT) {
             double t = __fma_rn(-4.0, (double)c, (double)s);
             t = __ddiv_rn(t, (double)hx);
@@ -176,18 +178,44 @@ template <> struct Ar<double> {
     static FB_DEV double mul(double a, double b) { return __dmul_rn(a, b); }
     // DIV_POW2 (hx, hy powers of two): x / h and x * (1/h) are the same real number rounded once, for
     // every x including subnormal results, so each division becomes one multiplication by an exact
-    // reciprocal and nothing needs a flag. (fp64 has no division-free mode for other spacings.)
-    template <int MODE> static FB_DEV double cdiff(double a, double b, double h, double h2, double inv_h2, double, Flags&) {
-        (void)h2;
-        const double half = __dmul_rn(__dsub_rn(a, b), 0.5);  // "/ 2." is an exact halving
+    // reciprocal and nothing needs a flag.
+    // DIV_FAST (any other spacing): the quotient by a constant h in five fp64 instructions instead of
+    // __ddiv_rn (a reciprocal seed, its refinement and a range branch: the predictor spent 4.1 ms of a
+    // 8192^2 step in them). y = RN(1/h), correctly rounded (the host's division); q0 = RN(d y) is within
+    // 2 ulp of d / h; the remainder d - q h of such a q is a double, so each fused multiply-add computes it
+    // exactly; one correction makes q faithful, and for a faithful q and a correctly rounded reciprocal
+    // the next correction RN(q + r y) is the correctly rounded quotient (Markstein, IBM J. Res. Dev. 34,
+    // 1990; make_metric keeps divisors whose significand is all ones, the one doubtful case, out of
+    // this mode) -- as long as nothing underflows or overflows on the way: d = 0 or 2^-800 <= |d| < 2^800
+    // with the spacings bounded by make_metric; anything else is flagged and redone with IEEE divisions.
+    static FB_DEV double quot(double d, double h, double y, Flags& fl) {
+        const double q0 = __dmul_rn(d, y);
+        double r = __fma_rn(-q0, h, d);
+        double q = __fma_rn(r, y, q0);
+        r = __fma_rn(-q, h, d);
+        q = __fma_rn(r, y, q);
+        const unsigned hi = (unsigned)__double2hiint(d) & 0x7fffffffu;
+        const bool zero = (hi | (unsigned)__double2loint(d)) == 0u;
+        fl.bad |= !zero && (hi - 0x0df00000u /* 2^-800 */) >= (0x71f00000u /* 2^800 */ - 0x0df00000u);
+        return zero ? q0 : q;   // (a zero keeps its sign: the corrections would add +0 to -0)
+    }
+    template <int MODE> static FB_DEV double cdiff(double a, double b, double h, double h2, double inv_h2, double, Flags& fl) {
+        const double d = __dsub_rn(a, b);
+        if (MODE == DIV_FAST) return quot(d, h2, inv_h2, fl);   // d / (2h) is the same real number as (d / 2.) / h, rounded once either way
+        const double half = __dmul_rn(d, 0.5);  // "/ 2." is an exact halving
         if (MODE == DIV_POW2) return __dmul_rn(half, inv_h2 * 2.0);
         return __ddiv_rn(half, h);
     }
-    template <int MODE> static FB_DEV double lap_tail(double s, double c, double hx, double hy, double inv_hxhy, double, Flags&) {
+    template <int MODE> static FB_DEV double lap_tail(double s, double c, const Metric<double>& m, Flags& fl) {
+        const double hx = m.hx, hy = m.hy, inv_hxhy = m.inv_hxhy;
         double d = __fma_rn(-4.0, c, s);  // 4.*c exact -> single rounding
         if (MODE == DIV_POW2) {
             d = __dmul_rn(d, inv_hxhy * hy);       // 1/hx, exact
             return __dmul_rn(d, inv_hxhy * hx);    // 1/hy, exact
+        }
+        if (MODE == DIV_FAST) {   // two divisions, each one rounded like the reference's; 2 RN(1/(2h)) = RN(1/h) exactly
+            d = quot(d, hx, __dmul_rn(2.0, m.inv_hx2), fl);
+            return quot(d, hy, __dmul_rn(2.0, m.inv_hy2), fl);
         }
         d = __ddiv_rn(d, hx);
         return __ddiv_rn(d, hy);
@@ -1050,8 +1078,8 @@ FB_DEV UV<T> tentative_cell(const PredictorArgs<T>& A, T uc, T vc, T uxm, T uxp,
     const T dv_dy = A_::template cdiff<MODE>(vyp, vym, A.m.hy, A.m.hy2, A.m.inv_hy2, A.m.inv_hy2f, fl);
     const T su = A_::add(A_::add(A_::add(uxm, uxp), uyp), uym);
     const T sv = A_::add(A_::add(A_::add(vxm, vxp), vyp), vym);
-    const T u_lap = A_::template lap_tail<MODE>(su, uc, A.m.hx, A.m.hy, A.m.inv_hxhy, A.m.inv_hxhyf, fl);
-    const T v_lap = A_::template lap_tail<MODE>(sv, vc, A.m.hx, A.m.hy, A.m.inv_hxhy, A.m.inv_hxhyf, fl);
+    const T u_lap = A_::template lap_tail<MODE>(su, uc, A.m, fl);
+    const T v_lap = A_::template lap_tail<MODE>(sv, vc, A.m, fl);
     const T du_dt = A_::sub(A_::sub(A_::mul(A.nu, u_lap), A_::mul(uc, du_dx)), A_::mul(vc, du_dy));
     const T dv_dt = A_::sub(A_::sub(A_::mul(A.nu, v_lap), A_::mul(uc, dv_dx)), A_::mul(vc, dv_dy));
     UV<T> r;

@@ -195,7 +195,7 @@ template <typename T> int launch_predictor(const fb::PredictorArgs<T>& a, int nc
     set_ranges({a.u, a.v, a.us, a.vs, a.rhs}, (size_t)a.g.rows * a.g.pitch * sizeof(T));
     const int mode = a.m.mode;
     if (mode == 2) run_grid(a.g.nstrips, nchunks, [&](int s, int c, int l) { fb::predictor_task<T, V, 2>(a, s, c, l, l, 32); });
-    else if (mode == 1) run_grid(a.g.nstrips, nchunks, [&](int s, int c, int l) { fb::predictor_task<T, V, (sizeof(T) == 4 ? 1 : 0)>(a, s, c, l, l, 32); });
+    else if (mode == 1) run_grid(a.g.nstrips, nchunks, [&](int s, int c, int l) { fb::predictor_task<T, V, 1>(a, s, c, l, l, 32); });
     else run_grid(a.g.nstrips, nchunks, [&](int s, int c, int l) { fb::predictor_task<T, V, 0>(a, s, c, l, l, 32); });
     return 0;
 }
@@ -204,10 +204,10 @@ template <typename T> int launch_corrector(const fb::CorrectorArgs<T>& a, bool m
     set_ranges({a.p, a.us, a.vs, a.u, a.v}, (size_t)a.g.rows * a.g.pitch * sizeof(T));
     const int mode = a.m.mode;
     if (mask) {
-        if (mode != 0) run_grid(a.g.nstrips, nchunks, [&](int s, int c, int l) { fb::corrector_task<T, V, true, (sizeof(T) == 4 ? 1 : 0)>(a, s, c, l); });
+        if (mode != 0) run_grid(a.g.nstrips, nchunks, [&](int s, int c, int l) { fb::corrector_task<T, V, true, 1>(a, s, c, l); });
         else run_grid(a.g.nstrips, nchunks, [&](int s, int c, int l) { fb::corrector_task<T, V, true, 0>(a, s, c, l); });
     } else if (mode == 2) run_grid(a.g.nstrips, nchunks, [&](int s, int c, int l) { fb::corrector_task<T, V, false, 2>(a, s, c, l); });
-    else if (mode == 1) run_grid(a.g.nstrips, nchunks, [&](int s, int c, int l) { fb::corrector_task<T, V, false, (sizeof(T) == 4 ? 1 : 0)>(a, s, c, l); });
+    else if (mode == 1) run_grid(a.g.nstrips, nchunks, [&](int s, int c, int l) { fb::corrector_task<T, V, false, 1>(a, s, c, l); });
     else run_grid(a.g.nstrips, nchunks, [&](int s, int c, int l) { fb::corrector_task<T, V, false, 0>(a, s, c, l); });
     return 0;
 }
@@ -275,31 +275,40 @@ template <int MODE> static void lap_hook(const float* s, const float* c, float h
     const fb::Metric<float> m = fb::make_metric<float>(hx, hy);
     for (long long i = 0; i < n; ++i) {
         fb::Flags fl;
-        out[i] = fb::Ar<float>::lap_tail<MODE>(s[i], c[i], m.hx, m.hy, m.inv_hxhy, m.inv_hxhyf, fl);
+        out[i] = fb::Ar<float>::lap_tail<MODE>(s[i], c[i], m, fl);
         if (fl.raised(m.pow2_lo_m1)) {
             constexpr int FB = fb::FallbackMode<float, MODE>::value;
             fb::Flags f2;
-            out[i] = fb::Ar<float>::lap_tail<FB>(s[i], c[i], m.hx, m.hy, m.inv_hxhy, m.inv_hxhyf, f2);
-            if (FB == fb::DIV_FAST_CHECKED && f2.bad) { out[i] = fb::Ar<float>::lap_tail<fb::DIV_EXACT>(s[i], c[i], m.hx, m.hy, m.inv_hxhy, m.inv_hxhyf, f2); ++g_second_fallbacks; }
+            out[i] = fb::Ar<float>::lap_tail<FB>(s[i], c[i], m, f2);
+            if (FB == fb::DIV_FAST_CHECKED && f2.bad) { out[i] = fb::Ar<float>::lap_tail<fb::DIV_EXACT>(s[i], c[i], m, f2); ++g_second_fallbacks; }
         }
     }
 }
 extern "C" int emu_metric_mode_f32(float hx, float hy) { return fb::make_metric<float>(hx, hy).mode; }
 extern "C" int emu_metric_mode_f64(double hx, double hy) { return fb::make_metric<double>(hx, hy).mode; }
 // fp64: mode 2 (power-of-two spacing) against mode 0, element-wise
-extern "C" void emu_cdiff_f64(int mode, const double* a, const double* b, double h, long long n, double* out) {
+// fp64: modes 2 (power-of-two spacing) and 1 (quotients by FMA corrections, flagged elements redone) against mode 0, element-wise
+template <int MODE> static void cdiff64_hook(const double* a, const double* b, double h, long long n, double* out) {
     const fb::Metric<double> m = fb::make_metric<double>(h, h);
-    fb::Flags fl;
-    for (long long i = 0; i < n; ++i)
-        out[i] = mode == 2 ? fb::Ar<double>::cdiff<2>(a[i], b[i], m.hx, m.hx2, m.inv_hx2, 0.0, fl)
-                           : fb::Ar<double>::cdiff<0>(a[i], b[i], m.hx, m.hx2, m.inv_hx2, 0.0, fl);
+    for (long long i = 0; i < n; ++i) {
+        fb::Flags fl;
+        out[i] = fb::Ar<double>::cdiff<MODE>(a[i], b[i], m.hx, m.hx2, m.inv_hx2, 0.0, fl);
+        if (fl.raised(m.pow2_lo_m1)) { out[i] = fb::Ar<double>::cdiff<fb::DIV_EXACT>(a[i], b[i], m.hx, m.hx2, m.inv_hx2, 0.0, fl); ++g_second_fallbacks; }
+    }
+}
+template <int MODE> static void lap64_hook(const double* s, const double* c, double hx, double hy, long long n, double* out) {
+    const fb::Metric<double> m = fb::make_metric<double>(hx, hy);
+    for (long long i = 0; i < n; ++i) {
+        fb::Flags fl;
+        out[i] = fb::Ar<double>::lap_tail<MODE>(s[i], c[i], m, fl);
+        if (fl.raised(m.pow2_lo_m1)) { out[i] = fb::Ar<double>::lap_tail<fb::DIV_EXACT>(s[i], c[i], m, fl); ++g_second_fallbacks; }
+    }
+}
+extern "C" void emu_cdiff_f64(int mode, const double* a, const double* b, double h, long long n, double* out) {
+    if (mode == 2) cdiff64_hook<2>(a, b, h, n, out); else if (mode == 1) cdiff64_hook<1>(a, b, h, n, out); else cdiff64_hook<0>(a, b, h, n, out);
 }
 extern "C" void emu_lap_tail_f64(int mode, const double* s, const double* c, double hx, double hy, long long n, double* out) {
-    const fb::Metric<double> m = fb::make_metric<double>(hx, hy);
-    fb::Flags fl;
-    for (long long i = 0; i < n; ++i)
-        out[i] = mode == 2 ? fb::Ar<double>::lap_tail<2>(s[i], c[i], m.hx, m.hy, m.inv_hxhy, 0.0, fl)
-                           : fb::Ar<double>::lap_tail<0>(s[i], c[i], m.hx, m.hy, m.inv_hxhy, 0.0, fl);
+    if (mode == 2) lap64_hook<2>(s, c, hx, hy, n, out); else if (mode == 1) lap64_hook<1>(s, c, hx, hy, n, out); else lap64_hook<0>(s, c, hx, hy, n, out);
 }
 extern "C" void emu_cdiff_f32(int mode, const float* a, const float* b, float h, long long n, float* out) {
     if (mode == 2) cdiff_hook<2>(a, b, h, n, out); else if (mode == 1) cdiff_hook<1>(a, b, h, n, out); else cdiff_hook<0>(a, b, h, n, out);

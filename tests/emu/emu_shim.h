@@ -86,4 +86,5 @@ inline float __fmaf_rn(float a, float b, float c) { return std::fma(a, b, c); }
 inline float __double2float_rn(double a) { return (float)a; }
 inline unsigned __float_as_uint(float a) { unsigned b; std::memcpy(&b, &a, 4); return b; }
 inline double __hiloint2double(int hi, int lo) { unsigned long long b = ((unsigned long long)(unsigned)hi << 32) | (unsigned)lo; double d; std::memcpy(&d, &b, 8); return d; }
+inline int __double2hiint(double a) { long long b; std::memcpy(&b, &a, 8); return (int)((unsigned long long)b >> 32); }
 inline int __double2loint(double a) { long long b; std::memcpy(&b, &a, 8); return (int)(b & 0xffffffffLL); }

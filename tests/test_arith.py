@@ -158,13 +158,12 @@ def test_laplacian_tail_ambiguous_cases_take_the_exact_path(emu):
 
 @pytest.mark.parametrize("hx,hy", [(1.0, 1.0), (1.0 / 128, 1.0 / 256), (4.0, 0.25), (2.0 ** -30, 2.0 ** -30), (2.0 ** 20, 2.0 ** 20)])
 def test_fp64_power_of_two_mode_is_the_division(emu, hx, hy):
-    """fp64 has one division-free mode: with power-of-two spacings every division is a multiplication
-    by an exact reciprocal, i.e. the same real number rounded once -- for every input, subnormal
-    results included, so there is nothing to flag."""
+    """fp64 with power-of-two spacings: every division is a multiplication by an exact reciprocal, i.e. the
+    same real number rounded once -- for every input, subnormal results included, so there is nothing to flag."""
     emu.emu_cdiff_f64.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_double, C.c_longlong, C.c_void_p]
     emu.emu_lap_tail_f64.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_double, C.c_double, C.c_longlong, C.c_void_p]
     emu.emu_metric_mode_f64.argtypes = [C.c_double, C.c_double]
-    assert emu.emu_metric_mode_f64(hx, hy) == 2 and emu.emu_metric_mode_f64(0.1, hy) == 0
+    assert emu.emu_metric_mode_f64(hx, hy) == 2 and emu.emu_metric_mode_f64(0.1, hy) == 1
     n = 200_000
     rng = np.random.default_rng(11)
     def inputs(seed):
@@ -187,3 +186,57 @@ def test_fp64_power_of_two_mode_is_the_division(emu, hx, hy):
             call(mode, out)
             ok = (out.view(np.uint64) == want.view(np.uint64)) | (np.isnan(out) & np.isnan(want))
             assert ok.all(), f"mode {mode}: {np.count_nonzero(~ok)} mismatches"
+
+
+def test_fp64_quotients_by_fma_corrections_are_the_divisions(emu):
+    """fp64, spacings that are not powers of two (mode 1): every division by a constant is a multiplication by the
+    rounded reciprocal plus two remainder corrections by FMA. Against NumPy's IEEE divisions over 300 spacings:
+    the whole double range (what underflows or overflows on the way is flagged and redone), and numerators built
+    so that the quotient sits on or next to the midpoint of two doubles (via x87 extended precision), the inputs
+    a wrong last-bit correction gets wrong."""
+    emu.emu_cdiff_f64.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_double, C.c_longlong, C.c_void_p]
+    emu.emu_lap_tail_f64.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_double, C.c_double, C.c_longlong, C.c_void_p]
+    emu.emu_metric_mode_f64.argtypes = [C.c_double, C.c_double]
+    emu.emu_second_fallbacks.restype = C.c_longlong
+    assert np.finfo(np.longdouble).nmant >= 63, "needs x87 extended precision to build double midpoints"
+    rng = np.random.default_rng(21)
+    n = 40_000
+    hs = list(np.exp2(rng.uniform(-20, 6, 280)))
+    hs += [1.0 / 999, 1.0 / 40, 1.0 / 16383, 0.1, 0.3, 3.0, 1.0 / 3, np.nextafter(1.0, 0.0), np.nextafter(0.25, 1.0), np.nextafter(np.nextafter(2.0, 0.0), 0.0)]
+    assert emu.emu_metric_mode_f64(np.nextafter(1.0, 0.0), 0.1) == 0      # significand all ones: IEEE divisions
+    bad = []
+    for k, hx in enumerate(hs):
+        hx = float(hx)
+        hy = float(hs[(k * 7 + 3) % len(hs)])
+        if emu.emu_metric_mode_f64(hx, hy) != 1:
+            continue
+        r = np.random.default_rng(1000 + k)
+        a = r.uniform(1.0, 2.0, n) * np.exp2(r.integers(-1074, 1000, n).astype(np.float64)) * r.choice([-1.0, 1.0], n)
+        a[r.integers(0, n, n // 50)] = 0.0
+        a[r.integers(0, n, n // 50)] = -0.0
+        b = np.zeros(n)
+        # quotients on the midpoints of doubles in [1, 2) times a power of two: d = RN64(m * 2hx), and for the
+        # Laplacian tail D = RN64(RN80(m * hx) * hy), computed in extended precision
+        m = r.uniform(1.0, 2.0, n // 2).astype(np.longdouble) + np.longdouble(2.0) ** -53
+        sc = np.exp2(r.integers(-200, 200, n // 2).astype(np.float64)).astype(np.longdouble)
+        a[: n // 2] = (m * sc * np.longdouble(2.0 * hx)).astype(np.float64)
+        with np.errstate(all="ignore"):
+            want = (a - b) / 2.0 / hx
+        out = np.empty(n)
+        emu.emu_second_fallbacks()
+        emu.emu_cdiff_f64(1, a.ctypes.data, b.ctypes.data, hx, n, out.ctypes.data)
+        redone = emu.emu_second_fallbacks()
+        ok = (out.view(np.uint64) == want.view(np.uint64)) | (np.isnan(out) & np.isnan(want))
+        if not ok.all():
+            bad.append(("cdiff", hx, int(np.count_nonzero(~ok)), a[~ok][:2].tolist()))
+        assert redone < n // 3, "the corrected quotient is meant to cover the working range"
+        c = np.zeros(n)
+        s_ = a.copy()
+        s_[: n // 2] = ((m * sc * np.longdouble(hx)) * np.longdouble(hy)).astype(np.float64)
+        with np.errstate(all="ignore"):
+            want = (s_ - 4.0 * c) / hx / hy
+        emu.emu_lap_tail_f64(1, s_.ctypes.data, c.ctypes.data, hx, hy, n, out.ctypes.data)
+        ok = (out.view(np.uint64) == want.view(np.uint64)) | (np.isnan(out) & np.isnan(want))
+        if not ok.all():
+            bad.append(("lap", hx, hy, int(np.count_nonzero(~ok)), s_[~ok][:2].tolist()))
+    assert not bad, bad[:5]
