@@ -363,11 +363,11 @@ def test_fp64_power_of_two_spacing(Solver, X, Y):
 
 
 @pytest.mark.parametrize("X,Y,K,chunk,dtype", [(256, 100, 5, None, "float32"), (300, 77, 3, 20, "float32"), (200, 40, 2, 16, "float64"),
-                                               (333, 150, 9, 44, "float32")])
+                                               (333, 150, 9, 44, "float32"), (400, 64, 3, 100, "float32"), (530, 40, 4, 128, "float64")])
 def test_migrate_solve_pipelined_over_row_chunks(Solver, env, X, Y, K, chunk, dtype):
     """fluidb200_migrate_solve with one timestep: upload, compute and download run chunk by chunk, every chunk
-    on its rows plus K+2 recomputed halo rows. Host results and the state left on the device equal the plain
-    upload + solve + download, and the oracle."""
+    on its rows plus K+2 recomputed halo rows (the last two cases have a last chunk long enough to be cut in three).
+    Host results and the state left on the device equal the plain upload + solve + download, and the oracle."""
     if chunk:
         env["FLUIDB200_E2E_CHUNK"] = str(chunk)
     rng = np.random.default_rng(X + Y)
