@@ -681,7 +681,7 @@ template <typename T, int NC>
 FB_DEV void resident_cell_body(const ResidentArgs<T>& A) {
     extern __shared__ __align__(16) unsigned char fb_res_smem[];
     using A_ = Ar<T>;
-    const int tid = threadIdx.x;
+    const int tid = threadIdx.x, NT = blockDim.x;   // (NC * NT >= cells: the planner's choice)
     const int X = A.X, Y = A.Y, n = X * Y;
     const long long pitch = A.pitch;
     const int NP = n + 4;                      // + one slot per edge for its constant
@@ -700,7 +700,7 @@ FB_DEV void resident_cell_body(const ResidentArgs<T>& A) {
     const bool bconst = A.pmode[BOTTOM] == EDGE_CONST, tconst = A.pmode[TOP] == EDGE_CONST;
 #pragma unroll
     for (int k = 0; k < NC; ++k) {
-        const int c = tid + k * kCellThreads;
+        const int c = tid + k * NT;
         const int x = c / Y, y = c - x * Y;
         cell[k] = c;
         interior[k] = c < n && x >= 1 && x <= X - 2 && y >= 1 && y <= Y - 2;
@@ -711,7 +711,7 @@ FB_DEV void resident_cell_body(const ResidentArgs<T>& A) {
         b[k] = T(0);
     }
     // load the state
-    for (int c = tid; c < n; c += kCellThreads) {
+    for (int c = tid; c < n; c += NT) {
         const int x = c / Y, y = c - x * Y;
         const long long o = (long long)x * pitch + y;
         pbuf0[c] = A.f[2][o];
@@ -824,7 +824,7 @@ FB_DEV void resident_cell_body(const ResidentArgs<T>& A) {
     }
 
     // write the state back. `src` holds the final p on the interior, `dst` the state before the last sweep.
-    for (int c = tid; c < n; c += kCellThreads) {
+    for (int c = tid; c < n; c += NT) {
         const int x = c / Y, y = c - x * Y;
         const long long o = (long long)x * pitch + y;
         const bool xin = x >= 1 && x <= X - 2, yin = y >= 1 && y <= Y - 2;
