@@ -51,8 +51,9 @@ template <typename T> struct Ar;
 // The two divisions of the path come in three flavours, selected by MODE (Metric::mode):
 //   DIV_EXACT  the reference's operations literally (IEEE divisions);
 //   DIV_FAST   a division-free evaluation that is provably equal except for inputs it flags in
-//              `bad`; the caller recomputes a flagged row with DIV_EXACT. Flags are OR-ed, never
-//              branched on, so the ~40 independent chains of a row can overlap;
+//              `bad`; the caller evaluates a flagged row a second time (FallbackMode below). Flags are
+//              OR-ed, never branched on, so the ~40 independent chains of a row can overlap. fp32: one
+//              product in double per division; fp64: reciprocal multiply + two FMA remainder corrections;
 //   DIV_POW2   hx and hy are powers of two (unit spacing, 2^k+1 points on a unit box, ...): every
 //              division is an exact scaling, i.e. one correctly rounded multiplication.
 enum { DIV_EXACT = 0, DIV_FAST = 1, DIV_POW2 = 2, DIV_POW2_WIDE = 3, DIV_FAST_CHECKED = 4 };
@@ -62,9 +63,10 @@ enum { DIV_EXACT = 0, DIV_FAST = 1, DIV_POW2 = 2, DIV_POW2_WIDE = 3, DIV_FAST_CH
 //     scaling, so the flagged cells (results in the subnormal range, where the float product would round
 //     twice) need no division either: the Laplacian numerator is formed in double, scaled and rounded
 //     once, which is the reference's evaluation to the letter.
-//   DIV_FAST -> DIV_FAST_CHECKED -> DIV_EXACT. The same products as DIV_FAST, each one verified by
+//   DIV_FAST -> DIV_FAST_CHECKED -> DIV_EXACT (fp32). The same products as DIV_FAST, each one verified by
 //     rounding the two ends of an interval that holds the reference's double (Ar<float>::rounds_alike);
 //     only a cell that fails this (a tie, or nearly one) takes the divisions.
+//   fp64: DIV_FAST -> DIV_EXACT (numerators whose corrections would underflow or overflow).
 template <typename T, int MODE> struct FallbackMode {
     static constexpr int value = sizeof(T) != 4 ? DIV_EXACT : MODE == DIV_POW2 ? DIV_POW2_WIDE : MODE == DIV_FAST ? DIV_FAST_CHECKED : DIV_EXACT;
 };
