@@ -33,8 +33,12 @@ constexpr int kThreads = fb::kWarpsPerCta * 32;
 
 // Resident CTAs per SM the register allocator must leave room for: the pipeline is latency bound
 // (ncu: ~50 % issue, ~50 % DRAM at 12 warps/SM), so shallow depths trade registers for warps.
+// Depth 8 is capped at 168 registers (56 bytes spilled) although the kernel wants 210: in a split launch it
+// runs the wall chunks underneath the lean kernel, and a 210-register CTA takes the place of TWO lean CTAs
+// (3 x 162 registers fill the file) where a 168-register one takes one: 568 -> 564 us per launch at 16384^2,
+// 321 -> 316 us on a 4096 x 32768 slab (depth 7: no gain, left at 2).
 #ifndef FLUIDB200_JACOBI_MIN_BLOCKS
-#define FLUIDB200_JACOBI_MIN_BLOCKS(K) ((K) <= 2 ? 5 : (K) <= 4 ? 4 : (K) <= 6 ? 3 : 2)
+#define FLUIDB200_JACOBI_MIN_BLOCKS(K) ((K) <= 2 ? 5 : (K) <= 4 ? 4 : (K) <= 6 ? 3 : (K) == 8 ? 3 : 2)
 #endif
 // Programmatic dependent launch (sm_90+): a kernel launched with the attribute below may be scheduled
 // while its predecessor in the stream is still running; it announces at once that its own successor
