@@ -64,7 +64,7 @@ constexpr int kJacobiTasks = 148 * 16 * 9, kJacobiTasksDeep = 148 * 16 * 5, kLig
 // compiled for, and a partial last wave showed up as a 10-15 % loss at 16384^2. A chunk that
 // touches a wall must hold >= 2 rows because the wall row is derived while its neighbour row is
 // produced.
-void plan_chunks(int n, int halo, int nstrips, int ctas_per_sm, int default_tasks, int* rpc_out, int* nchunks_out) {
+void plan_chunks(int n, int halo, int nstrips, int ctas_per_sm, int default_tasks, int* rpc_out, int* nchunks_out, int rpc_hint = 0) {
     const long long target_tasks = env_int("FLUIDB200_TARGET_TASKS", default_tasks);
     int min_rpc = env_int("FLUIDB200_MIN_RPC", 0);
     const long long ctas_x = (nstrips + fb::kWarpsPerCta - 1) / fb::kWarpsPerCta;
@@ -81,6 +81,7 @@ void plan_chunks(int n, int halo, int nstrips, int ctas_per_sm, int default_task
     if (aligned >= 1 && !env_int("FLUIDB200_NO_WAVE_ALIGN", 0)) want_chunks = aligned;
     int rpc = (int)((n + want_chunks - 1) / want_chunks);
     rpc = std::max(rpc, min_rpc);
+    if (rpc_hint > 0 && target_tasks == default_tasks) rpc = rpc_hint;   // (the caller's measured choice; the task knob overrides it)
     const int fixed = env_int("FLUIDB200_RPC", 0);
     if (fixed > 0) rpc = fixed;
     rpc = std::max(2, std::min(rpc, n));
@@ -254,6 +255,20 @@ int poisson_t(const fluidb200_slab* g, const void* p_in, void* p_out, const void
     // us per launch with 2 / 3 / 5 / 7 waves: 4096 rows 315 / 315 / 331 / 340; 16384 rows (16384 columns) - / 590 / 584 / 591.
     const int nrows = out_hi - out_lo;
     const int tasks = sweeps >= 7 ? 148 * 16 * std::max(2, std::min(5, nrows / 2700)) : 148 * 16 * std::max(3, std::min(9, nrows / 1800));
+    // Deep launches on big ranges, from scans of the rows per chunk (profiles/README_r2.md section 5; tools/scan_rpc.sh): a grid
+    // that is an exact number of waves is the WORST choice there, because the wall and y-edge kernels underneath take slots
+    // from the first wave and push the last CTAs into one more. (1) Tall ranges: chunks of ~270 rows (6 % of recomputed halo
+    // rows) once that makes at least 4.4 waves: 16384^2 544-550 us against 563 at exactly 7 waves, 32768 x 8192 556 against
+    // 580. (2) Short, wide ranges (the 4096 x 32768 slab of 8 GPUs): 4.4 waves if the chunks stay >= 150 rows: 305 against 315.
+    int rpc_hint = 0;
+    if (sweeps >= 7) {
+        const double slots = (double)fbk::be_sm_count() * ctas_per_sm, ctas_x = (nstrips + fb::kWarpsPerCta - 1) / fb::kWarpsPerCta;
+        const int inner = nrows - (out_lo == 0 ? 2 * sweeps + 2 : 0) - (out_hi == g->X ? sweeps + 1 : 0);
+        const int by_len = (inner + 269) / 270;
+        const int by_waves = (int)(4.4 * slots / ctas_x);
+        if (by_len * ctas_x >= 4.4 * slots) rpc_hint = (inner + by_len - 1) / by_len;
+        else if (by_waves >= 1 && inner / by_waves >= 150) rpc_hint = (inner + by_waves - 1) / by_waves;
+    }
     // First try: the chunks at an x wall as short as the pipeline allows (the next chunk must start
     // at row >= 2K+2, the previous one end at row <= X-K-2), because only the register-heavy general
     // kernel can run them; the rows between are chunked uniformly and go to the lean kernels.
@@ -262,14 +277,14 @@ int poisson_t(const fluidb200_slab* g, const void* p_in, void* p_out, const void
     a.tail = out_hi == g->X ? sweeps + 1 : 0;
     a.part = 0;
     if (allow_split && (!use_mask || a.mtiles) && (a.head || a.tail) && n - a.head - a.tail >= 4 * sweeps + 8) {
-        plan_chunks(n - a.head - a.tail, sweeps, nstrips, ctas_per_sm, tasks, &rpc, &nchunks);
+        plan_chunks(n - a.head - a.tail, sweeps, nstrips, ctas_per_sm, tasks, &rpc, &nchunks, rpc_hint);
         nchunks += (a.head > 0) + (a.tail > 0);
         a.g = make_geom(g, nstrips, rpc);
         split_jacobi<T>(&a, g, sweeps, nchunks, use_mask);
     }
     if (a.part == 0) {  // no split (small grid, masked sweep, no wall in range): plain uniform chunks
         a.head = a.tail = 0;
-        plan_chunks(n, sweeps, nstrips, ctas_per_sm, tasks, &rpc, &nchunks);
+        plan_chunks(n, sweeps, nstrips, ctas_per_sm, tasks, &rpc, &nchunks, rpc_hint);
         a.g = make_geom(g, nstrips, rpc);
         split_jacobi<T>(&a, g, sweeps, nchunks, use_mask);
         if (!allow_split) a.part = 0;
@@ -704,6 +719,7 @@ bool resident_wanted(const fluidb200_solver* s) {
     const int on = s->resident >= 0 ? s->resident : env_int("FLUIDB200_RESIDENT", 1);
     if (!on) return false;
     if ((long long)s->S * s->K < 2) return false;   // the corner rule needs a sweep before the last one
+    if ((long long)s->S * s->K > (1LL << 30)) return false;   // sweeps are numbered in 32 bits (packet sequence numbers)
     for (int f = 0; f < 3; ++f)
         if (s->mask[f].set) return false;
     for (int e = 0; e < 4; ++e) {
