@@ -701,8 +701,16 @@ template <typename T> bool plan_resident(int X, int Y, fb::ResidentPlan* out) {
                 const size_t smem = fb::resident_smem_bytes<T>(R, wy, wx);
                 if (smem > 220u * 1024u) continue;
                 const int warps = wx * wy;
-                // (columns crossing tiles cannot leave before the whole patch is computed; rows leave first)
-                const double cost = (R * 20.0 + 40.0) * ((warps + 3) / 4) + (ty * tx > 1 ? 1500.0 : 0.0) + (ty > 1 ? 1000.0 : 0.0);
+                // Cycles per sweep, roughly: the arithmetic of the warps sharing a scheduler, plus -- once there are several
+                // tiles -- what crosses them through L2: ~720 cycles per polling round a warp makes one after the other (the
+                // two rows are polled together; a column crossing tiles is one more round, two when a warp has both), and
+                // ~0.62 cycles per value of the CTA's borders. Fitted to forced tilings of 1000^2 (8 x 1024-cell tiles 99.5 ms
+                // per 1000 x 50, 16 x 512 102.3, 32 x 256 94.5, 64 x 128 102.6) and checked on 1000 x 500 and 800 x 1200
+                // (profiles/README_r2.md section 2).
+                const int TC = wy * W, TR = wx * R;
+                const double rounds = (tx > 1 ? 1.0 : 0.0) + (ty > 1 ? (wy == 1 ? 2.0 : 1.0) : 0.0);
+                const double values = (tx > 1 ? 2.0 * TC : 0.0) + (ty > 1 ? 2.0 * TR : 0.0);
+                const double cost = (R * 20.0 + 40.0) * ((warps + 3) / 4) + 720.0 * rounds + 0.62 * values;
                 if (cost < best) {   // (ties keep the taller patch: fewer rows cross shared memory per sweep)
                     best = cost;
                     found = true;

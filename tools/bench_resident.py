@@ -8,9 +8,10 @@ from fluid_simulation_b200 import ParallelNavierStokes
 sizes = [int(a) for a in sys.argv[1:]] or [41, 129, 300, 1000]
 S, K = int(os.environ.get("S", 1000)), int(os.environ.get("K", 50))
 for n in sizes:
-    out = {"grid": n, "steps": S, "sweeps": K}
+    out = {"grid": n if int(os.environ.get("NY", n)) == n else [n, int(os.environ.get("NY", n))], "steps": S, "sweeps": K}
     for resident in (True, False):
-        s = ParallelNavierStokes(n, n, 1.0, 1.0)
+        ny = int(os.environ.get("NY", n))
+        s = ParallelNavierStokes(n, ny, 1.0, 1.0 * (ny - 1) / (n - 1))
         s.time_step = float(np.float32(0.125) * np.float32(1.0 / (n - 1)) ** 2 / np.float32(0.1))
         s.num_poisson_iterations = K
         s.set_resident(resident); s.upload_cavity(1.0)
