@@ -215,3 +215,37 @@ def test_migrate_solve_pipeline_at_size(Solver):
     for n in ("u_next", "v_next", "rhs", "p_next"):
         H.assert_bit_equal(a.device_field(n), b.device_field(n), f"pipeline-device/{n}")
     a.close(); b.close()
+
+
+def test_more_cells_than_a_32_bit_index_holds(Solver):
+    """65538 x 32768 = 2^31 + 65536 cells (8.6 GB per field; the reference's `int` cell index, ParallelNavierStokes.cu:22,
+    overflows here): u, v, p after one step of 8 sweeps are bit-identical for blocking depths 8 and 3 -- different chunk plans,
+    launches and halo rows over the same cells -- compared on the device through zero-copy views; the rows beyond element 2^31
+    are written (the lid drives every row) and the lid column is intact at both ends."""
+    import torch
+    X, Y = 65538, 32768
+    if torch.cuda.mem_get_info()[0] < 110e9:
+        pytest.skip("needs ~90 GB of free device memory")
+    kept = None
+    for kmax in (8, 3):
+        s = Solver(X, Y, float(X - 1), float(Y - 1))
+        s.num_iterations, s.num_poisson_iterations = 1, 8
+        s.set_sweeps_per_launch(kmax)
+        s.upload_cavity(1.0)
+        s.solve(); s.synchronize()
+        views = {n: torch.as_tensor(s.device_array(n), device="cuda") for n in ("u", "v", "p")}
+        assert views["u"].shape == (X, Y)
+        assert bool((views["u"][:, Y - 1] == 1.0).all())
+        tail = views["u"][X - 8: X - 1, Y - 64: Y - 1]                 # interior cells beyond element 2^31, right under the lid
+        assert bool((tail != 0).any()), "rows beyond 2^31 elements were not computed"
+        assert bool(torch.isfinite(views["p"][X - 4:]).all())
+        if kept is None:
+            kept = {n: v.clone() for n, v in views.items()}
+        else:
+            for n, v in views.items():
+                assert torch.equal(kept[n], v), f"{n} differs between blocking depths 8 and 3"
+        del views
+        s.close()
+    del kept
+    torch.cuda.empty_cache()
+
