@@ -171,12 +171,15 @@ def test_interior_strip_fast_paths(Solver, env, X, Y, K, kmax, dtype, rpc):
     s.close()
 
 
-def test_subnormal_front_takes_exact_fallback(Solver):
+@pytest.mark.parametrize("X,Y", [(40, 300), (33, 257)])
+def test_subnormal_front_takes_exact_fallback(Solver, X, Y):
     """A tiny diffusion number makes the values at the advancing front underflow through the
     subnormal range (the reference runs on x86 without flush-to-zero). The fp32 kernels' division-
-    free arithmetic flags those inputs and recomputes the affected rows with IEEE divisions, inside
-    a per-lane branch: this must neither change bits nor deadlock on a warp shuffle."""
-    X, Y, S, K = 40, 300, 9, 2
+    free arithmetic flags those inputs and evaluates the affected rows a second time, inside
+    a per-lane branch: this must neither change bits nor deadlock on a warp shuffle. 40 x 300 points on
+    the unit box: spacings 1/39, 1/299 (checked products, then divisions for ties); 33 x 257: powers
+    of two (the Laplacian tail in double)."""
+    S, K = 9, 2
     o = Oracle(X, Y).set_cavity()
     o.time_step, o.num_iterations, o.num_poisson_iterations = 1e-9, S, K
     s = Solver(X, Y).set_cavity()
@@ -185,7 +188,7 @@ def test_subnormal_front_takes_exact_fallback(Solver):
     o.solve()
     tiny = np.finfo(np.float32).tiny
     assert np.any((np.abs(o.u_next) < tiny) & (o.u_next != 0)), "case no longer produces subnormals"
-    H.compare_with(s, o, tag="subnormal-front")
+    H.compare_with(s, o, tag=f"subnormal-front/{X}x{Y}")
     s.close()
 
 

@@ -193,3 +193,24 @@ def test_what_the_resident_path_declines(Solver, env, golden):
     assert s.resident_launch_count() == 0
     H.compare_with(s, H.load_fields(golden["cavity41_S1_K1"]), tag="single-sweep")
     s.close()
+
+
+@pytest.mark.parametrize("X,Y,layout", [(40, 300, "auto"), (33, 257, "auto"), (33, 257, "patch8"), (40, 300, "patch4")])
+def test_subnormal_front_resident(Solver, env, X, Y, layout):
+    """The front of a starting flow underflows through the subnormal range: the flagged cells take their second evaluation
+    per cell here (checked products for spacings 1/39, 1/299; the double Laplacian tail for the power-of-two spacings of 33 x 257)."""
+    if layout != "auto":
+        env["FLUIDB200_RESIDENT_R"] = layout[-1]
+    S, K = 9, 2
+    o = Oracle(X, Y).set_cavity()
+    o.time_step, o.num_iterations, o.num_poisson_iterations = 1e-9, S, K
+    s = Solver(X, Y).set_cavity()
+    s.time_step, s.num_iterations, s.num_poisson_iterations = 1e-9, S, K
+    s.migrateSolve()
+    _took_resident_path(s)
+    o.solve()
+    tiny = np.finfo(np.float32).tiny
+    assert np.any((np.abs(o.u_next) < tiny) & (o.u_next != 0)), "case no longer produces subnormals"
+    H.compare_with(s, o, tag=f"resident/subnormal-front/{X}x{Y}/{layout}")
+    s.close()
+
