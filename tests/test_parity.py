@@ -408,3 +408,29 @@ def test_migrate_solve_pipelined_over_row_chunks(Solver, env, X, Y, K, chunk, dt
     for n, g in zip(("u", "v", "p"), got2):
         H.assert_bit_equal(g, getattr(o, n), f"migrate_solve/second/{n}")
     a.close()
+
+
+@pytest.mark.parametrize("X,Y,scale", [(37, 150, 1e-262), (64, 131, 1e+250)])
+def test_fp64_numerators_out_of_range_take_the_divisions(Solver, X, Y, scale):
+    """fp64 with a spacing that is not a power of two divides by FMA corrections, valid for numerators in [2^-800, 2^800):
+    fields scaled far below (or above) that range, next to boundary values of order one, send the flagged rows through the
+    IEEE divisions while their neighbours stay on the fast path. (1e+250: products overflow to inf / nan in the reference
+    too; the comparison treats equal non-finite bit patterns and NaNs alike.)"""
+    rng = np.random.default_rng(X * Y)
+    st = {n: (scale * rng.standard_normal((X, Y))) for n in ("u", "v", "p")}
+    pair = []
+    for cls in (Solver, Oracle):
+        q = cls(X, Y, 1.0, 1.0, np.dtype("float64")).set_cavity(1.0)
+        for n in ("u", "v", "p"):
+            (q._hostf(n) if cls is Solver else getattr(q, n))[1:-1, 1:-1] = st[n][1:-1, 1:-1]
+        q.time_step, q.num_iterations, q.num_poisson_iterations = 1e-5, 2, 3
+        pair.append(q)
+    s, o = pair
+    if hasattr(o, "p_next"):
+        o.p_next[:] = o.p
+    with np.errstate(all="ignore"):
+        s.migrateSolve()
+        o.solve()
+    H.compare_with(s, o, tag=f"f64-out-of-range/{X}x{Y}/{scale:g}")
+    s.close()
+

@@ -67,17 +67,17 @@ def test_golden_digests_resident(Solver, env, golden, name):
     s.close()
 
 
-def _random_state(X, Y, dtype, seed):
+def _random_state(X, Y, dtype, seed, scale=0.01):
     rng = np.random.default_rng(seed)
-    return {n: (0.01 * rng.standard_normal((X, Y))).astype(dtype) for n in H.ALL_FIELDS}
+    return {n: (scale * rng.standard_normal((X, Y))).astype(dtype) for n in H.ALL_FIELDS}
 
 
-def _setup_pair(Solver, X, Y, dtype, seed, p_edges="cavity", domain=None):
+def _setup_pair(Solver, X, Y, dtype, seed, p_edges="cavity", domain=None, scale=0.01):
     """A GPU solver and an oracle with the same random initial fields and cavity-style boundaries.
     p_edges: 'cavity' (lid Dirichlet 0, rest copy), 'all_const', 'none', 'mixed'."""
     dtype = np.dtype(dtype)
     wx, wy = domain if domain else (1.0, 1.0)
-    st = _random_state(X, Y, dtype, seed)
+    st = _random_state(X, Y, dtype, seed, scale)
     pair = []
     for cls in (Solver, Oracle):
         s = cls(X, Y, wx, wy, dtype)
@@ -212,5 +212,22 @@ def test_subnormal_front_resident(Solver, env, X, Y, layout):
     tiny = np.finfo(np.float32).tiny
     assert np.any((np.abs(o.u_next) < tiny) & (o.u_next != 0)), "case no longer produces subnormals"
     H.compare_with(s, o, tag=f"resident/subnormal-front/{X}x{Y}/{layout}")
+    s.close()
+
+
+@pytest.mark.parametrize("X,Y,layout", [(41, 41, "auto"), (47, 200, "patch4"), (70, 150, "patch8")])
+def test_fp64_numerators_out_of_range_take_the_divisions(Solver, env, X, Y, layout):
+    """fp64 with a spacing that is not a power of two divides by FMA corrections (Ar<double>::quot), valid for numerators in
+    [2^-800, 2^800): a state scaled to 1e-262 (next to boundary values of order one) puts most differences below that, so
+    the flagged cells go through the IEEE divisions while their neighbours do not."""
+    if layout != "auto":
+        env["FLUIDB200_RESIDENT_R"] = layout[-1]
+    s, o = _setup_pair(Solver, X, Y, "float64", seed=X + Y, p_edges="mixed", scale=1e-262)
+    for q in (s, o):
+        q.time_step, q.num_iterations, q.num_poisson_iterations = 1e-4, 2, 4
+    s.migrateSolve()
+    _took_resident_path(s)
+    o.solve()
+    H.compare_with(s, o, tag=f"resident-f64-tiny/{X}x{Y}/{layout}")
     s.close()
 
